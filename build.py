@@ -1,0 +1,112 @@
+"""In-tree native build: nvcc (sm_100a) for the CUDA kernels, g++ for the host runtime.
+
+Produces two shared libraries next to the Python package (they travel to the GPU box with the
+source snapshot; they are git-ignored):
+
+  deeplearning_mpi_b200/_lib/libdmpi_host.so   TCP store + reducer core       (no CUDA dependency)
+  deeplearning_mpi_b200/_lib/libdmpi_cuda.so   all sm_100a kernels + P2P arena + CUDA reducer glue
+
+Objects are rebuilt only when the content hash of the translation unit, its local headers and the
+flags changes.  Usage:  python build.py [--force] [--verbose]
+"""
+from __future__ import annotations
+
+import concurrent.futures as cf
+import hashlib
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+LIB_DIR = ROOT / "deeplearning_mpi_b200" / "_lib"
+OBJ_DIR = ROOT / "build" / "obj"
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+CXX = os.environ.get("CXX", "g++")
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+    "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC", "-Xptxas", "-v",
+]
+CXX_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-Wall", "-pthread"]
+
+CUDA_SOURCES = sorted(str(p.relative_to(ROOT)) for p in (ROOT / "csrc").rglob("*.cu"))
+HOST_SOURCES = sorted(str(p.relative_to(ROOT)) for p in (ROOT / "csrc").rglob("*.cpp"))
+
+
+def _headers_digest() -> str:
+    h = hashlib.sha256()
+    for pat in ("csrc/**/*.cuh", "csrc/**/*.h", "include/*.h"):
+        for p in sorted(ROOT.glob(pat)):
+            h.update(p.read_bytes())
+    return h.hexdigest()
+
+
+def _digest(src: Path, flags: list[str], hdr: str) -> str:
+    h = hashlib.sha256()
+    h.update(src.read_bytes())
+    h.update(" ".join(flags).encode())
+    h.update(hdr.encode())
+    return h.hexdigest()
+
+
+def _compile(src_rel: str, force: bool, hdr: str, verbose: bool) -> tuple[str, str]:
+    src = ROOT / src_rel
+    is_cu = src.suffix == ".cu"
+    flags = NVCC_FLAGS if is_cu else CXX_FLAGS
+    obj = OBJ_DIR / (src_rel.replace("/", "__") + ".o")
+    stamp = obj.with_suffix(".hash")
+    dig = _digest(src, flags, hdr)
+    if not force and obj.exists() and stamp.exists() and stamp.read_text() == dig:
+        return str(obj), ""
+    cmd = ([NVCC] + flags if is_cu else [CXX] + flags) + ["-I", str(ROOT / "include"), "-c", str(src), "-o", str(obj)]
+    if not is_cu:
+        cmd += ["-I", "/usr/local/cuda/include"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"compile failed: {' '.join(cmd)}\n{r.stdout}\n{r.stderr}")
+    stamp.write_text(dig)
+    log = r.stderr if is_cu else ""
+    if verbose and log:
+        print(f"--- {src_rel}\n{log}")
+    return str(obj), log
+
+
+def build(force: bool = False, verbose: bool = False) -> dict[str, str]:
+    LIB_DIR.mkdir(parents=True, exist_ok=True)
+    OBJ_DIR.mkdir(parents=True, exist_ok=True)
+    hdr = _headers_digest()
+    logs: dict[str, str] = {}
+    objs: dict[str, str] = {}
+    with cf.ThreadPoolExecutor(max_workers=os.cpu_count() or 4) as ex:
+        futs = {ex.submit(_compile, s, force, hdr, verbose): s for s in CUDA_SOURCES + HOST_SOURCES}
+        for f in cf.as_completed(futs):
+            s = futs[f]
+            objs[s], logs[s] = f.result()
+    (ROOT / "build" / "ptxas.log").write_text("\n".join(f"--- {k}\n{v}" for k, v in sorted(logs.items()) if v))
+
+    host_objs = [objs[s] for s in HOST_SOURCES if "/cudaglue/" not in s]
+    cuda_objs = [objs[s] for s in CUDA_SOURCES]
+    host_lib = LIB_DIR / "libdmpi_host.so"
+    cuda_lib = LIB_DIR / "libdmpi_cuda.so"
+
+    def link(out: Path, inputs: list[str], extra: list[str]) -> None:
+        if not inputs:
+            return
+        newest = max(os.path.getmtime(i) for i in inputs)
+        if not force and out.exists() and os.path.getmtime(out) >= newest:
+            return
+        cmd = [CXX, "-shared", "-o", str(out)] + inputs + extra
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"link failed: {' '.join(cmd)}\n{r.stderr}")
+
+    link(host_lib, host_objs, ["-pthread"])
+    link(cuda_lib, cuda_objs, ["-L/usr/local/cuda/lib64", "-lcudart", "-pthread", "-ldl",
+                               "-Wl,-rpath,/usr/local/cuda/lib64"])
+    return {"host": str(host_lib), "cuda": str(cuda_lib)}
+
+
+if __name__ == "__main__":
+    out = build(force="--force" in sys.argv, verbose="--verbose" in sys.argv)
+    print(out)

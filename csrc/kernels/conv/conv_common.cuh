@@ -1,0 +1,49 @@
+// Shared between the K-major implicit-GEMM kernel (igemm.cu) and the MN-major weight-gradient
+// kernel (wgrad.cu): kernel parameter block and the host-side plan that owns the tensor maps.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../../include/dmpi_conv.h"
+
+namespace dmpi {
+
+struct alignas(64) ConvKernelParams {
+  CUtensorMap a_map[DMPI_MAX_MAPS];  // igemm: A views;  wgrad: X (N-side) views
+  CUtensorMap b_map;                 // igemm: weights;  wgrad: dY (M-side)
+  CUtensorMap o_map[DMPI_MAX_MAPS];  // igemm: output views
+  int ntaps, cblocks;
+  int tap_view[DMPI_MAX_TAPS];
+  int tap_dw[DMPI_MAX_TAPS];
+  int tap_dh[DMPI_MAX_TAPS];
+  int tap_koff[DMPI_MAX_TAPS];
+  int tap_woff[DMPI_MAX_TAPS];
+  int box_w, box_h, box_n, rows;
+  int tiles_w, tiles_h, tiles_n;
+  int grid_w, grid_h, grid_n;
+  int num_m_tiles, num_n_tiles, nblk_per_oview;
+  int n_out;
+  int bias_mod, stat_mod, relu, out_mode;
+  long long out_ld;
+  const float* bias;
+  float* stat_sum;
+  float* stat_sq;
+  float* out_f32;
+  // wgrad
+  float* dw;
+  long long w_ld;
+  int k_out, c_total, splits, num_k_tiles, num_c_tiles;
+};
+
+}  // namespace dmpi
+
+struct dmpi_conv_plan {
+  dmpi_conv_desc desc;
+  dmpi::ConvKernelParams params;
+  const void* cached_a;
+  const void* cached_b;
+  const void* cached_o;
+  bool maps_valid;
+  int num_sms;
+};

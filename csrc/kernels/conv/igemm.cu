@@ -1,0 +1,451 @@
+// Persistent, warp-specialised implicit-GEMM kernel for sm_100a.
+//
+//   D[pixels, n] = sum over taps t, channel blocks cb of  A_t[pixels, cb*64 .. +64] * B[n, koff_t + cb*64 .. +64]^T
+//
+// * A tiles (128 output pixels x 64 channels, bf16) are fetched by TMA from a rank-4 NHWC view; the
+//   filter tap is a coordinate offset and the halo is TMA's out-of-bounds zero fill.  Stride-2
+//   convolutions use one strided view per input parity class, so every tap is still a dense box.
+// * B tiles (BN filters x 64 channels) come from the K-major bf16 weight shadow.
+// * tcgen05.mma (cta_group::1, M=128, N=BN, K=16) accumulates in TMEM; two accumulator stages let the
+//   epilogue of tile i overlap the main loop of tile i+1.
+// * Epilogue warps read TMEM (tcgen05.ld), add bias / ReLU, round to bf16, stage the tile in
+//   128B-swizzled shared memory, issue a TMA store into the (possibly strided / channel-sliced) output
+//   view, and accumulate per-channel sum and sum-of-squares of the stored values for BatchNorm.
+//
+// Roles: warp 0 = TMA producer, warp 1 = MMA issuer, warp 2 = TMEM allocator, warps 4..7 = epilogue.
+//
+// Replaces cuDNN fprop/dgrad and cuBLAS GEMM behind ref:pytorch/unet/model.py:8-14,37-38,68 and
+// torchvision's resnet conv/fc.
+#include <stdio.h>
+#include <string.h>
+
+#include <mutex>
+#include <new>
+
+#include "../../common/ptx.cuh"
+#include "../../common/tensormap.h"
+#include "conv_common.cuh"
+
+namespace dmpi {
+
+constexpr int kThreads = 256;
+constexpr int kTileM = 128;
+constexpr int kBlockK = 64;  // bf16 elements = one 128-byte swizzle row
+constexpr int kABytes = kTileM * kBlockK * 2;
+
+template <int BN>
+struct IgemmCfg {
+  static constexpr int kStages = BN == 256 ? 3 : (BN == 128 ? 5 : 6);
+  static constexpr int kBBytes = BN * kBlockK * 2;
+  static constexpr int kOutBytes = kTileM * BN * 2;
+  static constexpr int kSmemBytes = kStages * (kABytes + kBBytes) + kOutBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int kTmemCols = 2 * BN;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constant__ ConvKernelParams p) {
+  using Cfg = IgemmCfg<BN>;
+  constexpr int S = Cfg::kStages;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem_a + S * kABytes;
+  uint8_t* smem_o = smem_b + S * Cfg::kBBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_o + Cfg::kOutBytes);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + S;
+  uint64_t* tfull = bars + 2 * S;
+  uint64_t* tempty = bars + 2 * S + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * S + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    for (int i = 0; i < DMPI_MAX_MAPS; ++i) tma_prefetch_desc(&p.a_map[i]);
+    tma_prefetch_desc(&p.b_map);
+    tma_prefetch_desc(&p.o_map[0]);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < S; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tfull[i], 1);
+      mbar_init(&tempty[i], 128);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int total_tiles = p.num_m_tiles * p.num_n_tiles;
+  const int num_kb = p.ntaps * p.cblocks;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      const uint32_t tx_bytes = static_cast<uint32_t>(p.rows) * 128u + Cfg::kBBytes;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int n_blk = tile % p.num_n_tiles;
+        const int m_blk = tile / p.num_n_tiles;
+        const int tw = m_blk % p.tiles_w;
+        const int th = (m_blk / p.tiles_w) % p.tiles_h;
+        const int tn = m_blk / (p.tiles_w * p.tiles_h);
+        const int w0 = tw * p.box_w, h0 = th * p.box_h, n0 = tn * p.box_n;
+        for (int t = 0; t < p.ntaps; ++t) {
+          const CUtensorMap* amap = &p.a_map[p.tap_view[t]];
+          const int cw = w0 + p.tap_dw[t], ch = h0 + p.tap_dh[t], koff = p.tap_koff[t];
+          for (int cb = 0; cb < p.cblocks; ++cb) {
+            mbar_wait(&empty[stage], phase ^ 1u);
+            mbar_arrive_expect_tx(&full[stage], tx_bytes);
+            tma_load_4d(smem_a + stage * kABytes, amap, &full[stage], cb * kBlockK, cw, ch, n0);
+            tma_load_2d(smem_b + stage * Cfg::kBBytes, &p.b_map, &full[stage], koff + cb * kBlockK, n_blk * BN);
+            if (++stage == S) {
+              stage = 0;
+              phase ^= 1u;
+            }
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(kTileM, BN, 0, 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        mbar_wait(&tempty[acc], acc_phase ^ 1u);
+        tc_fence_after_sync();
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after_sync();
+          const uint32_t a_addr = smem_u32(smem_a + stage * kABytes);
+          const uint32_t b_addr = smem_u32(smem_b + stage * Cfg::kBBytes);
+#pragma unroll
+          for (int k = 0; k < kBlockK / 16; ++k) {
+            const uint64_t adesc = umma_smem_desc(a_addr + k * 32, 0, 1024);
+            const uint64_t bdesc = umma_smem_desc(b_addr + k * 32, 0, 1024);
+            umma_bf16(d_tmem, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty[stage]);
+          if (++stage == S) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+        umma_commit(&tfull[acc]);
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1u;
+      }
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    // ------------------------------------------------------------------ epilogue
+    const int q = warp - 4;
+    const int row = q * 32 + lane;
+    const int et = threadIdx.x - 128;  // 0..127
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    const int wi = row % p.box_w;
+    const int hi = (row / p.box_w) % p.box_h;
+    const int ni = row / (p.box_w * p.box_h);
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int n_blk = tile % p.num_n_tiles;
+      const int m_blk = tile / p.num_n_tiles;
+      const int tw = m_blk % p.tiles_w;
+      const int th = (m_blk / p.tiles_w) % p.tiles_h;
+      const int tn = m_blk / (p.tiles_w * p.tiles_h);
+      const int w0 = tw * p.box_w, h0 = th * p.box_h, n0 = tn * p.box_n;
+      const bool valid = row < p.rows && (w0 + wi) < p.grid_w && (h0 + hi) < p.grid_h && (n0 + ni) < p.grid_n;
+
+      mbar_wait(&tfull[acc], acc_phase);
+      tc_fence_after_sync();
+      if (p.out_mode == 0) {
+        if (et == 0) tma_store_wait_read0();  // previous tile's TMA store has finished reading smem_o
+        named_bar_sync(1, 128);
+      }
+      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(acc * BN);
+#pragma unroll 1
+      for (int chunk = 0; chunk < BN / 32; ++chunk) {
+        uint32_t v[32];
+        tmem_ld_32x32(t_addr + chunk * 32, v);
+        tmem_ld_wait();
+        const int col0 = n_blk * BN + chunk * 32;
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+        if (p.bias_mod > 0) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int c = col0 + j;
+            if (c < p.n_out) f[j] += __ldg(p.bias + (c % p.bias_mod));
+          }
+        }
+        if (p.relu) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+        }
+        if (p.out_mode == 0) {
+          if (!valid) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = 0.f;
+          }
+          // 128-byte swizzle: 16-byte chunk index XOR (row & 7) inside each 64-channel half.
+          uint8_t* half_base = smem_o + (chunk >> 1) * (kTileM * 128) + row * 128;
+          const int c16_0 = (chunk & 1) * 4;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            uint4 pk;
+            pk.x = pack_bf16x2(f[i * 8 + 0], f[i * 8 + 1]);
+            pk.y = pack_bf16x2(f[i * 8 + 2], f[i * 8 + 3]);
+            pk.z = pack_bf16x2(f[i * 8 + 4], f[i * 8 + 5]);
+            pk.w = pack_bf16x2(f[i * 8 + 6], f[i * 8 + 7]);
+            const int c16 = (c16_0 + i) ^ (row & 7);
+            *reinterpret_cast<uint4*>(half_base + c16 * 16) = pk;
+          }
+        } else if (valid) {
+          float* dst = p.out_f32 + static_cast<long long>(w0 + wi) * p.out_ld + col0;
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (col0 + j < p.n_out) dst[j] = f[j];
+        }
+      }
+      tc_fence_before_sync();
+      mbar_arrive(&tempty[acc]);
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1u;
+
+      if (p.out_mode == 0) {
+        fence_proxy_async_smem();
+        named_bar_sync(1, 128);
+        if (et == 0) {
+          const CUtensorMap* omap = &p.o_map[n_blk / p.nblk_per_oview];
+          const int ch0 = (n_blk % p.nblk_per_oview) * BN;
+#pragma unroll
+          for (int h = 0; h < BN / 64; ++h) {
+            if (n_blk * BN + h * 64 < p.n_out) tma_store_4d(omap, smem_o + h * (kTileM * 128), ch0 + h * 64, w0, h0, n0);
+          }
+          tma_store_commit();
+        }
+        if (p.stat_mod > 0) {
+          // Column sums of the bf16 tile just staged (exactly the values that reach memory).
+          constexpr int kColsPerPass = 128;
+#pragma unroll 1
+          for (int cbase = 0; cbase < BN; cbase += kColsPerPass) {
+            int col, r0, r1;
+            if (BN >= 128) {
+              col = cbase + et;
+              r0 = 0;
+              r1 = kTileM;
+            } else {
+              col = et & 63;
+              r0 = (et >> 6) * 64;
+              r1 = r0 + 64;
+            }
+            const int gcol = n_blk * BN + col;
+            if (gcol < p.n_out) {
+              const uint8_t* hb = smem_o + (col >> 6) * (kTileM * 128);
+              const int c16 = (col & 63) >> 3, within = (col & 7) * 2;
+              float s = 0.f, s2 = 0.f;
+#pragma unroll 8
+              for (int r = r0; r < r1; ++r) {
+                const uint16_t raw = *reinterpret_cast<const uint16_t*>(hb + r * 128 + ((c16 ^ (r & 7)) * 16) + within);
+                const float x = __uint_as_float(static_cast<uint32_t>(raw) << 16);
+                s += x;
+                s2 = fmaf(x, x, s2);
+              }
+              atomicAdd(p.stat_sum + (gcol % p.stat_mod), s);
+              atomicAdd(p.stat_sq + (gcol % p.stat_mod), s2);
+            }
+          }
+        }
+      }
+    }
+    if (p.out_mode == 0 && et == 0) tma_store_wait_all0();
+  }
+
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+}
+
+// ------------------------------------------------------------------------------------------ host
+static thread_local char g_err[512] = {0};
+static void set_err(const char* msg) { snprintf(g_err, sizeof(g_err), "%s", msg); }
+
+static int device_sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+static int encode_view(CUtensorMap* map, const void* base, const dmpi_tensor4& v, int box_c, int bw, int bh, int bn) {
+  const uint8_t* ptr = static_cast<const uint8_t*>(base) + v.offset * 2;
+  int box[4] = {box_c, bw, bh, bn};
+  // TMA box extents may not exceed 256 and need not be clipped to the tensor; they must be >= 1.
+  return encode_bf16_map(map, ptr, 4, v.dims, v.strides, box);
+}
+
+template <int BN>
+static int launch_igemm(const ConvKernelParams& kp, int num_sms, cudaStream_t stream) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e =
+        cudaFuncSetAttribute(igemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, IgemmCfg<BN>::kSmemBytes);
+    if (e != cudaSuccess) {
+      set_err(cudaGetErrorString(e));
+      return -10;
+    }
+    attr_set = true;
+  }
+  const int total = kp.num_m_tiles * kp.num_n_tiles;
+  const int grid = total < num_sms ? total : num_sms;
+  igemm_kernel<BN><<<grid, kThreads, IgemmCfg<BN>::kSmemBytes, stream>>>(kp);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_err(cudaGetErrorString(e));
+    return -11;
+  }
+  return 0;
+}
+
+}  // namespace dmpi
+
+using namespace dmpi;
+
+extern "C" dmpi_conv_plan* dmpi_conv_plan_create(const dmpi_conv_desc* desc) {
+  dmpi_conv_plan* plan = new (std::nothrow) dmpi_conv_plan();
+  if (!plan) return nullptr;
+  memset(&plan->params, 0, sizeof(plan->params));
+  plan->desc = *desc;
+  plan->cached_a = plan->cached_b = plan->cached_o = nullptr;
+  plan->maps_valid = false;
+  plan->num_sms = 0;
+  ConvKernelParams& kp = plan->params;
+  const dmpi_conv_desc& d = plan->desc;
+  kp.ntaps = d.ntaps;
+  kp.cblocks = d.cblocks;
+  for (int t = 0; t < DMPI_MAX_TAPS; ++t) {
+    kp.tap_view[t] = d.tap_view[t];
+    kp.tap_dw[t] = d.tap_dw[t];
+    kp.tap_dh[t] = d.tap_dh[t];
+    kp.tap_koff[t] = d.tap_koff[t];
+    kp.tap_woff[t] = d.tap_woff[t];
+  }
+  kp.box_w = d.box_w;
+  kp.box_h = d.box_h;
+  kp.box_n = d.box_n;
+  kp.rows = d.box_w * d.box_h * d.box_n;
+  kp.grid_w = d.grid_w;
+  kp.grid_h = d.grid_h;
+  kp.grid_n = d.grid_n;
+  kp.tiles_w = (d.grid_w + d.box_w - 1) / d.box_w;
+  kp.tiles_h = (d.grid_h + d.box_h - 1) / d.box_h;
+  kp.tiles_n = (d.grid_n + d.box_n - 1) / d.box_n;
+  kp.num_m_tiles = kp.tiles_w * kp.tiles_h * kp.tiles_n;
+  kp.num_n_tiles = d.bn > 0 ? (d.n_out + d.bn - 1) / d.bn : 0;
+  kp.nblk_per_oview = d.nblk_per_oview > 0 ? d.nblk_per_oview : (kp.num_n_tiles > 0 ? kp.num_n_tiles : 1);
+  kp.n_out = d.n_out;
+  kp.bias_mod = d.bias_mod;
+  kp.stat_mod = d.stat_mod;
+  kp.relu = d.relu;
+  kp.out_mode = d.out_mode;
+  kp.out_ld = d.out_ld;
+  kp.k_out = d.k_out;
+  kp.c_total = d.c_total;
+  kp.w_ld = d.w_ld;
+  kp.splits = d.splits;
+  return plan;
+}
+
+extern "C" void dmpi_conv_plan_destroy(dmpi_conv_plan* plan) { delete plan; }
+
+extern "C" int dmpi_conv_last_error(char* buf, int buflen) {
+  snprintf(buf, buflen, "%s", g_err);
+  return static_cast<int>(strlen(g_err));
+}
+
+extern "C" int dmpi_igemm_run(dmpi_conv_plan* plan, const void* a, const void* b, void* out, const float* bias,
+                              float* stat_sum, float* stat_sqsum, void* stream) {
+  const dmpi_conv_desc& d = plan->desc;
+  ConvKernelParams& kp = plan->params;
+  if (kp.rows < 1 || kp.rows > kTileM) {
+    set_err("igemm: pixel box must hold 1..128 rows");
+    return -1;
+  }
+  if (d.bn != 64 && d.bn != 128 && d.bn != 256) {
+    set_err("igemm: bn must be 64, 128 or 256");
+    return -2;
+  }
+  if (d.out_mode == 1 && !(d.box_h == 1 && d.box_n == 1 && d.grid_h == 1 && d.grid_n == 1)) {
+    set_err("igemm: fp32 direct output needs the flat (GEMM) pixel layout");
+    return -3;
+  }
+  if (!plan->maps_valid || plan->cached_a != a || plan->cached_b != b || plan->cached_o != out) {
+    for (int i = 0; i < d.a_nviews; ++i)
+      if (encode_view(&kp.a_map[i], a, d.a_view[i], kBlockK, d.box_w, d.box_h, d.box_n)) {
+        set_err("igemm: A tensor map encode failed");
+        return -4;
+      }
+    for (int i = d.a_nviews; i < DMPI_MAX_MAPS; ++i) kp.a_map[i] = kp.a_map[0];
+    {
+      int64_t dims[2] = {d.b_k, d.b_rows};
+      int64_t strides[1] = {d.b_k};
+      int box[2] = {kBlockK, d.bn};
+      if (encode_bf16_map(&kp.b_map, b, 2, dims, strides, box)) {
+        set_err("igemm: B tensor map encode failed");
+        return -5;
+      }
+    }
+    if (d.out_mode == 0) {
+      for (int i = 0; i < d.o_nviews; ++i)
+        if (encode_view(&kp.o_map[i], out, d.o_view[i], 64, d.box_w, d.box_h, d.box_n)) {
+          set_err("igemm: output tensor map encode failed");
+          return -6;
+        }
+      for (int i = d.o_nviews; i < DMPI_MAX_MAPS; ++i) kp.o_map[i] = kp.o_map[0];
+    } else {
+      for (int i = 0; i < DMPI_MAX_MAPS; ++i) kp.o_map[i] = kp.a_map[0];
+    }
+    plan->cached_a = a;
+    plan->cached_b = b;
+    plan->cached_o = out;
+    plan->maps_valid = true;
+  }
+  kp.bias = bias;
+  kp.stat_sum = stat_sum;
+  kp.stat_sq = stat_sqsum;
+  kp.out_f32 = d.out_mode == 1 ? static_cast<float*>(out) : nullptr;
+  if (d.bias_mod > 0 && !bias) {
+    set_err("igemm: bias_mod set but bias pointer is null");
+    return -7;
+  }
+  if (d.stat_mod > 0 && (!stat_sum || !stat_sqsum)) {
+    set_err("igemm: stat_mod set but statistics pointers are null");
+    return -8;
+  }
+  if (plan->num_sms == 0) plan->num_sms = device_sm_count();
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  switch (d.bn) {
+    case 64: return launch_igemm<64>(kp, plan->num_sms, s);
+    case 128: return launch_igemm<128>(kp, plan->num_sms, s);
+    default: return launch_igemm<256>(kp, plan->num_sms, s);
+  }
+}

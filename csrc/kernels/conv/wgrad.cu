@@ -1,0 +1,233 @@
+// Weight-gradient kernel for sm_100a:  dW[k, tap, c] += sum over pixels  dY[pixel, k] * X[pixel + tap, c].
+//
+// The reduction runs over pixels, which is the *strided* axis of both NHWC operands, so both UMMA
+// operands are MN-major: a TMA box of 64 pixels x 64 channels lands in shared memory as 64 rows of
+// 128 bytes (128B swizzle) and is consumed directly as a [K=64 pixels] x [MN=64 channels] atom.
+//   M side: dY channels (k), 2 atoms = 128 rows.     N side: X channels (c), BN/64 atoms.
+// Each CTA owns one (k tile, c tile, tap) output tile and one slice of the pixel range (split-K);
+// partial results are added into the fp32 gradient with red.global.add.v4.f32, i.e. straight into
+// the parameter's slot of the gradient bucket that the all-reduce kernel later reads.
+//
+// Replaces cuDNN wgrad / cuBLAS dW GEMMs.
+#include <stdio.h>
+
+#include "../../common/ptx.cuh"
+#include "../../common/tensormap.h"
+#include "conv_common.cuh"
+
+namespace dmpi {
+
+constexpr int kWThreads = 256;
+constexpr int kPix = 64;                    // pixels per pipeline stage (GEMM K)
+constexpr int kAtomBytes = kPix * 128;      // 64 pixels x 64 bf16
+constexpr int kWABytes = 2 * kAtomBytes;    // M = 128
+
+template <int BN>
+struct WgradCfg {
+  static constexpr int kBBytes = (BN / 64) * kAtomBytes;
+  static constexpr int kStages = BN == 256 ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr int kSmemBytes = kStages * (kWABytes + kBBytes) + 1024 + 256;
+  static constexpr int kTmemCols = BN;
+};
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+template <int BN>
+__global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_constant__ ConvKernelParams p) {
+  using Cfg = WgradCfg<BN>;
+  constexpr int S = Cfg::kStages;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem_a + S * kWABytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_b + S * Cfg::kBBytes);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + S;
+  uint64_t* tfull = bars + 2 * S;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * S + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  // tile decode: blockIdx.x = ((tap * num_k_tiles + k_blk) * num_c_tiles + c_blk), blockIdx.y = split
+  const int c_blk = blockIdx.x % p.num_c_tiles;
+  const int k_blk = (blockIdx.x / p.num_c_tiles) % p.num_k_tiles;
+  const int tap = blockIdx.x / (p.num_c_tiles * p.num_k_tiles);
+  const int split = blockIdx.y;
+  const int pt_total = p.num_m_tiles;
+  const int pt_begin = static_cast<int>((static_cast<long long>(pt_total) * split) / p.splits);
+  const int pt_end = static_cast<int>((static_cast<long long>(pt_total) * (split + 1)) / p.splits);
+  const int num_it = pt_end - pt_begin;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.a_map[p.tap_view[tap]]);
+    tma_prefetch_desc(&p.b_map);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < S; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    mbar_init(tfull, 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (num_it > 0) {
+    if (warp == 0) {
+      if (lane == 0) {
+        const CUtensorMap* xmap = &p.a_map[p.tap_view[tap]];
+        const int dw = p.tap_dw[tap], dh = p.tap_dh[tap];
+        constexpr uint32_t tx_bytes = kWABytes + Cfg::kBBytes;
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int it = 0; it < num_it; ++it) {
+          const int m_blk = pt_begin + it;
+          const int tw = m_blk % p.tiles_w;
+          const int th = (m_blk / p.tiles_w) % p.tiles_h;
+          const int tn = m_blk / (p.tiles_w * p.tiles_h);
+          const int w0 = tw * p.box_w, h0 = th * p.box_h, n0 = tn * p.box_n;
+          mbar_wait(&empty[stage], phase ^ 1u);
+          mbar_arrive_expect_tx(&full[stage], tx_bytes);
+          uint8_t* sa = smem_a + stage * kWABytes;
+          uint8_t* sb = smem_b + stage * Cfg::kBBytes;
+#pragma unroll
+          for (int j = 0; j < 2; ++j)
+            tma_load_4d(sa + j * kAtomBytes, &p.b_map, &full[stage], k_blk * 128 + j * 64, w0, h0, n0);
+#pragma unroll
+          for (int j = 0; j < BN / 64; ++j)
+            tma_load_4d(sb + j * kAtomBytes, xmap, &full[stage], c_blk * BN + j * 64, w0 + dw, h0 + dh, n0);
+          if (++stage == S) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+      }
+      __syncwarp();
+    } else if (warp == 1) {
+      if (lane == 0) {
+        constexpr uint32_t idesc = umma_idesc_bf16(128, BN, 1, 1);
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int it = 0; it < num_it; ++it) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after_sync();
+          const uint32_t a_addr = smem_u32(smem_a + stage * kWABytes);
+          const uint32_t b_addr = smem_u32(smem_b + stage * Cfg::kBBytes);
+#pragma unroll
+          for (int k = 0; k < kPix / 16; ++k) {
+            // MN-major, 128B swizzle: LBO = stride between 64-channel atoms, SBO = stride between
+            // 8-pixel groups; one MMA consumes 16 pixels = 2048 bytes of every atom.
+            const uint64_t adesc = umma_smem_desc(a_addr + k * 2048, kAtomBytes, 1024);
+            const uint64_t bdesc = umma_smem_desc(b_addr + k * 2048, kAtomBytes, 1024);
+            umma_bf16(tmem_base, adesc, bdesc, idesc, (it | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty[stage]);
+          if (++stage == S) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+        umma_commit(tfull);
+      }
+      __syncwarp();
+    } else if (warp >= 4) {
+      const int q = warp - 4;
+      const int krow = k_blk * 128 + q * 32 + lane;
+      mbar_wait(tfull, 0);
+      tc_fence_after_sync();
+      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+      float* dst_row = p.dw + static_cast<long long>(krow) * p.w_ld + p.tap_woff[tap] + c_blk * BN;
+#pragma unroll 1
+      for (int chunk = 0; chunk < BN / 32; ++chunk) {
+        uint32_t v[32];
+        tmem_ld_32x32(t_addr + chunk * 32, v);
+        tmem_ld_wait();
+        if (krow < p.k_out) {
+          const int c0 = c_blk * BN + chunk * 32;
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            if (c0 + j < p.c_total)
+              red_add_v4(dst_row + chunk * 32 + j, __uint_as_float(v[j]), __uint_as_float(v[j + 1]),
+                         __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+}
+
+static thread_local char g_werr[256] = {0};
+
+template <int BN>
+static int launch_wgrad(const ConvKernelParams& kp, cudaStream_t stream) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e =
+        cudaFuncSetAttribute(wgrad_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, WgradCfg<BN>::kSmemBytes);
+    if (e != cudaSuccess) return -10;
+    attr_set = true;
+  }
+  dim3 grid(kp.ntaps * kp.num_k_tiles * kp.num_c_tiles, kp.splits, 1);
+  wgrad_kernel<BN><<<grid, kWThreads, WgradCfg<BN>::kSmemBytes, stream>>>(kp);
+  return cudaGetLastError() == cudaSuccess ? 0 : -11;
+}
+
+}  // namespace dmpi
+
+using namespace dmpi;
+
+// M-side operand (dY) is described by desc.o_view[0]; the tapped N-side operand (X) by desc.a_view[] / taps.
+extern "C" int dmpi_wgrad_run(dmpi_conv_plan* plan, const void* dy, const void* x, float* dw, void* stream) {
+  const dmpi_conv_desc& d = plan->desc;
+  ConvKernelParams& kp = plan->params;
+  if (kp.rows != kPix) return -1;
+  if (d.bn != 64 && d.bn != 128 && d.bn != 256) return -2;
+  if (!plan->maps_valid || plan->cached_a != x || plan->cached_b != dy) {
+    int box[4] = {64, d.box_w, d.box_h, d.box_n};
+    for (int i = 0; i < d.a_nviews; ++i) {
+      const uint8_t* ptr = static_cast<const uint8_t*>(x) + d.a_view[i].offset * 2;
+      if (encode_bf16_map(&kp.a_map[i], ptr, 4, d.a_view[i].dims, d.a_view[i].strides, box)) return -4;
+    }
+    for (int i = d.a_nviews; i < DMPI_MAX_MAPS; ++i) kp.a_map[i] = kp.a_map[0];
+    const uint8_t* yptr = static_cast<const uint8_t*>(dy) + d.o_view[0].offset * 2;
+    if (encode_bf16_map(&kp.b_map, yptr, 4, d.o_view[0].dims, d.o_view[0].strides, box)) return -5;
+    plan->cached_a = x;
+    plan->cached_b = dy;
+    plan->maps_valid = true;
+  }
+  kp.dw = dw;
+  kp.num_k_tiles = (d.k_out + 127) / 128;
+  kp.num_c_tiles = (d.c_total + d.bn - 1) / d.bn;
+  if (plan->num_sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&plan->num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (plan->num_sms <= 0) plan->num_sms = 148;
+  }
+  int splits = d.splits;
+  if (splits <= 0) {
+    const int tiles = kp.ntaps * kp.num_k_tiles * kp.num_c_tiles;
+    splits = (2 * plan->num_sms + tiles - 1) / tiles;
+    const int max_splits = kp.num_m_tiles / 4 > 0 ? kp.num_m_tiles / 4 : 1;
+    if (splits > max_splits) splits = max_splits;
+    if (splits < 1) splits = 1;
+  }
+  if (splits > kp.num_m_tiles) splits = kp.num_m_tiles > 0 ? kp.num_m_tiles : 1;
+  kp.splits = splits;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  switch (d.bn) {
+    case 64: return launch_wgrad<64>(kp, s);
+    case 128: return launch_wgrad<128>(kp, s);
+    default: return launch_wgrad<256>(kp, s);
+  }
+}

@@ -1,0 +1,368 @@
+// Fused BatchNorm2d (+ residual add) (+ ReLU), training and eval, forward and backward, NHWC bf16.
+//
+// The per-channel batch statistics (sum, sum of squares) are produced by the convolution epilogue
+// (igemm.cu), so the forward is ONE pass: normalise + affine (+ residual) (+ ReLU), plus the
+// running-stat update done by block 0.  The backward is two passes (reduce, apply) with the ReLU
+// mask folded in.  Semantics match torch.nn.BatchNorm2d in training mode (biased variance for
+// normalisation, unbiased for running_var, momentum EMA, num_batches_tracked += 1) followed by
+// ReLU(inplace) — ref:pytorch/unet/model.py:10-11,13-14 and torchvision resnet bn/relu
+// (K5, K6, K7).
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../common/ptx.cuh"
+
+namespace dmpi {
+
+constexpr int kBnThreads = 256;
+constexpr int kMaxC = 2048;
+
+struct BnFwdArgs {
+  const __nv_bfloat16* y;    // conv output [M, C] (row stride ldy)
+  const __nv_bfloat16* res;  // optional residual [M, C] (row stride ldr)
+  __nv_bfloat16* out;        // [M, C] (row stride ldo)
+  long long M;
+  int C;
+  long long ldy, ldr, ldo;
+  const float* sum;    // [C] batch sum of y      (training)
+  const float* sqsum;  // [C] batch sum of y*y    (training)
+  const float* gamma;
+  const float* beta;
+  float* save_mean;    // [C] out (training)
+  float* save_invstd;  // [C] out (training)
+  float* running_mean;
+  float* running_var;
+  long long* num_batches_tracked;
+  float eps, momentum;
+  int training, relu;
+};
+
+__global__ void __launch_bounds__(kBnThreads) bn_fwd_kernel(const BnFwdArgs a) {
+  extern __shared__ float sm[];  // scale[C], shift[C]
+  float* scale = sm;
+  float* shift = sm + a.C;
+  const float invM = 1.f / static_cast<float>(a.M);
+  for (int c = threadIdx.x; c < a.C; c += blockDim.x) {
+    float mean, invstd;
+    if (a.training) {
+      mean = a.sum[c] * invM;
+      float var = fmaxf(a.sqsum[c] * invM - mean * mean, 0.f);
+      invstd = rsqrtf(var + a.eps);
+      if (blockIdx.x == 0) {
+        a.save_mean[c] = mean;
+        a.save_invstd[c] = invstd;
+        if (a.running_mean) {
+          const float unbiased = a.M > 1 ? var * (static_cast<float>(a.M) / static_cast<float>(a.M - 1)) : var;
+          a.running_mean[c] = (1.f - a.momentum) * a.running_mean[c] + a.momentum * mean;
+          a.running_var[c] = (1.f - a.momentum) * a.running_var[c] + a.momentum * unbiased;
+        }
+      }
+    } else {
+      mean = a.running_mean[c];
+      invstd = rsqrtf(a.running_var[c] + a.eps);
+    }
+    const float g = a.gamma ? a.gamma[c] : 1.f;
+    const float b = a.beta ? a.beta[c] : 0.f;
+    scale[c] = g * invstd;
+    shift[c] = b - mean * g * invstd;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0 && a.training && a.num_batches_tracked) *a.num_batches_tracked += 1;
+  __syncthreads();
+
+  const int vecC = a.C >> 3;  // 8 channels (16 bytes) per thread
+  const long long total = a.M * vecC;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long row = i / vecC;
+    const int c0 = static_cast<int>(i - row * vecC) << 3;
+    const uint4 v = *reinterpret_cast<const uint4*>(a.y + row * a.ldy + c0);
+    uint4 r = make_uint4(0, 0, 0, 0);
+    if (a.res) r = *reinterpret_cast<const uint4*>(a.res + row * a.ldr + c0);
+    const uint32_t vi[4] = {v.x, v.y, v.z, v.w};
+    const uint32_t ri[4] = {r.x, r.y, r.z, r.w};
+    uint32_t oi[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int c = c0 + 2 * j;
+      float lo = fmaf(bf16lo(vi[j]), scale[c], shift[c]) + bf16lo(ri[j]);
+      float hi = fmaf(bf16hi(vi[j]), scale[c + 1], shift[c + 1]) + bf16hi(ri[j]);
+      if (a.relu) {
+        lo = fmaxf(lo, 0.f);
+        hi = fmaxf(hi, 0.f);
+      }
+      oi[j] = pack_bf16x2(lo, hi);
+    }
+    *reinterpret_cast<uint4*>(a.out + row * a.ldo + c0) = make_uint4(oi[0], oi[1], oi[2], oi[3]);
+  }
+}
+
+struct BnBwdArgs {
+  const __nv_bfloat16* dout;  // grad wrt the block output (post ReLU) [M, C]
+  const __nv_bfloat16* y;     // saved conv output (pre BN)
+  const __nv_bfloat16* act;   // saved block output (post ReLU); ReLU mask = act > 0 (null: no ReLU)
+  __nv_bfloat16* dy;          // grad wrt conv output
+  __nv_bfloat16* dres;        // optional: grad wrt the residual input (= masked dout)
+  long long M;
+  int C;
+  long long ld_dout, ldy, ld_act, ld_dy, ld_dres;
+  const float* mean;
+  const float* invstd;
+  const float* gamma;
+  float* acc;     // scratch [2*C]: sum(dz), sum(dz * xhat); must be zero on entry of the reduce pass
+  float* dgamma;  // parameter gradients, accumulated (+=) by the apply pass
+  float* dbeta;
+};
+
+// Pass 1: per-channel reductions.  Thread (tx, ty): tx owns 8 consecutive channels, ty strides rows.
+__global__ void __launch_bounds__(kBnThreads) bn_bwd_reduce_kernel(const BnBwdArgs a) {
+  const int vecC = a.C >> 3;
+  const int tx = threadIdx.x % vecC;  // host guarantees vecC divides or is <= blockDim
+  const int ty = threadIdx.x / vecC;
+  const int rows_per_block = blockDim.x / vecC;
+  const int c0 = tx << 3;
+  float s1[8], s2[8], mean[8], istd[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    s1[j] = s2[j] = 0.f;
+    mean[j] = a.mean[c0 + j];
+    istd[j] = a.invstd[c0 + j];
+  }
+  if (ty < rows_per_block) {
+    for (long long row = blockIdx.x * static_cast<long long>(rows_per_block) + ty; row < a.M;
+         row += static_cast<long long>(gridDim.x) * rows_per_block) {
+      const uint4 g = *reinterpret_cast<const uint4*>(a.dout + row * a.ld_dout + c0);
+      const uint4 yv = *reinterpret_cast<const uint4*>(a.y + row * a.ldy + c0);
+      uint4 av = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);
+      if (a.act) av = *reinterpret_cast<const uint4*>(a.act + row * a.ld_act + c0);
+      const uint32_t gi[4] = {g.x, g.y, g.z, g.w}, yi[4] = {yv.x, yv.y, yv.z, yv.w}, ai[4] = {av.x, av.y, av.z, av.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float d0 = bf16lo(ai[j]) > 0.f ? bf16lo(gi[j]) : 0.f;
+        const float d1 = bf16hi(ai[j]) > 0.f ? bf16hi(gi[j]) : 0.f;
+        s1[2 * j] += d0;
+        s1[2 * j + 1] += d1;
+        s2[2 * j] = fmaf(d0, (bf16lo(yi[j]) - mean[2 * j]) * istd[2 * j], s2[2 * j]);
+        s2[2 * j + 1] = fmaf(d1, (bf16hi(yi[j]) - mean[2 * j + 1]) * istd[2 * j + 1], s2[2 * j + 1]);
+      }
+    }
+  }
+  // block reduction over ty through shared memory
+  extern __shared__ float red[];  // [rows_per_block][C][2] would be large; reduce in 8-channel slabs
+  float* r1 = red;                 // [blockDim.x * 8]
+  float* r2 = red + blockDim.x * 8;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    r1[threadIdx.x * 8 + j] = s1[j];
+    r2[threadIdx.x * 8 + j] = s2[j];
+  }
+  __syncthreads();
+  // thread t < C handles channel t (loop if C > blockDim)
+  for (int c = threadIdx.x; c < a.C; c += blockDim.x) {
+    const int ctx = c >> 3, cj = c & 7;
+    float t1 = 0.f, t2 = 0.f;
+    for (int r = 0; r < rows_per_block; ++r) {
+      t1 += r1[(r * vecC + ctx) * 8 + cj];
+      t2 += r2[(r * vecC + ctx) * 8 + cj];
+    }
+    atomicAdd(a.acc + c, t1);
+    atomicAdd(a.acc + a.C + c, t2);
+  }
+}
+
+// Pass 2: dy = gamma * invstd * (dz - mean(dz) - xhat * mean(dz * xhat)); block 0 also emits dgamma/dbeta.
+__global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_kernel(const BnBwdArgs a) {
+  extern __shared__ float sm[];  // k1[C] = gamma*invstd, k2[C] = mean(dz), k3[C] = mean(dz*xhat), mean[C], istd[C]
+  float* k1 = sm;
+  float* k2 = sm + a.C;
+  float* k3 = sm + 2 * a.C;
+  float* mu = sm + 3 * a.C;
+  float* is = sm + 4 * a.C;
+  const float invM = 1.f / static_cast<float>(a.M);
+  for (int c = threadIdx.x; c < a.C; c += blockDim.x) {
+    const float sdz = a.acc[c], sdzx = a.acc[a.C + c];
+    const float g = a.gamma ? a.gamma[c] : 1.f;
+    k1[c] = g * a.invstd[c];
+    k2[c] = sdz * invM;
+    k3[c] = sdzx * invM;
+    mu[c] = a.mean[c];
+    is[c] = a.invstd[c];
+    if (blockIdx.x == 0) {
+      if (a.dgamma) a.dgamma[c] += sdzx;
+      if (a.dbeta) a.dbeta[c] += sdz;
+    }
+  }
+  __syncthreads();
+  const int vecC = a.C >> 3;
+  const long long total = a.M * vecC;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long row = i / vecC;
+    const int c0 = static_cast<int>(i - row * vecC) << 3;
+    const uint4 g = *reinterpret_cast<const uint4*>(a.dout + row * a.ld_dout + c0);
+    const uint4 yv = *reinterpret_cast<const uint4*>(a.y + row * a.ldy + c0);
+    uint4 av = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);
+    if (a.act) av = *reinterpret_cast<const uint4*>(a.act + row * a.ld_act + c0);
+    const uint32_t gi[4] = {g.x, g.y, g.z, g.w}, yi[4] = {yv.x, yv.y, yv.z, yv.w}, ai[4] = {av.x, av.y, av.z, av.w};
+    uint32_t oi[4], ri[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int c = c0 + 2 * j;
+      const float d0 = bf16lo(ai[j]) > 0.f ? bf16lo(gi[j]) : 0.f;
+      const float d1 = bf16hi(ai[j]) > 0.f ? bf16hi(gi[j]) : 0.f;
+      const float x0 = (bf16lo(yi[j]) - mu[c]) * is[c];
+      const float x1 = (bf16hi(yi[j]) - mu[c + 1]) * is[c + 1];
+      oi[j] = pack_bf16x2(k1[c] * (d0 - k2[c] - x0 * k3[c]), k1[c + 1] * (d1 - k2[c + 1] - x1 * k3[c + 1]));
+      ri[j] = pack_bf16x2(d0, d1);
+    }
+    *reinterpret_cast<uint4*>(a.dy + row * a.ld_dy + c0) = make_uint4(oi[0], oi[1], oi[2], oi[3]);
+    if (a.dres) *reinterpret_cast<uint4*>(a.dres + row * a.ld_dres + c0) = make_uint4(ri[0], ri[1], ri[2], ri[3]);
+  }
+}
+
+// Standalone per-channel statistics (for inputs that did not come out of the igemm epilogue).
+__global__ void __launch_bounds__(kBnThreads) bn_stats_kernel(const __nv_bfloat16* y, long long M, int C, long long ld,
+                                                              float* sum, float* sqsum) {
+  const int vecC = C >> 3;
+  const int tx = threadIdx.x % vecC, ty = threadIdx.x / vecC;
+  const int rows_per_block = blockDim.x / vecC;
+  const int c0 = tx << 3;
+  float s1[8], s2[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s1[j] = s2[j] = 0.f;
+  if (ty < rows_per_block) {
+    for (long long row = blockIdx.x * static_cast<long long>(rows_per_block) + ty; row < M;
+         row += static_cast<long long>(gridDim.x) * rows_per_block) {
+      const uint4 v = *reinterpret_cast<const uint4*>(y + row * ld + c0);
+      const uint32_t vi[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float a0 = bf16lo(vi[j]), a1 = bf16hi(vi[j]);
+        s1[2 * j] += a0;
+        s1[2 * j + 1] += a1;
+        s2[2 * j] = fmaf(a0, a0, s2[2 * j]);
+        s2[2 * j + 1] = fmaf(a1, a1, s2[2 * j + 1]);
+      }
+    }
+  }
+  extern __shared__ float red[];
+  float* r1 = red;
+  float* r2 = red + blockDim.x * 8;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    r1[threadIdx.x * 8 + j] = s1[j];
+    r2[threadIdx.x * 8 + j] = s2[j];
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const int ctx = c >> 3, cj = c & 7;
+    float t1 = 0.f, t2 = 0.f;
+    for (int r = 0; r < rows_per_block; ++r) {
+      t1 += r1[(r * vecC + ctx) * 8 + cj];
+      t2 += r2[(r * vecC + ctx) * 8 + cj];
+    }
+    atomicAdd(sum + c, t1);
+    atomicAdd(sqsum + c, t2);
+  }
+}
+
+static int grid_for(long long work_items, int threads) {
+  long long blocks = (work_items + threads - 1) / threads;
+  const long long cap = 148LL * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return static_cast<int>(blocks);
+}
+
+}  // namespace dmpi
+
+using namespace dmpi;
+
+extern "C" int dmpi_bn_forward(const void* y, const void* res, void* out, long long M, int C, long long ldy,
+                               long long ldr, long long ldo, const float* sum, const float* sqsum, const float* gamma,
+                               const float* beta, float* save_mean, float* save_invstd, float* running_mean,
+                               float* running_var, long long* num_batches_tracked, float eps, float momentum,
+                               int training, int relu, void* stream) {
+  if (C % 8 != 0 || C > kMaxC * 4) return -1;
+  BnFwdArgs a;
+  a.y = static_cast<const __nv_bfloat16*>(y);
+  a.res = static_cast<const __nv_bfloat16*>(res);
+  a.out = static_cast<__nv_bfloat16*>(out);
+  a.M = M;
+  a.C = C;
+  a.ldy = ldy;
+  a.ldr = ldr;
+  a.ldo = ldo;
+  a.sum = sum;
+  a.sqsum = sqsum;
+  a.gamma = gamma;
+  a.beta = beta;
+  a.save_mean = save_mean;
+  a.save_invstd = save_invstd;
+  a.running_mean = running_mean;
+  a.running_var = running_var;
+  a.num_batches_tracked = num_batches_tracked;
+  a.eps = eps;
+  a.momentum = momentum;
+  a.training = training;
+  a.relu = relu;
+  const int grid = grid_for(M * (C / 8), kBnThreads);
+  bn_fwd_kernel<<<grid, kBnThreads, 2 * C * sizeof(float), static_cast<cudaStream_t>(stream)>>>(a);
+  return cudaGetLastError() == cudaSuccess ? 0 : -2;
+}
+
+// Launches the reduce and apply passes.  `acc` is scratch of 2*C floats that must be zero on entry.
+extern "C" int dmpi_bn_backward(const void* dout, const void* y, const void* act, void* dy, void* dres, long long M,
+                                int C, long long ld_dout, long long ldy, long long ld_act, long long ld_dy,
+                                long long ld_dres, const float* mean, const float* invstd, const float* gamma,
+                                float* acc, float* dgamma, float* dbeta, void* stream) {
+  if (C % 8 != 0) return -1;
+  const int vecC = C / 8;
+  BnBwdArgs a;
+  a.dout = static_cast<const __nv_bfloat16*>(dout);
+  a.y = static_cast<const __nv_bfloat16*>(y);
+  a.act = static_cast<const __nv_bfloat16*>(act);
+  a.dy = static_cast<__nv_bfloat16*>(dy);
+  a.dres = static_cast<__nv_bfloat16*>(dres);
+  a.M = M;
+  a.C = C;
+  a.ld_dout = ld_dout;
+  a.ldy = ldy;
+  a.ld_act = ld_act;
+  a.ld_dy = ld_dy;
+  a.ld_dres = ld_dres;
+  a.mean = mean;
+  a.invstd = invstd;
+  a.gamma = gamma;
+  a.acc = acc;
+  a.dgamma = dgamma;
+  a.dbeta = dbeta;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  // reduce: block = vecC * rows_per_block threads (vecC <= 256 for C <= 2048)
+  int threads = kBnThreads;
+  if (vecC > threads) return -3;
+  threads = (threads / vecC) * vecC;
+  const int rows_per_block = threads / vecC;
+  long long blocks = (M + rows_per_block * 8 - 1) / (rows_per_block * 8);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks < 1) blocks = 1;
+  bn_bwd_reduce_kernel<<<static_cast<int>(blocks), threads, threads * 16 * sizeof(float), s>>>(a);
+  const int grid = grid_for(M * vecC, kBnThreads);
+  bn_bwd_apply_kernel<<<grid, kBnThreads, 5 * C * sizeof(float), s>>>(a);
+  return cudaGetLastError() == cudaSuccess ? 0 : -2;
+}
+
+extern "C" int dmpi_bn_stats(const void* y, long long M, int C, long long ld, float* sum, float* sqsum, void* stream) {
+  if (C % 8 != 0) return -1;
+  const int vecC = C / 8;
+  int threads = kBnThreads;
+  if (vecC > threads) return -3;
+  threads = (threads / vecC) * vecC;
+  const int rows_per_block = threads / vecC;
+  long long blocks = (M + rows_per_block * 8 - 1) / (rows_per_block * 8);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks < 1) blocks = 1;
+  bn_stats_kernel<<<static_cast<int>(blocks), threads, threads * 16 * sizeof(float), static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(y), M, C, ld, sum, sqsum);
+  return cudaGetLastError() == cudaSuccess ? 0 : -2;
+}

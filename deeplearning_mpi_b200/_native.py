@@ -1,0 +1,152 @@
+"""ctypes bindings to the in-tree native libraries (built by ``build.py``).
+
+``libdmpi_host.so``  — TCP key/value store and the reducer core; pure C++, loads anywhere.
+``libdmpi_cuda.so``  — every sm_100a kernel, the P2P arena and the CUDA side of the reducer.
+
+The CUDA library is mandatory on a GPU machine: if CUDA is available and the library is missing or
+fails to load we raise instead of silently falling back to eager PyTorch.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+_LIB_DIR = Path(__file__).resolve().parent / "_lib"
+
+MAX_TAPS = 32
+MAX_MAPS = 4
+
+
+class Tensor4(C.Structure):
+    _fields_ = [("dims", C.c_int64 * 4), ("strides", C.c_int64 * 3), ("offset", C.c_int64)]
+
+
+class ConvDesc(C.Structure):
+    """Mirror of ``dmpi_conv_desc`` (include/dmpi_conv.h)."""
+
+    _fields_ = [
+        ("a_nviews", C.c_int),
+        ("a_view", Tensor4 * MAX_MAPS),
+        ("box_w", C.c_int), ("box_h", C.c_int), ("box_n", C.c_int),
+        ("grid_w", C.c_int), ("grid_h", C.c_int), ("grid_n", C.c_int),
+        ("ntaps", C.c_int), ("cblocks", C.c_int),
+        ("tap_view", C.c_int * MAX_TAPS),
+        ("tap_dw", C.c_int * MAX_TAPS),
+        ("tap_dh", C.c_int * MAX_TAPS),
+        ("tap_koff", C.c_int * MAX_TAPS),
+        ("b_rows", C.c_int64), ("b_k", C.c_int64),
+        ("o_nviews", C.c_int), ("nblk_per_oview", C.c_int),
+        ("o_view", Tensor4 * MAX_MAPS),
+        ("n_out", C.c_int), ("bn", C.c_int),
+        ("bias_mod", C.c_int), ("stat_mod", C.c_int), ("relu", C.c_int), ("out_mode", C.c_int),
+        ("out_ld", C.c_int64),
+        ("k_out", C.c_int), ("c_total", C.c_int),
+        ("w_ld", C.c_int64),
+        ("tap_woff", C.c_int * MAX_TAPS),
+        ("splits", C.c_int),
+    ]
+
+
+_host = None
+_cuda = None
+_launch_count = 0
+
+
+def count_launch(n: int = 1) -> None:
+    """Launch accounting for bench.py's ``gpu_launches``: every wrapper that starts one of OUR kernels calls this."""
+    global _launch_count
+    _launch_count += n
+
+
+def launches() -> int:
+    return _launch_count
+
+
+def _load(name: str):
+    path = _LIB_DIR / name
+    if not path.exists():
+        raise FileNotFoundError(f"{path} not found — run `python build.py` (or __graft_entry__.build()) first")
+    return C.CDLL(str(path), mode=C.RTLD_GLOBAL)
+
+
+def host():
+    global _host
+    if _host is None:
+        lib = _load("libdmpi_host.so")
+        _bind_host(lib)
+        _host = lib
+    return _host
+
+
+def cuda():
+    global _cuda
+    if _cuda is None:
+        lib = _load("libdmpi_cuda.so")
+        _bind_cuda(lib)
+        _cuda = lib
+    return _cuda
+
+
+def cuda_available() -> bool:
+    try:
+        import torch
+
+        return torch.cuda.is_available()
+    except Exception:  # pragma: no cover
+        return False
+
+
+def _sig(lib, name, restype, argtypes):
+    fn = getattr(lib, name, None)
+    if fn is None:
+        return
+    fn.restype = restype
+    fn.argtypes = argtypes
+
+
+VP = C.c_void_p
+I = C.c_int
+I64 = C.c_int64
+F = C.c_float
+
+
+def _bind_host(lib) -> None:
+    _sig(lib, "dmpi_store_server_start", VP, [I, C.POINTER(I)])
+    _sig(lib, "dmpi_store_server_stop", None, [VP])
+    _sig(lib, "dmpi_store_connect", VP, [C.c_char_p, I, I])
+    _sig(lib, "dmpi_store_close", None, [VP])
+    _sig(lib, "dmpi_store_set", I, [VP, C.c_char_p, VP, I64])
+    _sig(lib, "dmpi_store_get", I64, [VP, C.c_char_p, VP, I64, I])
+    _sig(lib, "dmpi_store_add", I64, [VP, C.c_char_p, I64])
+    _sig(lib, "dmpi_store_check", I, [VP, C.c_char_p])
+    _sig(lib, "dmpi_plan_buckets", I, [C.POINTER(I64), I, I64, I64, C.POINTER(I)])
+    _sig(lib, "dmpi_reducer_create", VP, [I, C.POINTER(I), I])
+    _sig(lib, "dmpi_reducer_destroy", None, [VP])
+    _sig(lib, "dmpi_reducer_reset", None, [VP])
+    _sig(lib, "dmpi_reducer_mark_ready", I, [VP, I, C.POINTER(I), I])
+    _sig(lib, "dmpi_reducer_num_buckets", I, [VP])
+    _sig(lib, "dmpi_reducer_pending", I, [VP])
+    _sig(lib, "dmpi_reducer_ready_order", I, [VP, C.POINTER(I), I])
+    _sig(lib, "dmpi_reducer_set_launch_cb", None, [VP, VP, VP])
+    _sig(lib, "dmpi_sampler_indices", I64, [I64, I, I, I64, I, I, I, C.POINTER(I64), I64])
+
+
+def _bind_cuda(lib) -> None:
+    _sig(lib, "dmpi_conv_plan_create", VP, [C.POINTER(ConvDesc)])
+    _sig(lib, "dmpi_conv_plan_destroy", None, [VP])
+    _sig(lib, "dmpi_igemm_run", I, [VP, VP, VP, VP, VP, VP, VP, VP])
+    _sig(lib, "dmpi_wgrad_run", I, [VP, VP, VP, VP, VP])
+    _sig(lib, "dmpi_conv_last_error", I, [C.c_char_p, I])
+
+
+def conv_last_error() -> str:
+    buf = C.create_string_buffer(512)
+    cuda().dmpi_conv_last_error(buf, 512)
+    return buf.value.decode()
+
+
+def stream_ptr() -> int:
+    import torch
+
+    return torch.cuda.current_stream().cuda_stream

@@ -1,0 +1,608 @@
+"""Lowering of Conv2d / ConvTranspose2d / Linear (forward, data-gradient, weight-gradient) onto the two
+tcgen05 kernels in ``csrc/kernels/conv`` (``dmpi_igemm_run`` and ``dmpi_wgrad_run``).
+
+Conventions
+-----------
+* Activations are ``torch.bfloat16`` tensors of logical shape ``[N, H, W, C]`` with unit channel stride
+  (NHWC).  Channel *slices* of a wider buffer are fine — that is how the UNet skip "concat" is made
+  zero-copy (ref:pytorch/unet/model.py:47 does a ``torch.cat`` copy instead).
+* Conv weights reach the kernels as a K-major bf16 matrix ``[K_out, R*S*C]`` (fprop) or
+  ``[C, R*S*K_out]`` (dgrad).  fp32 gradients are accumulated in ``[K_out, R, S, C]`` order, which is
+  exactly the physical layout of a ``channels_last`` ``[K_out, C, R, S]`` parameter.
+
+This module only builds descriptors and caches plans; all math runs in the native kernels.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import functools
+from typing import Optional, Sequence, Tuple
+
+import torch
+
+from .. import _native as N
+
+__all__ = [
+    "conv2d_fprop", "conv2d_dgrad", "conv2d_wgrad", "linear_fwd", "linear_dgrad", "linear_wgrad",
+    "convt2x2_fwd", "convt2x2_dgrad", "convt2x2_wgrad", "smallc_fprop", "smallc_wgrad", "choose_box",
+]
+
+_plans: dict = {}
+
+
+def _check(rc: int, what: str) -> None:
+    if rc != 0:
+        raise RuntimeError(f"{what} failed (rc={rc}): {N.conv_last_error()}")
+
+
+@functools.lru_cache(maxsize=None)
+def choose_box(ow: int, oh: int, n: int, rows: int = 128, exact: bool = False) -> Tuple[int, int, int]:
+    """Pick the (w, h, n) pixel box of one M tile: product <= rows (== rows when ``exact``), maximising the
+    fraction of useful rows over the whole tensor."""
+    best, best_eff, best_rank = None, -1.0, (0, 0)
+    wc = sorted({min(ow, rows)} | {-(-ow // k) for k in range(1, 17)} | {1 << i for i in range(0, 8)})
+    for bw in wc:
+        if bw < 1 or bw > rows or bw > 256:
+            continue
+        hmax = rows // bw
+        hc = sorted({min(oh, hmax)} | {-(-oh // k) for k in range(1, 17)} | {1 << i for i in range(0, 8)})
+        for bh in hc:
+            if bh < 1 or bh > hmax:
+                continue
+            nmax = rows // (bw * bh)
+            for bn in sorted({min(n, nmax), nmax} | {1 << i for i in range(0, 8)}):
+                if bn < 1 or bn > nmax or bn > 256:
+                    continue
+                if exact and bw * bh * bn != rows:
+                    continue
+                tiles = -(-ow // bw) * -(-oh // bh) * -(-n // bn)
+                eff = (ow * oh * n) / (tiles * rows)
+                # ties: prefer the most compact spatial patch (halo reuse), then the widest rows
+                rank = (bw * bh, bw)
+                if eff > best_eff + 1e-9 or (abs(eff - best_eff) <= 1e-9 and rank > best_rank):
+                    best, best_eff, best_rank = (bw, bh, bn), eff, rank
+    if best is None:
+        raise ValueError(f"no pixel box for {ow}x{oh}x{n} rows={rows}")
+    return best
+
+
+def _t4(dims: Sequence[int], strides: Sequence[int], offset: int = 0) -> N.Tensor4:
+    t = N.Tensor4()
+    for i in range(4):
+        t.dims[i] = int(dims[i])
+    for i in range(3):
+        t.strides[i] = int(strides[i])
+    t.offset = int(offset)
+    return t
+
+
+def _nhwc_meta(x: torch.Tensor):
+    assert x.dim() == 4 and x.dtype == torch.bfloat16 and x.stride(3) == 1, (x.shape, x.dtype, x.stride())
+    n, h, w, c = x.shape
+    sn, sh, sw, _ = x.stride()
+    return n, h, w, c, sn, sh, sw
+
+
+def _is_flat(n, h, w, sn, sh, sw) -> bool:
+    return sh == w * sw and (n == 1 or sn == h * sh)
+
+
+def _pick_bn(n_out: int) -> int:
+    if n_out <= 64:
+        return 64
+    if n_out % 256 == 0 and n_out >= 512:
+        return 256
+    return 128
+
+
+def _views_for_stride(h, w, c, sn, sh, sw, n, stride):
+    """One strided view per input parity class (stride 2) or the plain view (stride 1)."""
+    if stride == 1:
+        return [_t4((c, w, h, n), (sw, sh, sn))], lambda a, b: 0
+    views = []
+    for a in range(2):
+        for b in range(2):
+            views.append(_t4((c, (w - b + 1) // 2, (h - a + 1) // 2, n), (2 * sw, 2 * sh, sn), a * sh + b * sw))
+    return views, lambda a, b: a * 2 + b
+
+
+def _get_plan(key, build):
+    ent = _plans.get(key)
+    if ent is None:
+        desc = build()
+        handle = N.cuda().dmpi_conv_plan_create(C.byref(desc))
+        if not handle:
+            raise RuntimeError("dmpi_conv_plan_create failed")
+        ent = (handle, desc)
+        _plans[key] = ent
+    return ent[0]
+
+
+def _run_igemm(plan, a, b, out, bias, stats):
+    s0 = stats[0].data_ptr() if stats is not None else None
+    s1 = stats[1].data_ptr() if stats is not None else None
+    rc = N.cuda().dmpi_igemm_run(plan, a.data_ptr(), b.data_ptr(), out.data_ptr(),
+                                 bias.data_ptr() if bias is not None else None, s0, s1, N.stream_ptr())
+    N.count_launch()
+    _check(rc, "dmpi_igemm_run")
+
+
+# --------------------------------------------------------------------------------------- fprop
+def conv2d_fprop(x: torch.Tensor, w2d: torch.Tensor, R: int, S: int, stride: int = 1, pad: int = 0,
+                 out: Optional[torch.Tensor] = None, bias: Optional[torch.Tensor] = None,
+                 stats: Optional[Tuple[torch.Tensor, torch.Tensor]] = None, relu: bool = False) -> torch.Tensor:
+    """y[n,oh,ow,k] = sum_{r,s,c} x[n, oh*stride+r-pad, ow*stride+s-pad, c] * w2d[k, (r*S+s)*C + c] (+bias)."""
+    n, h, w, c, sn, sh, sw = _nhwc_meta(x)
+    assert c % 64 == 0, "igemm needs C_in % 64 == 0 (use smallc_fprop for the RGB stem)"
+    kout = w2d.shape[0]
+    assert w2d.shape[1] == R * S * c and w2d.dtype == torch.bfloat16 and w2d.is_contiguous()
+    oh = (h + 2 * pad - R) // stride + 1
+    ow = (w + 2 * pad - S) // stride + 1
+    if out is None:
+        out = torch.empty((n, oh, ow, kout), dtype=torch.bfloat16, device=x.device)
+    on, ohh, oww, oc, osn, osh, osw = _nhwc_meta(out)
+    assert (on, ohh, oww, oc) == (n, oh, ow, kout)
+    flat = (R == 1 and S == 1 and stride == 1 and pad == 0 and _is_flat(n, h, w, sn, sh, sw)
+            and _is_flat(n, oh, ow, osn, osh, osw))
+    bn = _pick_bn(kout)
+    key = ("fprop", n, h, w, c, sn, sh, sw, kout, R, S, stride, pad, osn, osh, osw, bias is not None,
+           stats is not None, relu, bn)
+
+    def build():
+        d = N.ConvDesc()
+        if flat:
+            m = n * h * w
+            d.a_nviews = 1
+            d.a_view[0] = _t4((c, m, 1, 1), (sw, m * sw, m * sw))
+            d.box_w, d.box_h, d.box_n = 128, 1, 1
+            d.grid_w, d.grid_h, d.grid_n = m, 1, 1
+            d.ntaps = 1
+            d.tap_view[0] = 0
+            d.o_nviews = 1
+            d.o_view[0] = _t4((kout, m, 1, 1), (osw, m * osw, m * osw))
+        else:
+            views, vid = _views_for_stride(h, w, c, sn, sh, sw, n, stride)
+            d.a_nviews = len(views)
+            for i, v in enumerate(views):
+                d.a_view[i] = v
+            bw, bh, bnn = choose_box(ow, oh, n)
+            d.box_w, d.box_h, d.box_n = bw, bh, bnn
+            d.grid_w, d.grid_h, d.grid_n = ow, oh, n
+            d.ntaps = R * S
+            assert d.ntaps <= N.MAX_TAPS
+            t = 0
+            for r in range(R):
+                for s in range(S):
+                    if stride == 1:
+                        d.tap_view[t], d.tap_dh[t], d.tap_dw[t] = 0, r - pad, s - pad
+                    else:
+                        a, b = (r - pad) % 2, (s - pad) % 2
+                        d.tap_view[t] = vid(a, b)
+                        d.tap_dh[t], d.tap_dw[t] = (r - pad - a) // 2, (s - pad - b) // 2
+                    d.tap_koff[t] = t * c
+                    t += 1
+            d.o_nviews = 1
+            d.o_view[0] = _t4((kout, ow, oh, n), (osw, osh, osn))
+        d.cblocks = c // 64
+        d.b_rows, d.b_k = kout, R * S * c
+        d.nblk_per_oview = 0
+        d.n_out, d.bn = kout, bn
+        d.bias_mod = kout if bias is not None else 0
+        d.stat_mod = kout if stats is not None else 0
+        d.relu = int(relu)
+        d.out_mode = 0
+        return d
+
+    _run_igemm(_get_plan(key, build), x, w2d, out, bias, stats)
+    return out
+
+
+# --------------------------------------------------------------------------------------- dgrad
+def conv2d_dgrad(dy: torch.Tensor, wt2d: torch.Tensor, R: int, S: int, stride: int, pad: int,
+                 in_hw: Tuple[int, int], out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """dx[n,ih,iw,c] = sum_{r,s,k} dy[n,(ih+pad-r)/stride,(iw+pad-s)/stride,k] * wt2d[c, (r*S+s)*K + k]."""
+    n, oh, ow, k, sn, sh, sw = _nhwc_meta(dy)
+    assert k % 64 == 0
+    c = wt2d.shape[0]
+    assert wt2d.shape[1] == R * S * k and wt2d.is_contiguous()
+    ih, iw = in_hw
+    if out is None:
+        out = (torch.zeros if (stride == 2 and R == 1) else torch.empty)(
+            (n, ih, iw, c), dtype=torch.bfloat16, device=dy.device)
+    _, _, _, _, osn, osh, osw = _nhwc_meta(out)
+    bn = _pick_bn(c)
+    if stride == 1:
+        flat = R == 1 and S == 1 and pad == 0 and _is_flat(n, oh, ow, sn, sh, sw) and _is_flat(n, ih, iw, osn, osh, osw)
+        key = ("dgrad1", n, oh, ow, k, sn, sh, sw, c, R, S, pad, osn, osh, osw, bn)
+
+        def build():
+            d = N.ConvDesc()
+            d.a_nviews = 1
+            if flat:
+                m = n * oh * ow
+                d.a_view[0] = _t4((k, m, 1, 1), (sw, m * sw, m * sw))
+                d.box_w, d.box_h, d.box_n = 128, 1, 1
+                d.grid_w, d.grid_h, d.grid_n = m, 1, 1
+                d.ntaps = 1
+                d.o_view[0] = _t4((c, m, 1, 1), (osw, m * osw, m * osw))
+            else:
+                d.a_view[0] = _t4((k, ow, oh, n), (sw, sh, sn))
+                bw, bh, bnn = choose_box(iw, ih, n)
+                d.box_w, d.box_h, d.box_n = bw, bh, bnn
+                d.grid_w, d.grid_h, d.grid_n = iw, ih, n
+                d.ntaps = R * S
+                t = 0
+                for r in range(R):
+                    for s in range(S):
+                        d.tap_view[t], d.tap_dh[t], d.tap_dw[t], d.tap_koff[t] = 0, pad - r, pad - s, t * k
+                        t += 1
+                d.o_view[0] = _t4((c, iw, ih, n), (osw, osh, osn))
+            d.o_nviews = 1
+            d.cblocks = k // 64
+            d.b_rows, d.b_k = c, R * S * k
+            d.n_out, d.bn = c, bn
+            return d
+
+        _run_igemm(_get_plan(key, build), dy, wt2d, out, None, None)
+        return out
+
+    assert stride == 2
+    # Parity decomposition: input pixels with (ih%2, iw%2) == (a, b) only see taps r == (a+pad) mod 2,
+    # s == (b+pad) mod 2; on that sub-grid the gather is a dense stride-1 convolution over dy.
+    for a in range(2):
+        for b in range(2):
+            rs = [r for r in range(R) if (a + pad - r) % 2 == 0]
+            ss = [s for s in range(S) if (b + pad - s) % 2 == 0]
+            sub_h, sub_w = (ih - a + 1) // 2, (iw - b + 1) // 2
+            if sub_h <= 0 or sub_w <= 0:
+                continue
+            if not rs or not ss:
+                if not (R == 1):
+                    out[:, a::2, b::2, :].zero_()
+                continue
+            key = ("dgrad2", a, b, n, oh, ow, k, sn, sh, sw, c, R, S, pad, ih, iw, osn, osh, osw, bn)
+
+            def build(a=a, b=b, rs=rs, ss=ss, sub_h=sub_h, sub_w=sub_w):
+                d = N.ConvDesc()
+                d.a_nviews = 1
+                d.a_view[0] = _t4((k, ow, oh, n), (sw, sh, sn))
+                bw, bh, bnn = choose_box(sub_w, sub_h, n)
+                d.box_w, d.box_h, d.box_n = bw, bh, bnn
+                d.grid_w, d.grid_h, d.grid_n = sub_w, sub_h, n
+                t = 0
+                for r in rs:
+                    for s in ss:
+                        d.tap_view[t] = 0
+                        d.tap_dh[t] = (a + pad - r) // 2
+                        d.tap_dw[t] = (b + pad - s) // 2
+                        d.tap_koff[t] = (r * S + s) * k
+                        t += 1
+                d.ntaps = t
+                d.o_nviews = 1
+                d.o_view[0] = _t4((c, sub_w, sub_h, n), (2 * osw, 2 * osh, osn), a * osh + b * osw)
+                d.cblocks = k // 64
+                d.b_rows, d.b_k = c, R * S * k
+                d.n_out, d.bn = c, bn
+                return d
+
+            _run_igemm(_get_plan(key, build), dy, wt2d, out, None, None)
+    return out
+
+
+# --------------------------------------------------------------------------------------- wgrad
+def _wgrad_bn(c: int) -> int:
+    if c >= 256 and c % 256 == 0:
+        return 256
+    if c >= 128 and c % 128 == 0:
+        return 128
+    return 64
+
+
+def conv2d_wgrad(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, R: int, S: int, stride: int, pad: int) -> None:
+    """dw[k, r, s, c] += sum_{n,oh,ow} dy[n,oh,ow,k] * x[n, oh*stride+r-pad, ow*stride+s-pad, c]  (dw fp32)."""
+    n, oh, ow, k, sn, sh, sw = _nhwc_meta(dy)
+    xn, h, w, c, xsn, xsh, xsw = _nhwc_meta(x)
+    assert xn == n and c % 64 == 0 and dw.dtype == torch.float32
+    bn = _wgrad_bn(c)
+    key = ("wgrad", n, oh, ow, k, sn, sh, sw, h, w, c, xsn, xsh, xsw, R, S, stride, pad, bn)
+
+    def build():
+        d = N.ConvDesc()
+        views, vid = _views_for_stride(h, w, c, xsn, xsh, xsw, n, stride)
+        d.a_nviews = len(views)
+        for i, v in enumerate(views):
+            d.a_view[i] = v
+        bw, bh, bnn = choose_box(ow, oh, n, rows=64, exact=True)
+        d.box_w, d.box_h, d.box_n = bw, bh, bnn
+        d.grid_w, d.grid_h, d.grid_n = ow, oh, n
+        d.ntaps = R * S
+        t = 0
+        for r in range(R):
+            for s in range(S):
+                if stride == 1:
+                    d.tap_view[t], d.tap_dh[t], d.tap_dw[t] = 0, r - pad, s - pad
+                else:
+                    a, b = (r - pad) % 2, (s - pad) % 2
+                    d.tap_view[t] = vid(a, b)
+                    d.tap_dh[t], d.tap_dw[t] = (r - pad - a) // 2, (s - pad - b) // 2
+                d.tap_woff[t] = t * c
+                t += 1
+        d.o_nviews = 1
+        d.o_view[0] = _t4((k, ow, oh, n), (sw, sh, sn))
+        d.k_out, d.c_total, d.w_ld = k, c, R * S * c
+        d.bn = bn
+        d.splits = 0
+        return d
+
+    rc = N.cuda().dmpi_wgrad_run(_get_plan(key, build), dy.data_ptr(), x.data_ptr(), dw.data_ptr(), N.stream_ptr())
+    N.count_launch()
+    _check(rc, "dmpi_wgrad_run")
+
+
+# --------------------------------------------------------------------------------------- linear
+def linear_fwd(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """x [M, K] bf16, w [N_out, K] bf16 -> fp32 [M, N_out] (logits stay fp32 for the loss)."""
+    m, kk = x.shape
+    nout = w.shape[0]
+    assert kk % 64 == 0 and x.is_contiguous() and w.is_contiguous()
+    out = torch.empty((m, nout), dtype=torch.float32, device=x.device)
+    bn = 64 if nout <= 64 else 128
+    key = ("linfwd", m, kk, nout, bias is not None, bn)
+
+    def build():
+        d = N.ConvDesc()
+        d.a_nviews = 1
+        d.a_view[0] = _t4((kk, m, 1, 1), (kk, m * kk, m * kk))
+        d.box_w, d.box_h, d.box_n = 128, 1, 1
+        d.grid_w, d.grid_h, d.grid_n = m, 1, 1
+        d.ntaps, d.cblocks = 1, kk // 64
+        d.b_rows, d.b_k = nout, kk
+        d.o_nviews = 0
+        d.n_out, d.bn = nout, bn
+        d.bias_mod = nout if bias is not None else 0
+        d.out_mode, d.out_ld = 1, nout
+        return d
+
+    _run_igemm(_get_plan(key, build), x, w, out, bias, None)
+    return out
+
+
+def linear_dgrad(dy: torch.Tensor, wt: torch.Tensor) -> torch.Tensor:
+    """dy [M, N_pad] bf16 (N_pad % 64 == 0), wt [K, N_pad] bf16 -> dx [M, K] bf16."""
+    m, npad = dy.shape
+    kk = wt.shape[0]
+    assert npad % 64 == 0 and wt.shape[1] == npad
+    y4 = dy.view(1, 1, m, npad)
+    out = torch.empty((1, 1, m, kk), dtype=torch.bfloat16, device=dy.device)
+    conv2d_fprop(y4, wt, 1, 1, out=out)
+    return out.view(m, kk)
+
+
+def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor) -> None:
+    """dw[N_out, K] += dy[M, N_pad]^T x[M, K]   (rows of dy past N_out are ignored)."""
+    m, npad = dy.shape
+    kk = x.shape[1]
+    nout = dw.shape[0]
+    bn = _wgrad_bn(kk)
+    key = ("linwgrad", m, npad, kk, nout, bn)
+
+    def build():
+        d = N.ConvDesc()
+        d.a_nviews = 1
+        d.a_view[0] = _t4((kk, m, 1, 1), (kk, m * kk, m * kk))
+        d.box_w, d.box_h, d.box_n = 64, 1, 1
+        d.grid_w, d.grid_h, d.grid_n = m, 1, 1
+        d.ntaps = 1
+        d.o_nviews = 1
+        d.o_view[0] = _t4((npad, m, 1, 1), (npad, m * npad, m * npad))
+        d.k_out, d.c_total, d.w_ld = nout, kk, kk
+        d.bn = bn
+        return d
+
+    rc = N.cuda().dmpi_wgrad_run(_get_plan(key, build), dy.data_ptr(), x.data_ptr(), dw.data_ptr(), N.stream_ptr())
+    N.count_launch()
+    _check(rc, "dmpi_wgrad_run")
+
+
+# --------------------------------------------------------------------------------------- ConvTranspose2d k=2 s=2
+def convt2x2_fwd(x: torch.Tensor, wq: torch.Tensor, out: torch.Tensor, bias: Optional[torch.Tensor]) -> torch.Tensor:
+    """out[n, 2h+i, 2w+j, k] = sum_c x[n,h,w,c] * wq[(i*2+j)*K + k, c] + bias[k].
+
+    A plain GEMM [pixels, C] x [C, 4K]; the epilogue scatters each (i, j) quadrant through a strided output
+    view, so writing into the upper channel slice of the UNet concat buffer costs nothing extra
+    (ref:pytorch/unet/model.py:36-38,46-47)."""
+    n, h, w, c, sn, sh, sw = _nhwc_meta(x)
+    kq = wq.shape[0]
+    k = kq // 4
+    assert c % 64 == 0 and k % 64 == 0 and wq.shape[1] == c
+    on, oh, ow, oc, osn, osh, osw = _nhwc_meta(out)
+    assert (on, oh, ow, oc) == (n, 2 * h, 2 * w, k)
+    bn = 64 if k % 128 else 128
+    key = ("convt", n, h, w, c, sn, sh, sw, k, osn, osh, osw, bias is not None, bn)
+
+    def build():
+        d = N.ConvDesc()
+        d.a_nviews = 1
+        d.a_view[0] = _t4((c, w, h, n), (sw, sh, sn))
+        bw, bh, bnn = choose_box(w, h, n)
+        d.box_w, d.box_h, d.box_n = bw, bh, bnn
+        d.grid_w, d.grid_h, d.grid_n = w, h, n
+        d.ntaps, d.cblocks = 1, c // 64
+        d.b_rows, d.b_k = kq, c
+        d.o_nviews = 4
+        for i in range(2):
+            for j in range(2):
+                d.o_view[i * 2 + j] = _t4((k, w, h, n), (2 * osw, 2 * osh, osn), i * osh + j * osw)
+        d.nblk_per_oview = k // bn
+        d.n_out, d.bn = kq, bn
+        d.bias_mod = k if bias is not None else 0
+        return d
+
+    _run_igemm(_get_plan(key, build), x, wq, out, bias, None)
+    return out
+
+
+def convt2x2_dgrad(dout: torch.Tensor, wt: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """dx[n,h,w,c] = sum_{i,j,k} dout[n,2h+i,2w+j,k] * wt[c, (i*2+j)*K + k]."""
+    n, oh, ow, k, sn, sh, sw = _nhwc_meta(dout)
+    c = wt.shape[0]
+    h, w = oh // 2, ow // 2
+    assert k % 64 == 0 and wt.shape[1] == 4 * k
+    if out is None:
+        out = torch.empty((n, h, w, c), dtype=torch.bfloat16, device=dout.device)
+    _, _, _, _, osn, osh, osw = _nhwc_meta(out)
+    bn = _pick_bn(c)
+    key = ("convt_dgrad", n, oh, ow, k, sn, sh, sw, c, osn, osh, osw, bn)
+
+    def build():
+        d = N.ConvDesc()
+        d.a_nviews = 4
+        for i in range(2):
+            for j in range(2):
+                d.a_view[i * 2 + j] = _t4((k, w, h, n), (2 * sw, 2 * sh, sn), i * sh + j * sw)
+        bw, bh, bnn = choose_box(w, h, n)
+        d.box_w, d.box_h, d.box_n = bw, bh, bnn
+        d.grid_w, d.grid_h, d.grid_n = w, h, n
+        d.ntaps, d.cblocks = 4, k // 64
+        for t in range(4):
+            d.tap_view[t], d.tap_koff[t] = t, t * k
+        d.b_rows, d.b_k = c, 4 * k
+        d.o_nviews = 1
+        d.o_view[0] = _t4((c, w, h, n), (osw, osh, osn))
+        d.n_out, d.bn = c, bn
+        return d
+
+    _run_igemm(_get_plan(key, build), dout, wt, out, None, None)
+    return out
+
+
+def convt2x2_wgrad(dout: torch.Tensor, x: torch.Tensor, dw: torch.Tensor) -> None:
+    """dw[c, (i*2+j)*K + k] += sum_{n,h,w} x[n,h,w,c] * dout[n,2h+i,2w+j,k]   (dw fp32 [C, 4K])."""
+    n, oh, ow, k, sn, sh, sw = _nhwc_meta(dout)
+    xn, h, w, c, xsn, xsh, xsw = _nhwc_meta(x)
+    bn = _wgrad_bn(k)
+    key = ("convt_wgrad", n, oh, ow, k, sn, sh, sw, c, xsn, xsh, xsw, bn)
+
+    def build():
+        d = N.ConvDesc()
+        d.a_nviews = 4
+        for i in range(2):
+            for j in range(2):
+                d.a_view[i * 2 + j] = _t4((k, w, h, n), (2 * sw, 2 * sh, sn), i * sh + j * sw)
+        bw, bh, bnn = choose_box(w, h, n, rows=64, exact=True)
+        d.box_w, d.box_h, d.box_n = bw, bh, bnn
+        d.grid_w, d.grid_h, d.grid_n = w, h, n
+        d.ntaps = 4
+        for t in range(4):
+            d.tap_view[t], d.tap_woff[t] = t, t * k
+        d.o_nviews = 1
+        d.o_view[0] = _t4((c, w, h, n), (xsw, xsh, xsn))
+        d.k_out, d.c_total, d.w_ld = c, k, 4 * k
+        d.bn = bn
+        return d
+
+    # M side = x (rows of dw are input channels), N side = the four dout quadrants.
+    rc = N.cuda().dmpi_wgrad_run(_get_plan(key, build), x.data_ptr(), dout.data_ptr(), dw.data_ptr(), N.stream_ptr())
+    N.count_launch()
+    _check(rc, "dmpi_wgrad_run")
+
+
+# --------------------------------------------------------------------------------------- RGB stem (C_in = 3)
+def smallc_geometry(h: int, w: int, R: int, S: int, stride: int, pad: int):
+    """Padded NHWC8 staging buffer geometry for the small-channel trick (see smallc_fprop)."""
+    oh = (h + 2 * pad - R) // stride + 1
+    ow = (w + 2 * pad - S) // stride + 1
+    hp = h + 2 * pad
+    wp = max(w + 2 * pad, stride * (ow - 1) + 8)
+    return oh, ow, hp, wp
+
+
+def smallc_fprop(xp: torch.Tensor, wwin: torch.Tensor, R: int, stride: int, out_hw: Tuple[int, int],
+                 out: Optional[torch.Tensor] = None, bias: Optional[torch.Tensor] = None,
+                 stats: Optional[Tuple[torch.Tensor, torch.Tensor]] = None) -> torch.Tensor:
+    """First-layer convolution with C_in <= 8 (RGB): 7x7/s2 (ResNet) and 3x3/s1 (UNet).
+
+    ``xp`` is the zero-padded input in NHWC8 (``[N, Hp, Wp, 8]`` bf16).  Because W and C are adjacent in
+    memory, the S taps x 8 channels of one filter row are one contiguous 64-element window; a tensor map
+    with an *overlapping* W stride (stride*8 elements) presents those windows as the "channels" of a
+    [pixels, 64] operand, so each filter row is one K block and the stem runs on the same tcgen05 kernel.
+    ``wwin`` is the matching weight repack ``[K_out, R*64]`` (zeros where s >= S or c >= C_in)."""
+    n, hp, wp, c8 = xp.shape
+    assert c8 == 8 and xp.is_contiguous() and xp.dtype == torch.bfloat16
+    oh, ow = out_hw
+    kout = wwin.shape[0]
+    assert wwin.shape[1] == R * 64
+    if out is None:
+        out = torch.empty((n, oh, ow, kout), dtype=torch.bfloat16, device=xp.device)
+    _, _, _, _, osn, osh, osw = _nhwc_meta(out)
+    bn = _pick_bn(kout)
+    key = ("smallc", n, hp, wp, R, stride, oh, ow, kout, osn, osh, osw, bias is not None, stats is not None, bn)
+
+    def build():
+        d = N.ConvDesc()
+        srow, simg = wp * 8, hp * wp * 8
+        if stride == 1:
+            d.a_nviews = 1
+            d.a_view[0] = _t4((64, ow, hp, n), (8, srow, simg))
+        else:
+            d.a_nviews = 2
+            for a in range(2):
+                d.a_view[a] = _t4((64, ow, (hp - a + 1) // 2, n), (16, 2 * srow, simg), a * srow)
+        bw, bh, bnn = choose_box(ow, oh, n)
+        d.box_w, d.box_h, d.box_n = bw, bh, bnn
+        d.grid_w, d.grid_h, d.grid_n = ow, oh, n
+        d.ntaps, d.cblocks = R, 1
+        for r in range(R):
+            if stride == 1:
+                d.tap_view[r], d.tap_dh[r] = 0, r
+            else:
+                d.tap_view[r], d.tap_dh[r] = r % 2, r // 2
+            d.tap_dw[r] = 0
+            d.tap_koff[r] = r * 64
+        d.b_rows, d.b_k = kout, R * 64
+        d.o_nviews = 1
+        d.o_view[0] = _t4((kout, ow, oh, n), (osw, osh, osn))
+        d.n_out, d.bn = kout, bn
+        d.bias_mod = kout if bias is not None else 0
+        d.stat_mod = kout if stats is not None else 0
+        return d
+
+    _run_igemm(_get_plan(key, build), xp, wwin, out, bias, stats)
+    return out
+
+
+def smallc_wgrad(dy: torch.Tensor, xp: torch.Tensor, dwwin: torch.Tensor, R: int, stride: int) -> None:
+    """dwwin[k, r*64 + (s*8+c)] += sum dy[n,oh,ow,k] * window(xp)[n,oh,ow,r][s*8+c]   (fp32 [K_out, R*64])."""
+    n, oh, ow, k, sn, sh, sw = _nhwc_meta(dy)
+    _, hp, wp, _ = xp.shape
+    key = ("smallc_wgrad", n, oh, ow, k, sn, sh, sw, hp, wp, R, stride)
+
+    def build():
+        d = N.ConvDesc()
+        srow, simg = wp * 8, hp * wp * 8
+        if stride == 1:
+            d.a_nviews = 1
+            d.a_view[0] = _t4((64, ow, hp, n), (8, srow, simg))
+        else:
+            d.a_nviews = 2
+            for a in range(2):
+                d.a_view[a] = _t4((64, ow, (hp - a + 1) // 2, n), (16, 2 * srow, simg), a * srow)
+        bw, bh, bnn = choose_box(ow, oh, n, rows=64, exact=True)
+        d.box_w, d.box_h, d.box_n = bw, bh, bnn
+        d.grid_w, d.grid_h, d.grid_n = ow, oh, n
+        d.ntaps = R
+        for r in range(R):
+            if stride == 1:
+                d.tap_view[r], d.tap_dh[r] = 0, r
+            else:
+                d.tap_view[r], d.tap_dh[r] = r % 2, r // 2
+            d.tap_woff[r] = r * 64
+        d.o_nviews = 1
+        d.o_view[0] = _t4((k, ow, oh, n), (sw, sh, sn))
+        d.k_out, d.c_total, d.w_ld = k, 64, R * 64
+        d.bn = 64
+        return d
+
+    rc = N.cuda().dmpi_wgrad_run(_get_plan(key, build), dy.data_ptr(), xp.data_ptr(), dwwin.data_ptr(), N.stream_ptr())
+    N.count_launch()
+    _check(rc, "dmpi_wgrad_run")

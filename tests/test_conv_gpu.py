@@ -1,0 +1,209 @@
+"""Numerics of the tcgen05 implicit-GEMM / wgrad kernels against plain PyTorch fp32 references
+(same bf16-rounded inputs, fp32 math)."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev():
+    return torch.device("cuda:0")
+
+
+def _rand(*shape, scale=1.0):
+    return (torch.randn(*shape, device=_dev()) * scale).to(torch.bfloat16)
+
+
+def _close(got, ref, tol, what):
+    got = got.float()
+    ref = ref.float()
+    err = (got - ref).abs().max().item()
+    den = ref.abs().max().item() + 1e-6
+    print(f"[{what}] max_abs_err={err:.4e} ref_max={den:.4e} rel={err / den:.4e}")
+    assert torch.isfinite(got).all(), f"{what}: non-finite output"
+    assert err / den < tol, f"{what}: rel err {err / den:.4e} > {tol}"
+
+
+def _torch_setup():
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.manual_seed(0)
+
+
+def _w2d(w):  # [K, C, R, S] -> [K, R*S*C]
+    return w.permute(0, 2, 3, 1).contiguous().view(w.shape[0], -1)
+
+
+def _wt2d(w):  # [K, C, R, S] -> [C, R*S*K]
+    return w.permute(1, 2, 3, 0).contiguous().view(w.shape[1], -1)
+
+
+CONV_CASES = [
+    # n, h, w, c, k, R, stride, pad
+    (4, 14, 14, 256, 512, 1, 1, 0),
+    (2, 56, 56, 64, 64, 3, 1, 1),
+    (3, 28, 28, 128, 128, 3, 2, 1),
+    (2, 28, 28, 256, 512, 1, 2, 0),
+    (5, 7, 7, 512, 512, 3, 1, 1),
+    (2, 14, 14, 256, 256, 3, 2, 1),
+    (1, 32, 32, 192, 64, 3, 1, 1),
+]
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_fprop(case):
+    from deeplearning_mpi_b200.ops import conv as C
+
+    _torch_setup()
+    n, h, w, c, k, R, stride, pad = case
+    x = _rand(n, h, w, c)
+    wt = _rand(k, c, R, R, scale=(c * R * R) ** -0.5)
+    ssum = torch.zeros(k, device=_dev())
+    ssq = torch.zeros(k, device=_dev())
+    y = C.conv2d_fprop(x, _w2d(wt), R, R, stride, pad, stats=(ssum, ssq))
+    ref = F.conv2d(x.float().permute(0, 3, 1, 2), wt.float(), stride=stride, padding=pad).permute(0, 2, 3, 1)
+    _close(y, ref, 1e-2, f"fprop{case}")
+    yf = y.float()
+    _close(ssum, yf.sum(dim=(0, 1, 2)), 2e-3, f"stats_sum{case}")
+    _close(ssq, (yf * yf).sum(dim=(0, 1, 2)), 2e-3, f"stats_sq{case}")
+
+
+def test_fprop_bias_relu_slice():
+    from deeplearning_mpi_b200.ops import conv as C
+
+    _torch_setup()
+    n, h, w, c, k = 2, 16, 16, 128, 64
+    buf_in = _rand(n, h, w, c + 64)
+    x = buf_in[..., 64:]  # channel slice as input
+    wt = _rand(k, c, 3, 3, scale=(c * 9) ** -0.5)
+    bias = torch.randn(k, device=_dev())
+    buf_out = torch.zeros(n, h, w, k + 128, dtype=torch.bfloat16, device=_dev())
+    out = buf_out[..., 128:]
+    C.conv2d_fprop(x, _w2d(wt), 3, 3, 1, 1, out=out, bias=bias, relu=True)
+    ref = F.relu(F.conv2d(x.float().permute(0, 3, 1, 2), wt.float(), bias, padding=1)).permute(0, 2, 3, 1)
+    _close(out, ref, 1e-2, "fprop_bias_relu_slice")
+    assert buf_out[..., :128].abs().max().item() == 0.0
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_dgrad(case):
+    from deeplearning_mpi_b200.ops import conv as C
+
+    _torch_setup()
+    n, h, w, c, k, R, stride, pad = case
+    oh = (h + 2 * pad - R) // stride + 1
+    dy = _rand(n, oh, oh, k)
+    wt = _rand(k, c, R, R, scale=(k * R * R) ** -0.5)
+    dx = C.conv2d_dgrad(dy, _wt2d(wt), R, R, stride, pad, (h, w))
+    ref = torch.nn.grad.conv2d_input((n, c, h, w), wt.float(), dy.float().permute(0, 3, 1, 2), stride=stride,
+                                     padding=pad).permute(0, 2, 3, 1)
+    _close(dx, ref, 1e-2, f"dgrad{case}")
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_wgrad(case):
+    from deeplearning_mpi_b200.ops import conv as C
+
+    _torch_setup()
+    n, h, w, c, k, R, stride, pad = case
+    oh = (h + 2 * pad - R) // stride + 1
+    x = _rand(n, h, w, c)
+    dy = _rand(n, oh, oh, k)
+    dw = torch.zeros(k, R, R, c, device=_dev())
+    C.conv2d_wgrad(dy, x, dw, R, R, stride, pad)
+    ref = torch.nn.grad.conv2d_weight(x.float().permute(0, 3, 1, 2), (k, c, R, R), dy.float().permute(0, 3, 1, 2),
+                                      stride=stride, padding=pad).permute(0, 2, 3, 1)
+    _close(dw, ref, 1e-2, f"wgrad{case}")
+    # accumulation semantics: a second call doubles the gradient
+    C.conv2d_wgrad(dy, x, dw, R, R, stride, pad)
+    _close(dw, 2 * ref, 1e-2, f"wgrad_accum{case}")
+
+
+def test_linear():
+    from deeplearning_mpi_b200.ops import conv as C
+
+    _torch_setup()
+    m, kk, nout = 256, 2048, 1000
+    x = _rand(m, kk)
+    w = _rand(nout, kk, scale=kk ** -0.5)
+    b = torch.randn(nout, device=_dev())
+    y = C.linear_fwd(x, w, b)
+    _close(y, x.float() @ w.float().t() + b, 1e-2, "linear_fwd")
+    npad = 1024
+    dy = torch.zeros(m, npad, dtype=torch.bfloat16, device=_dev())
+    dy[:, :nout] = _rand(m, nout)
+    wt = torch.zeros(kk, npad, dtype=torch.bfloat16, device=_dev())
+    wt[:, :nout] = w.t()
+    dx = C.linear_dgrad(dy, wt)
+    _close(dx, dy[:, :nout].float() @ w.float(), 1e-2, "linear_dgrad")
+    dw = torch.zeros(nout, kk, device=_dev())
+    C.linear_wgrad(dy, x, dw)
+    _close(dw, dy[:, :nout].float().t() @ x.float(), 1e-2, "linear_wgrad")
+
+
+def test_linear_small():
+    from deeplearning_mpi_b200.ops import conv as C
+
+    _torch_setup()
+    m, kk, nout = 128, 512, 10
+    x = _rand(m, kk)
+    w = _rand(nout, kk, scale=kk ** -0.5)
+    y = C.linear_fwd(x, w, None)
+    _close(y, x.float() @ w.float().t(), 1e-2, "linear_small_fwd")
+
+
+def test_convt2x2():
+    from deeplearning_mpi_b200.ops import conv as C
+
+    _torch_setup()
+    n, h, w, c, k = 2, 16, 16, 128, 128
+    x = _rand(n, h, w, c)
+    wt = _rand(c, k, 2, 2, scale=c ** -0.5)  # torch layout [in, out, kh, kw]
+    bias = torch.randn(k, device=_dev())
+    wq = wt.permute(2, 3, 1, 0).contiguous().view(4 * k, c)        # [(i,j,k), c]
+    wtt = wt.permute(0, 2, 3, 1).contiguous().view(c, 4 * k)       # [c, (i,j,k)]
+    cat = torch.zeros(n, 2 * h, 2 * w, k + 64, dtype=torch.bfloat16, device=_dev())
+    out = cat[..., :k]
+    C.convt2x2_fwd(x, wq, out, bias)
+    ref = F.conv_transpose2d(x.float().permute(0, 3, 1, 2), wt.float(), bias, stride=2).permute(0, 2, 3, 1)
+    _close(out, ref, 1e-2, "convt_fwd")
+    assert cat[..., k:].abs().max().item() == 0.0
+    dout = _rand(n, 2 * h, 2 * w, k)
+    dx = C.convt2x2_dgrad(dout, wtt)
+    ref_dx = F.conv2d(dout.float().permute(0, 3, 1, 2), wt.float(), stride=2).permute(0, 2, 3, 1)
+    _close(dx, ref_dx, 1e-2, "convt_dgrad")
+    dw = torch.zeros(c, 4 * k, device=_dev())
+    C.convt2x2_wgrad(dout, x, dw)
+    # dw[c, i, j, k] = sum x[n,h,w,c] dout[n,2h+i,2w+j,k]
+    d6 = dout.float().view(n, h, 2, w, 2, k)
+    ref_dw = torch.einsum("nhwc,nhiwjk->cijk", x.float(), d6).reshape(c, 4 * k)
+    _close(dw, ref_dw, 1e-2, "convt_wgrad")
+
+
+@pytest.mark.parametrize("cfg", [(2, 64, 64, 7, 2, 3, 64), (2, 32, 32, 3, 1, 1, 64)])
+def test_smallc(cfg):
+    from deeplearning_mpi_b200.ops import conv as C
+
+    _torch_setup()
+    n, h, w, R, stride, pad, k = cfg
+    x = torch.randn(n, 3, h, w, device=_dev()).to(torch.bfloat16)
+    wt = _rand(k, 3, R, R, scale=(3 * R * R) ** -0.5)
+    oh, ow, hp, wp = C.smallc_geometry(h, w, R, R, stride, pad)
+    xp = torch.zeros(n, hp, wp, 8, dtype=torch.bfloat16, device=_dev())
+    xp[:, pad:pad + h, pad:pad + w, :3] = x.permute(0, 2, 3, 1)
+    wwin = torch.zeros(k, R, 8, 8, dtype=torch.bfloat16, device=_dev())
+    wwin[:, :, :R, :3] = wt.permute(0, 2, 3, 1)
+    wwin = wwin.view(k, R * 64)
+    ssum = torch.zeros(k, device=_dev())
+    ssq = torch.zeros(k, device=_dev())
+    y = C.smallc_fprop(xp, wwin, R, stride, (oh, ow), stats=(ssum, ssq))
+    ref = F.conv2d(x.float(), wt.float(), stride=stride, padding=pad).permute(0, 2, 3, 1)
+    _close(y, ref, 1e-2, f"smallc_fprop{cfg}")
+    dy = _rand(n, oh, ow, k)
+    dww = torch.zeros(k, R * 64, device=_dev())
+    C.smallc_wgrad(dy, xp, dww, R, stride)
+    ref_dw = torch.nn.grad.conv2d_weight(x.float(), (k, 3, R, R), dy.float().permute(0, 3, 1, 2), stride=stride,
+                                         padding=pad)
+    got = dww.view(k, R, 8, 8)[:, :, :R, :3].permute(0, 3, 1, 2)
+    _close(got, ref_dw, 1e-2, f"smallc_wgrad{cfg}")
