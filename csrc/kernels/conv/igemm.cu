@@ -12,7 +12,7 @@
 //   128B-swizzled shared memory, issue a TMA store into the (possibly strided / channel-sliced) output
 //   view, and accumulate per-channel sum and sum-of-squares of the stored values for BatchNorm.
 //
-// Roles: warp 0 = TMA producer, warp 1 = MMA issuer, warp 2 = TMEM allocator, warps 4..7 = epilogue.
+// Roles: warp 0 = TMA producer, warp 1 = MMA issuer, warp 2 = TMEM allocator, warps 4..11 = epilogue.
 //
 // Replaces cuDNN fprop/dgrad and cuBLAS GEMM behind ref:pytorch/unet/model.py:8-14,37-38,68 and
 // torchvision's resnet conv/fc.
@@ -28,17 +28,20 @@
 
 namespace dmpi {
 
-constexpr int kThreads = 256;
+constexpr int kThreads = 384;       // 4 control warps + 8 epilogue warps
+constexpr int kEpiThreads = 256;
 constexpr int kTileM = 128;
 constexpr int kBlockK = 64;  // bf16 elements = one 128-byte swizzle row
 constexpr int kABytes = kTileM * kBlockK * 2;
 
 template <int BN>
 struct IgemmCfg {
-  static constexpr int kStages = BN == 256 ? 3 : (BN == 128 ? 5 : 6);
+  static constexpr int kStages = BN == 256 ? 3 : (BN == 128 ? 4 : 6);
   static constexpr int kBBytes = BN * kBlockK * 2;
   static constexpr int kOutBytes = kTileM * BN * 2;
-  static constexpr int kSmemBytes = kStages * (kABytes + kBBytes) + kOutBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int kOutBufs = BN == 256 ? 1 : 2;  // staged output tiles (double buffered when they fit)
+  static constexpr int kSmemBytes =
+      kStages * (kABytes + kBBytes) + kOutBufs * kOutBytes + 1024 /*align slack*/ + 256 /*barriers*/;
   static constexpr int kTmemCols = 2 * BN;
 };
 
@@ -51,7 +54,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem_a + S * kABytes;
   uint8_t* smem_o = smem_b + S * Cfg::kBBytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_o + Cfg::kOutBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_o + Cfg::kOutBufs * Cfg::kOutBytes);
   uint64_t* full = bars;
   uint64_t* empty = bars + S;
   uint64_t* tfull = bars + 2 * S;
@@ -73,7 +76,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);
-      mbar_init(&tempty[i], 128);
+      mbar_init(&tempty[i], kEpiThreads);
     }
     fence_mbar_init();
   }
@@ -152,15 +155,26 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
     }
     __syncwarp();
   } else if (warp >= 4) {
-    // ------------------------------------------------------------------ epilogue
-    const int q = warp - 4;
+    // ------------------------------------------------------------------ epilogue (8 warps)
+    // TMEM lane quadrant q = warp % 4 (hardware rule); the two warps of a quadrant split the columns.
+    constexpr int CH = BN / 64;  // 32-column chunks per thread
+    const int q = warp & 3;
+    const int hf = (warp - 4) >> 2;
     const int row = q * 32 + lane;
-    const int et = threadIdx.x - 128;  // 0..127
+    const int et = threadIdx.x - 128;  // 0..255
     int acc = 0;
     uint32_t acc_phase = 0;
     const int wi = row % p.box_w;
     const int hi = (row / p.box_w) % p.box_h;
     const int ni = row / (p.box_w * p.box_h);
+    // BatchNorm statistics: thread -> (column, row slab); running sums live in registers across tiles.
+    constexpr int kStatSlabs = kEpiThreads / BN > 0 ? kEpiThreads / BN : 1;  // 4, 2, 1
+    constexpr int kStatRows = kTileM / kStatSlabs;
+    const int st_col = et % BN;
+    const int st_r0 = (et / BN) * kStatRows;
+    float st_sum = 0.f, st_sq = 0.f;
+    int st_nblk = -1;
+    int buf = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int n_blk = tile % p.num_n_tiles;
       const int m_blk = tile / p.num_n_tiles;
@@ -169,16 +183,22 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
       const int tn = m_blk / (p.tiles_w * p.tiles_h);
       const int w0 = tw * p.box_w, h0 = th * p.box_h, n0 = tn * p.box_n;
       const bool valid = row < p.rows && (w0 + wi) < p.grid_w && (h0 + hi) < p.grid_h && (n0 + ni) < p.grid_n;
+      uint8_t* obuf = smem_o + buf * Cfg::kOutBytes;
 
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after_sync();
       if (p.out_mode == 0) {
-        if (et == 0) tma_store_wait_read0();  // previous tile's TMA store has finished reading smem_o
-        named_bar_sync(1, 128);
+        // the TMA store that last read this buffer must have drained it
+        if (et == 0) {
+          if (Cfg::kOutBufs == 2) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          else tma_store_wait_read0();
+        }
+        named_bar_sync(1, kEpiThreads);
       }
       const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(acc * BN);
-#pragma unroll 1
-      for (int chunk = 0; chunk < BN / 32; ++chunk) {
+#pragma unroll
+      for (int ci = 0; ci < CH; ++ci) {
+        const int chunk = hf * CH + ci;
         uint32_t v[32];
         tmem_ld_32x32(t_addr + chunk * 32, v);
         tmem_ld_wait();
@@ -187,10 +207,10 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
 #pragma unroll
         for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
         if (p.bias_mod > 0) {
+          const int b0 = col0 % p.bias_mod;  // chunks never straddle a bias period (bias_mod % 32 == 0 or col < n_out)
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
-            const int c = col0 + j;
-            if (c < p.n_out) f[j] += __ldg(p.bias + (c % p.bias_mod));
+            if (col0 + j < p.n_out) f[j] += __ldg(p.bias + ((b0 + j) < p.bias_mod ? (b0 + j) : (b0 + j - p.bias_mod)));
           }
         }
         if (p.relu) {
@@ -203,7 +223,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
             for (int j = 0; j < 32; ++j) f[j] = 0.f;
           }
           // 128-byte swizzle: 16-byte chunk index XOR (row & 7) inside each 64-channel half.
-          uint8_t* half_base = smem_o + (chunk >> 1) * (kTileM * 128) + row * 128;
+          uint8_t* half_base = obuf + (chunk >> 1) * (kTileM * 128) + row * 128;
           const int c16_0 = (chunk & 1) * 4;
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
@@ -229,48 +249,47 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
 
       if (p.out_mode == 0) {
         fence_proxy_async_smem();
-        named_bar_sync(1, 128);
+        named_bar_sync(1, kEpiThreads);
         if (et == 0) {
           const CUtensorMap* omap = &p.o_map[n_blk / p.nblk_per_oview];
           const int ch0 = (n_blk % p.nblk_per_oview) * BN;
 #pragma unroll
           for (int h = 0; h < BN / 64; ++h) {
-            if (n_blk * BN + h * 64 < p.n_out) tma_store_4d(omap, smem_o + h * (kTileM * 128), ch0 + h * 64, w0, h0, n0);
+            if (n_blk * BN + h * 64 < p.n_out) tma_store_4d(omap, obuf + h * (kTileM * 128), ch0 + h * 64, w0, h0, n0);
           }
           tma_store_commit();
         }
         if (p.stat_mod > 0) {
           // Column sums of the bf16 tile just staged (exactly the values that reach memory).
-          constexpr int kColsPerPass = 128;
-#pragma unroll 1
-          for (int cbase = 0; cbase < BN; cbase += kColsPerPass) {
-            int col, r0, r1;
-            if (BN >= 128) {
-              col = cbase + et;
-              r0 = 0;
-              r1 = kTileM;
-            } else {
-              col = et & 63;
-              r0 = (et >> 6) * 64;
-              r1 = r0 + 64;
-            }
-            const int gcol = n_blk * BN + col;
-            if (gcol < p.n_out) {
-              const uint8_t* hb = smem_o + (col >> 6) * (kTileM * 128);
-              const int c16 = (col & 63) >> 3, within = (col & 7) * 2;
-              float s = 0.f, s2 = 0.f;
-#pragma unroll 8
-              for (int r = r0; r < r1; ++r) {
-                const uint16_t raw = *reinterpret_cast<const uint16_t*>(hb + r * 128 + ((c16 ^ (r & 7)) * 16) + within);
-                const float x = __uint_as_float(static_cast<uint32_t>(raw) << 16);
-                s += x;
-                s2 = fmaf(x, x, s2);
+          if (n_blk != st_nblk) {
+            if (st_nblk >= 0) {
+              const int gcol = st_nblk * BN + st_col;
+              if (gcol < p.n_out) {
+                atomicAdd(p.stat_sum + (gcol % p.stat_mod), st_sum);
+                atomicAdd(p.stat_sq + (gcol % p.stat_mod), st_sq);
               }
-              atomicAdd(p.stat_sum + (gcol % p.stat_mod), s);
-              atomicAdd(p.stat_sq + (gcol % p.stat_mod), s2);
             }
+            st_sum = st_sq = 0.f;
+            st_nblk = n_blk;
+          }
+          const uint8_t* hb = obuf + (st_col >> 6) * (kTileM * 128);
+          const int c16 = (st_col & 63) >> 3, within = (st_col & 7) * 2;
+#pragma unroll 8
+          for (int r = st_r0; r < st_r0 + kStatRows; ++r) {
+            const uint16_t raw = *reinterpret_cast<const uint16_t*>(hb + r * 128 + ((c16 ^ (r & 7)) * 16) + within);
+            const float x = __uint_as_float(static_cast<uint32_t>(raw) << 16);
+            st_sum += x;
+            st_sq = fmaf(x, x, st_sq);
           }
         }
+        buf = (buf + 1) % Cfg::kOutBufs;
+      }
+    }
+    if (p.out_mode == 0 && p.stat_mod > 0 && st_nblk >= 0) {
+      const int gcol = st_nblk * BN + st_col;
+      if (gcol < p.n_out) {
+        atomicAdd(p.stat_sum + (gcol % p.stat_mod), st_sum);
+        atomicAdd(p.stat_sq + (gcol % p.stat_mod), st_sq);
       }
     }
     if (p.out_mode == 0 && et == 0) tma_store_wait_all0();
@@ -316,7 +335,10 @@ static int launch_igemm(const ConvKernelParams& kp, int num_sms, cudaStream_t st
     attr_set = true;
   }
   const int total = kp.num_m_tiles * kp.num_n_tiles;
-  const int grid = total < num_sms ? total : num_sms;
+  int grid = total < num_sms ? total : num_sms;
+  // A grid that is a multiple of the N-tile count keeps n_blk fixed per CTA, so the BatchNorm partial sums stay
+  // in registers for the whole kernel (one atomic flush per CTA).
+  if (grid == num_sms && kp.num_n_tiles > 1 && kp.num_n_tiles <= num_sms) grid = (num_sms / kp.num_n_tiles) * kp.num_n_tiles;
   igemm_kernel<BN><<<grid, kThreads, IgemmCfg<BN>::kSmemBytes, stream>>>(kp);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {

@@ -166,8 +166,6 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
   if (warp == 2) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
 }
 
-static thread_local char g_werr[256] = {0};
-
 template <int BN>
 static int launch_wgrad(const ConvKernelParams& kp, cudaStream_t stream) {
   static bool attr_set = false;

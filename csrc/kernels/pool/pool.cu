@@ -1,0 +1,217 @@
+// Pooling kernels, NHWC bf16.
+//   * MaxPool2d(kernel k, stride s, pad p): ResNet stem 3/2/1 (torchvision resnet.py maxpool) and UNet 2/2/0
+//     (ref:pytorch/unet/model.py:25).  The forward stores the arg-max tap (uint8) so the backward routes
+//     the gradient exactly like PyTorch (first maximum in scan order), without atomics.
+//   * Global average pool [N,H,W,C] -> [N,C] and its backward (ResNet avgpool before fc).
+// All are bandwidth-bound: 16-byte vector accesses, one thread per (pixel, 8 channels).
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../common/ptx.cuh"
+
+namespace dmpi {
+
+__global__ void __launch_bounds__(256) maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x,
+                                                          __nv_bfloat16* __restrict__ y, uint8_t* __restrict__ idx,
+                                                          int N, int H, int W, int C, int OH, int OW, int k, int s,
+                                                          int p, long long xsn, long long xsh, long long xsw,
+                                                          long long ysn, long long ysh, long long ysw) {
+  const int vecC = C >> 3;
+  const long long total = static_cast<long long>(N) * OH * OW * vecC;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int cv = static_cast<int>(i % vecC);
+    long long t = i / vecC;
+    const int ow = static_cast<int>(t % OW);
+    t /= OW;
+    const int oh = static_cast<int>(t % OH);
+    const int n = static_cast<int>(t / OH);
+    float best[8];
+    int bidx[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      best[j] = -INFINITY;
+      bidx[j] = 0;
+    }
+    for (int r = 0; r < k; ++r) {
+      const int ih = oh * s + r - p;
+      if (ih < 0 || ih >= H) continue;
+      for (int q = 0; q < k; ++q) {
+        const int iw = ow * s + q - p;
+        if (iw < 0 || iw >= W) continue;
+        const uint4 v = *reinterpret_cast<const uint4*>(x + n * xsn + ih * xsh + iw * xsw + cv * 8);
+        const uint32_t vi[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float a = bf16lo(vi[j]), b = bf16hi(vi[j]);
+          if (a > best[2 * j] || a != a) {
+            best[2 * j] = a;
+            bidx[2 * j] = r * k + q;
+          }
+          if (b > best[2 * j + 1] || b != b) {
+            best[2 * j + 1] = b;
+            bidx[2 * j + 1] = r * k + q;
+          }
+        }
+      }
+    }
+    uint4 o;
+    o.x = pack_bf16x2(best[0], best[1]);
+    o.y = pack_bf16x2(best[2], best[3]);
+    o.z = pack_bf16x2(best[4], best[5]);
+    o.w = pack_bf16x2(best[6], best[7]);
+    *reinterpret_cast<uint4*>(y + n * ysn + oh * ysh + ow * ysw + cv * 8) = o;
+    if (idx) {
+      uint2 pk;
+      pk.x = bidx[0] | (bidx[1] << 8) | (bidx[2] << 16) | (bidx[3] << 24);
+      pk.y = bidx[4] | (bidx[5] << 8) | (bidx[6] << 16) | (bidx[7] << 24);
+      *reinterpret_cast<uint2*>(idx + ((static_cast<long long>(n) * OH + oh) * OW + ow) * C + cv * 8) = pk;
+    }
+  }
+}
+
+// One thread per (input pixel, 8 channels): gathers from every pooling window that covers the pixel.
+__global__ void __launch_bounds__(256) maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy,
+                                                          const uint8_t* __restrict__ idx,
+                                                          __nv_bfloat16* __restrict__ dx, int N, int H, int W, int C,
+                                                          int OH, int OW, int k, int s, int p, long long dsn,
+                                                          long long dsh, long long dsw, long long xsn, long long xsh,
+                                                          long long xsw) {
+  const int vecC = C >> 3;
+  const long long total = static_cast<long long>(N) * H * W * vecC;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int cv = static_cast<int>(i % vecC);
+    long long t = i / vecC;
+    const int iw = static_cast<int>(t % W);
+    t /= W;
+    const int ih = static_cast<int>(t % H);
+    const int n = static_cast<int>(t / H);
+    float g[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) g[j] = 0.f;
+    // windows oh with oh*s - p <= ih <= oh*s - p + k - 1
+    const int oh_lo = max(0, (ih + p - k + s) / s), oh_hi = min(OH - 1, (ih + p) / s);
+    const int ow_lo = max(0, (iw + p - k + s) / s), ow_hi = min(OW - 1, (iw + p) / s);
+    for (int oh = oh_lo; oh <= oh_hi; ++oh) {
+      const int r = ih - (oh * s - p);
+      if (r < 0 || r >= k) continue;
+      for (int ow = ow_lo; ow <= ow_hi; ++ow) {
+        const int q = iw - (ow * s - p);
+        if (q < 0 || q >= k) continue;
+        const int tap = r * k + q;
+        const uint2 id = *reinterpret_cast<const uint2*>(idx + ((static_cast<long long>(n) * OH + oh) * OW + ow) * C + cv * 8);
+        const uint4 d = *reinterpret_cast<const uint4*>(dy + n * dsn + oh * dsh + ow * dsw + cv * 8);
+        const uint32_t di[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int tj = ((j < 4 ? id.x : id.y) >> ((j & 3) * 8)) & 0xFF;
+          if (tj == tap) g[j] += (j & 1) ? bf16hi(di[j >> 1]) : bf16lo(di[j >> 1]);
+        }
+      }
+    }
+    uint4 o;
+    o.x = pack_bf16x2(g[0], g[1]);
+    o.y = pack_bf16x2(g[2], g[3]);
+    o.z = pack_bf16x2(g[4], g[5]);
+    o.w = pack_bf16x2(g[6], g[7]);
+    *reinterpret_cast<uint4*>(dx + n * xsn + ih * xsh + iw * xsw + cv * 8) = o;
+  }
+}
+
+// [N, HW, C] -> [N, C]: block = (C/8 vector lanes) x row slabs, tree-free accumulate then smem reduce.
+__global__ void __launch_bounds__(256) avgpool_fwd_kernel(const __nv_bfloat16* __restrict__ x,
+                                                          __nv_bfloat16* __restrict__ y, int HW, int C) {
+  const int n = blockIdx.y;
+  const int c0 = (blockIdx.x * blockDim.x + threadIdx.x) * 8;
+  if (c0 >= C) return;
+  float s[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = 0.f;
+  const __nv_bfloat16* base = x + static_cast<long long>(n) * HW * C + c0;
+  for (int i = 0; i < HW; ++i) {
+    const uint4 v = *reinterpret_cast<const uint4*>(base + static_cast<long long>(i) * C);
+    const uint32_t vi[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      s[2 * j] += bf16lo(vi[j]);
+      s[2 * j + 1] += bf16hi(vi[j]);
+    }
+  }
+  const float inv = 1.f / static_cast<float>(HW);
+  uint4 o;
+  o.x = pack_bf16x2(s[0] * inv, s[1] * inv);
+  o.y = pack_bf16x2(s[2] * inv, s[3] * inv);
+  o.z = pack_bf16x2(s[4] * inv, s[5] * inv);
+  o.w = pack_bf16x2(s[6] * inv, s[7] * inv);
+  *reinterpret_cast<uint4*>(y + static_cast<long long>(n) * C + c0) = o;
+}
+
+__global__ void __launch_bounds__(256) avgpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy,
+                                                          __nv_bfloat16* __restrict__ dx, int N, int HW, int C) {
+  const int vecC = C >> 3;
+  const long long total = static_cast<long long>(N) * HW * vecC;
+  const float inv = 1.f / static_cast<float>(HW);
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int cv = static_cast<int>(i % vecC);
+    const long long n = i / (static_cast<long long>(HW) * vecC);
+    const uint4 d = *reinterpret_cast<const uint4*>(dy + n * C + cv * 8);
+    uint4 o;
+    o.x = pack_bf16x2(bf16lo(d.x) * inv, bf16hi(d.x) * inv);
+    o.y = pack_bf16x2(bf16lo(d.y) * inv, bf16hi(d.y) * inv);
+    o.z = pack_bf16x2(bf16lo(d.z) * inv, bf16hi(d.z) * inv);
+    o.w = pack_bf16x2(bf16lo(d.w) * inv, bf16hi(d.w) * inv);
+    *reinterpret_cast<uint4*>(dx + i * 8) = o;
+  }
+}
+
+static int ew_grid(long long items) {
+  long long b = (items + 255) / 256;
+  if (b > 148LL * 16) b = 148LL * 16;
+  return b < 1 ? 1 : static_cast<int>(b);
+}
+
+}  // namespace dmpi
+
+using namespace dmpi;
+
+extern "C" int dmpi_maxpool_forward(const void* x, void* y, void* idx, int N, int H, int W, int C, int OH, int OW,
+                                    int k, int s, int p, long long xsn, long long xsh, long long xsw, long long ysn,
+                                    long long ysh, long long ysw, void* stream) {
+  if (C % 8 || k * k > 255) return -1;
+  const long long items = static_cast<long long>(N) * OH * OW * (C / 8);
+  maxpool_fwd_kernel<<<ew_grid(items), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), static_cast<uint8_t*>(idx), N, H, W, C, OH,
+      OW, k, s, p, xsn, xsh, xsw, ysn, ysh, ysw);
+  return cudaGetLastError() == cudaSuccess ? 0 : -2;
+}
+
+extern "C" int dmpi_maxpool_backward(const void* dy, const void* idx, void* dx, int N, int H, int W, int C, int OH,
+                                     int OW, int k, int s, int p, long long dsn, long long dsh, long long dsw,
+                                     long long xsn, long long xsh, long long xsw, void* stream) {
+  if (C % 8) return -1;
+  const long long items = static_cast<long long>(N) * H * W * (C / 8);
+  maxpool_bwd_kernel<<<ew_grid(items), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(dy), static_cast<const uint8_t*>(idx), static_cast<__nv_bfloat16*>(dx), N, H,
+      W, C, OH, OW, k, s, p, dsn, dsh, dsw, xsn, xsh, xsw);
+  return cudaGetLastError() == cudaSuccess ? 0 : -2;
+}
+
+extern "C" int dmpi_avgpool_forward(const void* x, void* y, int N, int HW, int C, void* stream) {
+  if (C % 8) return -1;
+  const int threads = 64;
+  dim3 grid((C / 8 + threads - 1) / threads, N);
+  avgpool_fwd_kernel<<<grid, threads, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(x),
+                                                                              static_cast<__nv_bfloat16*>(y), HW, C);
+  return cudaGetLastError() == cudaSuccess ? 0 : -2;
+}
+
+extern "C" int dmpi_avgpool_backward(const void* dy, void* dx, int N, int HW, int C, void* stream) {
+  if (C % 8) return -1;
+  const long long items = static_cast<long long>(N) * HW * (C / 8);
+  avgpool_bwd_kernel<<<ew_grid(items), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), N, HW, C);
+  return cudaGetLastError() == cudaSuccess ? 0 : -2;
+}

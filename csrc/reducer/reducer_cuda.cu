@@ -1,0 +1,105 @@
+// CUDA side of the reducer: the launch callback that reducer.cpp invokes when a bucket
+// (and all earlier buckets) is complete.  Pure stream/event choreography plus one kernel launch:
+//
+//   compute stream --record(ready[b])--> comm stream waits --> all-reduce kernel for bucket b
+//   after the last bucket: record(done) on the comm stream;  finalize(): compute stream waits on done.
+//
+// The all-reduce variant is chosen per bucket size (one-shot push below the threshold measured by
+// bench/allreduce_sweep.py, two-shot above), with the 1/world_size scale fused into the kernel.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include <new>
+#include <vector>
+
+#include "../../include/dmpi_comm.h"
+
+struct ReducerCuda {
+  dmpi_comm_ptrs ptrs;
+  int world = 1;
+  std::vector<long long> off, bytes;
+  std::vector<cudaEvent_t> ready;
+  cudaEvent_t done = nullptr;
+  cudaStream_t compute = nullptr, comm = nullptr;
+  bool own_comm = false;
+  long long oneshot_max_bytes = 0, slot_bytes = 0;
+  int nblocks = 32;
+  int wire_bf16 = 0;
+  float scale = 1.f;
+  int launched = 0;
+  int last_error = 0;
+};
+
+extern "C" void* dmpi_reducer_cuda_create(const dmpi_comm_ptrs* ptrs, int n_buckets, const long long* off_bytes,
+                                          const long long* nbytes, float scale, long long oneshot_max_bytes,
+                                          long long slot_bytes, int nblocks, int wire_bf16) {
+  ReducerCuda* r = new (std::nothrow) ReducerCuda();
+  if (!r) return nullptr;
+  r->ptrs = *ptrs;
+  r->world = ptrs->world;
+  r->off.assign(off_bytes, off_bytes + n_buckets);
+  r->bytes.assign(nbytes, nbytes + n_buckets);
+  r->ready.resize(n_buckets);
+  for (auto& e : r->ready) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+  cudaEventCreateWithFlags(&r->done, cudaEventDisableTiming);
+  int lo = 0, hi = 0;
+  cudaDeviceGetStreamPriorityRange(&lo, &hi);
+  cudaStreamCreateWithPriority(&r->comm, cudaStreamNonBlocking, hi);  // highest priority: comm blocks get SMs first
+  r->own_comm = true;
+  r->scale = scale;
+  r->oneshot_max_bytes = oneshot_max_bytes;
+  r->slot_bytes = slot_bytes;
+  r->nblocks = nblocks;
+  r->wire_bf16 = wire_bf16;
+  return r;
+}
+
+extern "C" void dmpi_reducer_cuda_destroy(void* h) {
+  ReducerCuda* r = static_cast<ReducerCuda*>(h);
+  if (!r) return;
+  for (auto& e : r->ready) cudaEventDestroy(e);
+  cudaEventDestroy(r->done);
+  if (r->own_comm) cudaStreamDestroy(r->comm);
+  delete r;
+}
+
+// Called at the start of every synchronising iteration with the stream the backward will run on.
+extern "C" void dmpi_reducer_cuda_begin(void* h, void* compute_stream) {
+  ReducerCuda* r = static_cast<ReducerCuda*>(h);
+  r->compute = static_cast<cudaStream_t>(compute_stream);
+  r->launched = 0;
+}
+
+// The dmpi_launch_cb installed into the reducer core.
+extern "C" void dmpi_reducer_cuda_launch(void* h, int bucket) {
+  ReducerCuda* r = static_cast<ReducerCuda*>(h);
+  cudaEventRecord(r->ready[bucket], r->compute);
+  cudaStreamWaitEvent(r->comm, r->ready[bucket], 0);
+  int rc = 0;
+  if (r->world > 1) {
+    if (r->bytes[bucket] <= r->oneshot_max_bytes && r->bytes[bucket] <= r->slot_bytes)
+      rc = dmpi_allreduce_oneshot(&r->ptrs, r->off[bucket], r->bytes[bucket], r->wire_bf16, r->scale, r->slot_bytes,
+                                  r->nblocks, 0, r->comm);
+    else
+      rc = dmpi_allreduce_twoshot(&r->ptrs, r->off[bucket], r->bytes[bucket], DMPI_F32, r->scale, r->nblocks, 0,
+                                  r->comm);
+  }
+  if (rc != 0) r->last_error = rc;
+  r->launched++;
+  if (r->launched == static_cast<int>(r->ready.size())) cudaEventRecord(r->done, r->comm);
+}
+
+// End of backward: later work on the compute stream (clip, optimizer) waits for the last all-reduce.
+extern "C" int dmpi_reducer_cuda_finalize(void* h) {
+  ReducerCuda* r = static_cast<ReducerCuda*>(h);
+  if (r->launched != static_cast<int>(r->ready.size())) return -1;
+  cudaStreamWaitEvent(r->compute, r->done, 0);
+  const int e = r->last_error;
+  r->last_error = 0;
+  return e;
+}
+
+extern "C" void* dmpi_reducer_cuda_comm_stream(void* h) { return static_cast<ReducerCuda*>(h)->comm; }
+extern "C" int dmpi_reducer_cuda_launched(void* h) { return static_cast<ReducerCuda*>(h)->launched; }
+extern "C" void* dmpi_reducer_cuda_launch_fn(void) { return reinterpret_cast<void*>(&dmpi_reducer_cuda_launch); }

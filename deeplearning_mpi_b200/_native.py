@@ -129,7 +129,7 @@ def _bind_host(lib) -> None:
     _sig(lib, "dmpi_reducer_pending", I, [VP])
     _sig(lib, "dmpi_reducer_ready_order", I, [VP, C.POINTER(I), I])
     _sig(lib, "dmpi_reducer_set_launch_cb", None, [VP, VP, VP])
-    _sig(lib, "dmpi_sampler_indices", I64, [I64, I, I, I64, I, I, I, C.POINTER(I64), I64])
+    _sig(lib, "dmpi_plan_hash", C.c_uint64, [C.POINTER(I64), C.POINTER(I), I])
 
 
 def _bind_cuda(lib) -> None:
@@ -138,6 +138,62 @@ def _bind_cuda(lib) -> None:
     _sig(lib, "dmpi_igemm_run", I, [VP, VP, VP, VP, VP, VP, VP, VP])
     _sig(lib, "dmpi_wgrad_run", I, [VP, VP, VP, VP, VP])
     _sig(lib, "dmpi_conv_last_error", I, [C.c_char_p, I])
+    # norm
+    _sig(lib, "dmpi_bn_forward", I, [VP, VP, VP, I64, I, I64, I64, I64, VP, VP, VP, VP, VP, VP, VP, VP, VP, F, F, I, I, VP])
+    _sig(lib, "dmpi_bn_backward", I, [VP, VP, VP, VP, VP, I64, I, I64, I64, I64, I64, I64, VP, VP, VP, VP, VP, VP, VP])
+    _sig(lib, "dmpi_bn_stats", I, [VP, I64, I, I64, VP, VP, VP])
+    # pool
+    _sig(lib, "dmpi_maxpool_forward", I, [VP, VP, VP, I, I, I, I, I, I, I, I, I, I64, I64, I64, I64, I64, I64, VP])
+    _sig(lib, "dmpi_maxpool_backward", I, [VP, VP, VP, I, I, I, I, I, I, I, I, I, I64, I64, I64, I64, I64, I64, VP])
+    _sig(lib, "dmpi_avgpool_forward", I, [VP, VP, I, I, I, VP])
+    _sig(lib, "dmpi_avgpool_backward", I, [VP, VP, I, I, I, VP])
+    # loss / head
+    _sig(lib, "dmpi_softmax_xent", I, [VP, VP, VP, VP, I, I, I64, I64, I, F, VP])
+    _sig(lib, "dmpi_bce_logits", I, [VP, VP, VP, VP, I64, F, VP])
+    _sig(lib, "dmpi_head_forward", I, [VP, VP, VP, VP, I64, I, I, I64, VP])
+    _sig(lib, "dmpi_head_backward", I, [VP, VP, VP, VP, VP, VP, I64, I, I, I64, I64, VP])
+    # optim
+    _sig(lib, "dmpi_sgd_step", I, [VP, VP, VP, VP, I64, F, F, F, F, I, VP, F, VP])
+    _sig(lib, "dmpi_adam_step", I, [VP, VP, VP, VP, VP, I64, F, F, F, F, F, F, F, VP, F, VP])
+    _sig(lib, "dmpi_sumsq", I, [VP, I64, VP, VP])
+    _sig(lib, "dmpi_scale_by_clip", I, [VP, I64, VP, F, VP])
+    _sig(lib, "dmpi_cast_bf16", I, [VP, VP, I64, VP])
+    # layout
+    _sig(lib, "dmpi_nchw_to_nhwc8_padded", I, [VP, VP, I, I, I, I, I, I, I, VP])
+    _sig(lib, "dmpi_nchw_to_nhwc", I, [VP, VP, I, I, I, VP])
+    _sig(lib, "dmpi_nhwc_to_nchw", I, [VP, VP, I, I, I, I64, VP])
+    _sig(lib, "dmpi_transpose_table", I, [VP, I, I, VP])
+    _sig(lib, "dmpi_stem_pack", I, [VP, VP, I, I, I, I, VP])
+    _sig(lib, "dmpi_stem_unpack_grad", I, [VP, VP, I, I, I, I, VP])
+    # p2p arena + collectives
+    _sig(lib, "dmpi_arena_create", VP, [I, I, I64, I64, I64])
+    _sig(lib, "dmpi_arena_create_emulated", VP, [I, I64, I64, I64])
+    _sig(lib, "dmpi_arena_destroy", None, [VP])
+    _sig(lib, "dmpi_arena_ipc_handle", I, [VP, VP])
+    _sig(lib, "dmpi_arena_open_peers", I, [VP, VP])
+    _sig(lib, "dmpi_arena_ptrs", VP, [VP])
+    _sig(lib, "dmpi_arena_data", VP, [VP, I])
+    _sig(lib, "dmpi_arena_stage_slot_bytes", I64, [VP])
+    _sig(lib, "dmpi_arena_mailbox", VP, [VP, I, I])
+    _sig(lib, "dmpi_arena_seq_flag", VP, [VP, I, I])
+    _sig(lib, "dmpi_arena_ack_flag", VP, [VP, I, I])
+    _sig(lib, "dmpi_arena_mailbox_bytes", I64, [VP])
+    _sig(lib, "dmpi_arena_last_error", C.c_char_p, [])
+    _sig(lib, "dmpi_allreduce_twoshot", I, [VP, I64, I64, I, F, I, I, VP])
+    _sig(lib, "dmpi_allreduce_oneshot", I, [VP, I64, I64, I, F, I64, I, I, VP])
+    _sig(lib, "dmpi_broadcast", I, [VP, I64, I64, I, I, I, VP])
+    _sig(lib, "dmpi_send", I, [VP, VP, I64, VP, VP, C.c_uint32, VP])
+    _sig(lib, "dmpi_recv", I, [VP, VP, I64, VP, VP, C.c_uint32, VP])
+    _sig(lib, "dmpi_sendrecv_emulated", I, [VP, VP, VP, I64, VP, VP, C.c_uint32, VP])
+    # reducer (CUDA glue)
+    _sig(lib, "dmpi_reducer_cuda_create", VP, [VP, I, C.POINTER(I64), C.POINTER(I64), F, I64, I64, I, I])
+    _sig(lib, "dmpi_reducer_cuda_destroy", None, [VP])
+    _sig(lib, "dmpi_reducer_cuda_begin", None, [VP, VP])
+    _sig(lib, "dmpi_reducer_cuda_launch", None, [VP, I])
+    _sig(lib, "dmpi_reducer_cuda_finalize", I, [VP])
+    _sig(lib, "dmpi_reducer_cuda_comm_stream", VP, [VP])
+    _sig(lib, "dmpi_reducer_cuda_launched", I, [VP])
+    _sig(lib, "dmpi_reducer_cuda_launch_fn", VP, [])
 
 
 def conv_last_error() -> str:

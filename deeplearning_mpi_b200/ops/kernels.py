@@ -1,0 +1,240 @@
+"""Thin, allocation-explicit Python wrappers over the C ABI of the non-GEMM sm_100a kernels
+(BatchNorm, pooling, losses, optimizers, layout).  No math happens here."""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from .. import _native as N
+
+
+def _p(t: Optional[torch.Tensor]):
+    return t.data_ptr() if t is not None else None
+
+
+def _chk(rc: int, name: str) -> None:
+    if rc != 0:
+        raise RuntimeError(f"{name} failed with code {rc}")
+
+
+def _rows_ld(x: torch.Tensor) -> Tuple[int, int]:
+    """[..., C] tensor with uniform pixel stride -> (rows, row stride)."""
+    assert x.stride(-1) == 1
+    c = x.shape[-1]
+    rows = x.numel() // c
+    if x.dim() == 2:
+        return rows, x.stride(0)
+    assert x.dim() == 4
+    n, h, w, _ = x.shape
+    sn, sh, sw, _ = x.stride()
+    assert sh == w * sw and (n == 1 or sn == h * sh), "tensor must have a uniform pixel stride"
+    return rows, sw
+
+
+# ------------------------------------------------------------------------------------------ BatchNorm
+def bn_forward(y, res, out, ssum, ssq, gamma, beta, save_mean, save_invstd, running_mean, running_var, nbt,
+               eps: float, momentum: float, training: bool, relu: bool) -> None:
+    M, ldy = _rows_ld(y)
+    _, ldo = _rows_ld(out)
+    ldr = _rows_ld(res)[1] if res is not None else 0
+    C = y.shape[-1]
+    rc = N.cuda().dmpi_bn_forward(_p(y), _p(res), _p(out), M, C, ldy, ldr, ldo, _p(ssum), _p(ssq), _p(gamma), _p(beta),
+                                  _p(save_mean), _p(save_invstd), _p(running_mean), _p(running_var), _p(nbt),
+                                  float(eps), float(momentum), int(training), int(relu), N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_bn_forward")
+
+
+def bn_backward(dout, y, act, dy, dres, mean, invstd, gamma, acc, dgamma, dbeta) -> None:
+    M, ld_dout = _rows_ld(dout)
+    _, ldy = _rows_ld(y)
+    ld_act = _rows_ld(act)[1] if act is not None else 0
+    _, ld_dy = _rows_ld(dy)
+    ld_dres = _rows_ld(dres)[1] if dres is not None else 0
+    C = y.shape[-1]
+    rc = N.cuda().dmpi_bn_backward(_p(dout), _p(y), _p(act), _p(dy), _p(dres), M, C, ld_dout, ldy, ld_act, ld_dy,
+                                   ld_dres, _p(mean), _p(invstd), _p(gamma), _p(acc), _p(dgamma), _p(dbeta),
+                                   N.stream_ptr())
+    N.count_launch(2)
+    _chk(rc, "dmpi_bn_backward")
+
+
+def channel_stats(y, ssum, ssq) -> None:
+    M, ld = _rows_ld(y)
+    rc = N.cuda().dmpi_bn_stats(_p(y), M, y.shape[-1], ld, _p(ssum), _p(ssq), N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_bn_stats")
+
+
+# ------------------------------------------------------------------------------------------ pooling
+def maxpool_forward(x, k: int, s: int, p: int, want_idx: bool):
+    n, h, w, c = x.shape
+    oh = (h + 2 * p - k) // s + 1
+    ow = (w + 2 * p - k) // s + 1
+    y = torch.empty((n, oh, ow, c), dtype=torch.bfloat16, device=x.device)
+    idx = torch.empty((n, oh, ow, c), dtype=torch.uint8, device=x.device) if want_idx else None
+    rc = N.cuda().dmpi_maxpool_forward(_p(x), _p(y), _p(idx), n, h, w, c, oh, ow, k, s, p, x.stride(0), x.stride(1),
+                                       x.stride(2), y.stride(0), y.stride(1), y.stride(2), N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_maxpool_forward")
+    return y, idx
+
+
+def maxpool_backward(dy, idx, in_shape, k: int, s: int, p: int):
+    n, h, w, c = in_shape
+    _, oh, ow, _ = dy.shape
+    dx = torch.empty((n, h, w, c), dtype=torch.bfloat16, device=dy.device)
+    rc = N.cuda().dmpi_maxpool_backward(_p(dy), _p(idx), _p(dx), n, h, w, c, oh, ow, k, s, p, dy.stride(0),
+                                        dy.stride(1), dy.stride(2), dx.stride(0), dx.stride(1), dx.stride(2),
+                                        N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_maxpool_backward")
+    return dx
+
+
+def avgpool_forward(x):
+    n, h, w, c = x.shape
+    assert x.is_contiguous()
+    y = torch.empty((n, c), dtype=torch.bfloat16, device=x.device)
+    rc = N.cuda().dmpi_avgpool_forward(_p(x), _p(y), n, h * w, c, N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_avgpool_forward")
+    return y
+
+
+def avgpool_backward(dy, in_shape):
+    n, h, w, c = in_shape
+    dx = torch.empty((n, h, w, c), dtype=torch.bfloat16, device=dy.device)
+    rc = N.cuda().dmpi_avgpool_backward(_p(dy.contiguous()), _p(dx), n, h * w, c, N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_avgpool_backward")
+    return dx
+
+
+# ------------------------------------------------------------------------------------------ losses / head
+def softmax_xent(logits: torch.Tensor, labels: torch.Tensor, grad_scale: float = 1.0):
+    """Returns (loss scalar fp32 tensor, dlogits fp32 [M, N]) for mean-reduced cross-entropy."""
+    m, n = logits.shape
+    assert logits.dtype == torch.float32 and logits.stride(1) == 1 and labels.dtype == torch.int64
+    loss = torch.zeros((), dtype=torch.float32, device=logits.device)
+    d = torch.empty((m, n), dtype=torch.float32, device=logits.device)
+    rc = N.cuda().dmpi_softmax_xent(_p(logits), _p(labels), _p(d), _p(loss), m, n, logits.stride(0), n, n,
+                                    float(grad_scale), N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_softmax_xent")
+    return loss, d
+
+
+def bce_logits(x: torch.Tensor, t: torch.Tensor, grad_scale: float = 1.0):
+    assert x.dtype == torch.float32 and t.dtype == torch.float32 and x.is_contiguous() and t.is_contiguous()
+    loss = torch.zeros((), dtype=torch.float32, device=x.device)
+    d = torch.empty_like(x)
+    rc = N.cuda().dmpi_bce_logits(_p(x), _p(t), _p(d), _p(loss), x.numel(), float(grad_scale), N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_bce_logits")
+    return loss, d
+
+
+def head_forward(x, w, b):
+    """x NHWC bf16 [..., C]; w fp32 [K, C]; -> fp32 [rows, K]."""
+    M, ldx = _rows_ld(x)
+    K, Cc = w.shape
+    y = torch.empty((M, K), dtype=torch.float32, device=x.device)
+    rc = N.cuda().dmpi_head_forward(_p(x), _p(w), _p(b), _p(y), M, Cc, K, ldx, N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_head_forward")
+    return y
+
+
+def head_backward(dy, x, w, dw, db):
+    M, ldx = _rows_ld(x)
+    K, Cc = w.shape
+    dx = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
+    rc = N.cuda().dmpi_head_backward(_p(dy), _p(x), _p(w), _p(dx), _p(dw), _p(db), M, Cc, K, ldx, Cc, N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_head_backward")
+    return dx
+
+
+# ------------------------------------------------------------------------------------------ optimizers
+def sgd_step(p, g, mom, shadow, n, lr, momentum, dampening, wd, first_step, sumsq=None, max_norm=0.0) -> None:
+    rc = N.cuda().dmpi_sgd_step(_p(p), _p(g), _p(mom), _p(shadow), n, lr, momentum, dampening, wd, int(first_step),
+                                _p(sumsq), float(max_norm), N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_sgd_step")
+
+
+def adam_step(p, g, m, v, shadow, n, lr, b1, b2, eps, wd, bc1, bc2, sumsq=None, max_norm=0.0) -> None:
+    rc = N.cuda().dmpi_adam_step(_p(p), _p(g), _p(m), _p(v), _p(shadow), n, lr, b1, b2, eps, wd, bc1, bc2, _p(sumsq),
+                                 float(max_norm), N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_adam_step")
+
+
+def sumsq(g, n, out) -> None:
+    rc = N.cuda().dmpi_sumsq(_p(g), n, _p(out), N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_sumsq")
+
+
+def scale_by_clip(g, n, sumsq_t, max_norm) -> None:
+    rc = N.cuda().dmpi_scale_by_clip(_p(g), n, _p(sumsq_t), float(max_norm), N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_scale_by_clip")
+
+
+def cast_bf16(src, dst, n) -> None:
+    rc = N.cuda().dmpi_cast_bf16(_p(src), _p(dst), n, N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_cast_bf16")
+
+
+# ------------------------------------------------------------------------------------------ layout
+def nchw_to_nhwc8_padded(x: torch.Tensor, pad: int, hp: int, wp: int, out: Optional[torch.Tensor] = None):
+    n, c, h, w = x.shape
+    assert x.dtype == torch.float32 and x.is_contiguous() and c <= 8
+    if out is None:
+        out = torch.empty((n, hp, wp, 8), dtype=torch.bfloat16, device=x.device)
+    rc = N.cuda().dmpi_nchw_to_nhwc8_padded(_p(x), _p(out), n, c, h, w, pad, hp, wp, N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_nchw_to_nhwc8_padded")
+    return out
+
+
+def nchw_to_nhwc(x: torch.Tensor):
+    n, c, h, w = x.shape
+    assert x.dtype == torch.float32 and x.is_contiguous()
+    out = torch.empty((n, h, w, c), dtype=torch.bfloat16, device=x.device)
+    rc = N.cuda().dmpi_nchw_to_nhwc(_p(x), _p(out), n, c, h * w, N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_nchw_to_nhwc")
+    return out
+
+
+def nhwc_to_nchw(x: torch.Tensor):
+    n, h, w, c = x.shape
+    _, ld = _rows_ld(x)
+    out = torch.empty((n, c, h, w), dtype=torch.float32, device=x.device)
+    rc = N.cuda().dmpi_nhwc_to_nchw(_p(x), _p(out), n, c, h * w, ld, N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_nhwc_to_nchw")
+    return out
+
+
+def transpose_table(table_dev: torch.Tensor, n_entries: int, total_tiles: int) -> None:
+    rc = N.cuda().dmpi_transpose_table(_p(table_dev), n_entries, total_tiles, N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_transpose_table")
+
+
+def stem_pack(w_master: torch.Tensor, out: torch.Tensor, K: int, R: int, S: int, Cc: int) -> None:
+    rc = N.cuda().dmpi_stem_pack(_p(w_master), _p(out), K, R, S, Cc, N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_stem_pack")
+
+
+def stem_unpack_grad(dwin: torch.Tensor, dw: torch.Tensor, K: int, R: int, S: int, Cc: int) -> None:
+    rc = N.cuda().dmpi_stem_unpack_grad(_p(dwin), _p(dw), K, R, S, Cc, N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_stem_unpack_grad")
