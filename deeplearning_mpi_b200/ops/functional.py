@@ -1,0 +1,269 @@
+"""Autograd functions that bind the sm_100a kernels into PyTorch's autograd graph.
+
+Activations between these functions are NHWC bf16.  Weight gradients are NOT returned to autograd: the
+wgrad kernels accumulate straight into the parameter's slot of the flat gradient arena (= the DDP bucket),
+after which ``arena.grad_ready(param)`` notifies the reducer — the "wgrad epilogue writes into the bucket
+and bumps the ready counter" design of SURVEY.md K3 / N8.  Parameters are still passed as inputs so that
+autograd knows the function needs a backward pass.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.nn as nn
+
+from . import conv as CV
+from . import kernels as K
+
+
+def _nb(t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+    return t if t is None else t.detach()
+
+
+class ConvBnAct(torch.autograd.Function):
+    """y = Conv2d(x) [+bias];  out = ReLU?(BatchNorm(y) [+ residual]).
+
+    Replaces the Conv2d -> BatchNorm2d -> ReLU(inplace) chains of ref:pytorch/unet/model.py:8-14 and the
+    conv/bn/relu/+identity patterns of torchvision BasicBlock/Bottleneck.
+    """
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, gamma, beta, residual, conv: nn.Conv2d, bn: nn.BatchNorm2d, arena, relu: bool,
+                out_holder, stem_in_hw):
+        # out_holder: None or a 1-element list holding a pre-allocated NHWC view (e.g. a channel slice of a UNet
+        # concat buffer).  It is wrapped in a list so that autograd does not treat it as a differentiable input.
+        out = out_holder[0] if out_holder else None
+        R, S = conv.kernel_size
+        stride, pad = conv.stride[0], conv.padding[0]
+        training = bn.training
+        stats = arena.bn_stats(bn) if training else None
+        is_stem = stem_in_hw is not None
+        if is_stem:
+            oh, ow, _, _ = CV.smallc_geometry(stem_in_hw[0], stem_in_hw[1], R, S, stride, pad)
+            y = CV.smallc_fprop(x, arena.stem_w[id(weight)], R, stride, (oh, ow), bias=_nb(bias), stats=stats)
+        else:
+            y = CV.conv2d_fprop(x, arena.w_natural(weight), R, S, stride, pad, bias=_nb(bias), stats=stats)
+        if out is None:
+            out = torch.empty_like(y)
+        c = y.shape[-1]
+        mean = torch.empty(c, dtype=torch.float32, device=y.device) if training else None
+        invstd = torch.empty(c, dtype=torch.float32, device=y.device) if training else None
+        track = bn.track_running_stats and bn.running_mean is not None
+        momentum = bn.momentum if bn.momentum is not None else 0.1
+        K.bn_forward(y, residual, out, stats[0] if training else None, stats[1] if training else None, _nb(gamma),
+                     _nb(beta), mean, invstd, bn.running_mean if track else None, bn.running_var if track else None,
+                     bn.num_batches_tracked if (track and training) else None, bn.eps, momentum, training, relu)
+        ctx.conv, ctx.bn, ctx.arena, ctx.relu, ctx.is_stem = conv, bn, arena, relu, is_stem
+        ctx.has_res = residual is not None
+        ctx.params = (weight, bias, gamma, beta)
+        ctx.in_hw = (x.shape[1], x.shape[2]) if not is_stem else stem_in_hw
+        ctx.save_for_backward(x, y, out, mean, invstd)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x, y, out, mean, invstd = ctx.saved_tensors
+        weight, bias, gamma, beta = ctx.params
+        conv, bn, arena = ctx.conv, ctx.bn, ctx.arena
+        R, S = conv.kernel_size
+        stride, pad = conv.stride[0], conv.padding[0]
+        if dout.stride(-1) != 1 or dout.dtype != torch.bfloat16:
+            dout = dout.to(torch.bfloat16).contiguous()
+        dy = torch.empty_like(y)
+        dres = torch.empty_like(y) if ctx.has_res else None
+        K.bn_backward(dout, y, out if ctx.relu else None, dy, dres, mean, invstd, gamma.detach(), arena.bn_acc(bn),
+                      arena.grad_physical(gamma), arena.grad_physical(beta))
+        arena.grad_ready(gamma)
+        arena.grad_ready(beta)
+        if bias is not None:
+            # d(bias) = sum(dy) is identically zero behind a training-mode BatchNorm; the slot stays as zeroed.
+            arena.grad_physical(bias)
+            arena.grad_ready(bias)
+        dx = None
+        if ctx.is_stem:
+            dwin = arena.stem_dw[id(weight)]
+            dwin.zero_()
+            CV.smallc_wgrad(dy, x, dwin, R, stride)
+            k, c = weight.shape[0], weight.shape[1]
+            K.stem_unpack_grad(dwin, arena.grad_physical(weight), k, R, S, c)
+        else:
+            CV.conv2d_wgrad(dy, x, arena.grad_physical(weight), R, S, stride, pad)
+            if ctx.needs_input_grad[0]:
+                dx = CV.conv2d_dgrad(dy, arena.w_transposed(weight), R, S, stride, pad, ctx.in_hw)
+        arena.grad_ready(weight)
+        return dx, None, None, None, None, dres, None, None, None, None, None, None
+
+
+class ConvTranspose2x2(torch.autograd.Function):
+    """ConvTranspose2d(k=2, s=2) writing into a channel slice of a pre-allocated NHWC buffer (zero-copy concat,
+    ref:pytorch/unet/model.py:36-38,46-47)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, out_holder, arena):
+        k = weight.shape[1]
+        out = out_holder[0]
+        CV.convt2x2_fwd(x, arena.w_transposed(weight), out, _nb(bias))
+        ctx.arena, ctx.params = arena, (weight, bias)
+        ctx.save_for_backward(x)
+        ctx.k = k
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        (x,) = ctx.saved_tensors
+        weight, bias = ctx.params
+        arena = ctx.arena
+        if dout.dtype != torch.bfloat16:
+            dout = dout.to(torch.bfloat16)
+        CV.convt2x2_wgrad(dout, x, arena.grad_physical(weight))
+        arena.grad_ready(weight)
+        if bias is not None:
+            k = ctx.k
+            scratch = torch.zeros(2 * k, dtype=torch.float32, device=dout.device)
+            K.channel_stats(dout, scratch[:k], scratch[k:])
+            arena.grad_physical(bias).add_(scratch[:k])
+            arena.grad_ready(bias)
+        dx = CV.convt2x2_dgrad(dout, arena.w_natural(weight)) if ctx.needs_input_grad[0] else None
+        return dx, None, None, None, None
+
+
+class ConcatView(torch.autograd.Function):
+    """Zero-copy torch.cat([up, skip], dim=channels): both producers already wrote their channel slice of ``buf``;
+    this node only ties them into the autograd graph and splits the incoming gradient into two slice views."""
+
+    @staticmethod
+    def forward(ctx, up, skip, buf_holder):
+        ctx.c_up = up.shape[-1]
+        return buf_holder[0].view(buf_holder[0].shape)
+
+    @staticmethod
+    def backward(ctx, g):
+        return g[..., : ctx.c_up], g[..., ctx.c_up:], None
+
+
+class MaxPool(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, k, s, p):
+        y, idx = K.maxpool_forward(x, k, s, p, want_idx=ctx.needs_input_grad[0])
+        ctx.cfg = (tuple(x.shape), k, s, p)
+        ctx.save_for_backward(idx)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (idx,) = ctx.saved_tensors
+        shape, k, s, p = ctx.cfg
+        if dy.stride(-1) != 1:
+            dy = dy.contiguous()
+        return K.maxpool_backward(dy, idx, shape, k, s, p), None, None, None
+
+
+class GlobalAvgPool(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        ctx.shape = tuple(x.shape)
+        return K.avgpool_forward(x.contiguous())
+
+    @staticmethod
+    def backward(ctx, dy):
+        return K.avgpool_backward(dy, ctx.shape)
+
+
+class LinearFn(torch.autograd.Function):
+    """bf16 [M, K] x fp32-master Linear -> fp32 logits [M, N] (nn.Linear of ref:pytorch/resnet/main.py:41)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, arena):
+        y = CV.linear_fwd(x.contiguous(), arena.w_natural(weight), _nb(bias))
+        ctx.arena, ctx.params = arena, (weight, bias)
+        ctx.save_for_backward(x)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x,) = ctx.saved_tensors
+        weight, bias = ctx.params
+        arena = ctx.arena
+        n_out, kk = weight.shape
+        wt = arena.w_transposed(weight)  # [K, N_pad]
+        npad = wt.shape[1]
+        dyp = torch.zeros((dy.shape[0], npad), dtype=torch.bfloat16, device=dy.device)
+        dyp[:, :n_out].copy_(dy)
+        CV.linear_wgrad(dyp, x.contiguous(), arena.grad_physical(weight))
+        arena.grad_ready(weight)
+        if bias is not None:
+            arena.grad_physical(bias).add_(dy.sum(0))
+            arena.grad_ready(bias)
+        dx = CV.linear_dgrad(dyp, wt) if ctx.needs_input_grad[0] else None
+        return dx, None, None, None
+
+
+class Head1x1(torch.autograd.Function):
+    """Conv2d(C, out_classes<=8, 1) on NHWC bf16 -> fp32 NCHW logits (ref:pytorch/unet/model.py:68)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, arena):
+        n, h, w, c = x.shape
+        kc = weight.shape[0]
+        y = K.head_forward(x, weight.detach().reshape(kc, c), _nb(bias))  # [n*h*w, kc]
+        ctx.arena, ctx.params = arena, (weight, bias)
+        ctx.save_for_backward(x)
+        if kc == 1:
+            return y.view(n, 1, h, w)
+        return y.view(n, h, w, kc).permute(0, 3, 1, 2)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x,) = ctx.saved_tensors
+        weight, bias = ctx.params
+        arena = ctx.arena
+        n, h, w, c = x.shape
+        kc = weight.shape[0]
+        d2 = dy.permute(0, 2, 3, 1).reshape(n * h * w, kc).contiguous().float()
+        dx = K.head_backward(d2, x, weight.detach().reshape(kc, c), arena.grad_physical(weight).view(kc, c),
+                             arena.grad_physical(bias) if bias is not None else None)
+        arena.grad_ready(weight)
+        if bias is not None:
+            arena.grad_ready(bias)
+        return dx, None, None, None
+
+
+class StageInput(torch.autograd.Function):
+    """NCHW fp32 batch -> zero-padded NHWC8 bf16 staging buffer for the RGB stem (no gradient)."""
+
+    @staticmethod
+    def forward(ctx, x, pad, hp, wp):
+        return K.nchw_to_nhwc8_padded(x.contiguous().float(), pad, hp, wp)
+
+    @staticmethod
+    def backward(ctx, g):
+        return None, None, None, None
+
+
+class SoftmaxCrossEntropy(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, labels):
+        loss, d = K.softmax_xent(logits.contiguous(), labels)
+        ctx.save_for_backward(d)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        (d,) = ctx.saved_tensors
+        return d * g, None
+
+
+class BCEWithLogits(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, targets):
+        shape = logits.shape
+        loss, d = K.bce_logits(logits.contiguous().view(-1), targets.contiguous().view(-1).float())
+        ctx.save_for_backward(d)
+        ctx.shape = shape
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        (d,) = ctx.saved_tensors
+        return (d * g).view(ctx.shape), None

@@ -24,6 +24,7 @@ import torch
 import torch.nn as nn
 
 PAD = 64  # elements; keeps every tensor 256-byte (fp32) / 128-byte (bf16) aligned
+_ARENAS: list = []  # weak references to every live ParamArena (lets the optimizers find the one owning their params)
 
 
 def _round_up(n: int, m: int = PAD) -> int:
@@ -209,6 +210,9 @@ class ParamArena:
         if self.is_cuda:
             self._build_bn_scratch()
             self.refresh_shadows(force=True)
+        import weakref
+
+        _ARENAS.append(weakref.ref(self))
 
     # ------------------------------------------------------------------ helpers
     def _set_buffer(self, dotted: str, value: torch.Tensor) -> None:
@@ -344,9 +348,23 @@ def ensure_arena(module: nn.Module, alloc=None) -> ParamArena:
     """Creates (once) the arena of a root module whose parameters already live on their final device."""
     arena = get_arena(module)
     if arena is not None and alloc is None:
-        return arena
+        s = arena.slots[0]
+        if s.param.device == arena.device and s.param.data_ptr() == arena.flat_p.data_ptr() + s.offset * 4:
+            return arena
+        # parameters were moved / replaced after the arena was built (e.g. model.to(device)): rebuild
     first = next(module.parameters())
     arena = ParamArena(module, first.device, alloc)
+    if not getattr(module, "_dmpi_sd_hook", False):
+        # Checkpoints must be ordinary tensors (contiguous, own storage, torch-native layouts) so that the
+        # reference scripts can torch.load them (SURVEY.md N25) — not strided views into the flat arena.
+        def _plain_state_dict(mod, sd, prefix, local_metadata):
+            for k in list(sd.keys()):
+                if k.startswith(prefix) and torch.is_tensor(sd[k]):
+                    sd[k] = sd[k].detach().clone(memory_format=torch.contiguous_format)
+            return sd
+
+        module._register_state_dict_hook(_plain_state_dict)
+        object.__setattr__(module, "_dmpi_sd_hook", True)
     object.__setattr__(module, "_dmpi_arena", arena)
     for m in module.modules():
         object.__setattr__(m, "_dmpi_arena_ref", arena)
