@@ -1,0 +1,391 @@
+"""Headline benchmark: data-parallel training throughput (images/s) on N B200s of one node.
+
+    python bench.py --gpus 1 --steps 20 --warmup 5                      # ours, ResNet-50 bf16 224x224 bs256/GPU
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+           bench.py --gpus N --steps K --warmup W                         # N > 1
+    python bench.py --impl reference ...                                  # the reference's stock DDP/NCCL/cuDNN path
+
+Metric / config follow BASELINE.json: "ResNet/UNet train images/sec ... (device, max over ranks)", config
+"pytorch/resnet ResNet-50 DDP bf16, synthetic 224x224 images, per-GPU batch 256" (``--model unet|resnet18`` select the
+other named configs).  One optimizer step per timed step; nothing is skipped or cached.
+
+Timing: W untimed warm-up steps, then exactly K steps between CUDA events on the compute stream, bracketed by a
+barrier + torch.cuda.synchronize() on both sides; the reported time is the MAX over ranks.  The per-step input
+(154 MB fp32 at the default config) is larger than the 126 MB L2, so no explicit L2 flush is needed.  SM clocks and
+throttle reasons are sampled with nvidia-smi during the timed region.  The ``e2e`` block repeats the measurement
+through the public API including, every step, the pinned-host -> device copy of that step's batch and the
+device -> host read of the loss.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import socket
+import statistics
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--model", choices=["resnet50", "resnet18", "unet"], default="resnet50")
+    ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default: 256 resnet, 16 unet)")
+    ap.add_argument("--size", type=int, default=0, help="image side (default: 224 resnet50/18, 512 unet)")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def free_port() -> int:
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def setup_env(args) -> None:
+    if "RANK" not in os.environ:
+        if args.gpus != 1:
+            # self-launch under torchrun so that `python bench.py --gpus N` also works
+            cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+                   "--master-addr", "127.0.0.1", "--master-port", str(free_port()), os.path.abspath(__file__)] + sys.argv[1:]
+            sys.exit(subprocess.call(cmd))
+        os.environ.update(RANK="0", LOCAL_RANK="0", WORLD_SIZE="1", LOCAL_WORLD_SIZE="1", MASTER_ADDR="127.0.0.1",
+                          MASTER_PORT=str(free_port()))
+
+
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.FIELDS}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            self.proc.kill()
+            out = ""
+        sm, mx, reasons = [], [], set()
+        for line in out.strip().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def model_defaults(args):
+    if args.model == "unet":
+        return (args.batch or 16), (args.size or 512)
+    return (args.batch or 256), (args.size or 224)
+
+
+def make_host_batches(args, batch, size, n_batches=3):
+    """Pinned host batches in the format the reference's DataLoader yields (fp32 NCHW images)."""
+    import torch
+
+    g = torch.Generator().manual_seed(1234 + int(os.environ.get("RANK", "0")))
+    out = []
+    for _ in range(n_batches):
+        x = torch.randn((batch, 3, size, size), generator=g).pin_memory()
+        if args.model == "unet":
+            y = (torch.rand((batch, size, size), generator=g) > 0.5).float().pin_memory()
+        else:
+            classes = 10 if args.model == "resnet18" else 1000
+            y = torch.randint(0, classes, (batch,), generator=g).pin_memory()
+        out.append((x, y))
+    return out
+
+
+class Cycle:
+    """Endless iterable over a few pinned host batches (the copy is real every step; only the values repeat)."""
+
+    def __init__(self, batches, n):
+        self.batches, self.n = batches, n
+
+    def __iter__(self):
+        for i in range(self.n):
+            yield self.batches[i % len(self.batches)]
+
+    def __len__(self):
+        return self.n
+
+
+# ---------------------------------------------------------------------------------------------- our arm
+def build_ours(args, batch, size):
+    import torch
+
+    import deeplearning_mpi_b200.nn as dnn
+    from deeplearning_mpi_b200 import optim
+    from deeplearning_mpi_b200.models import UNet, resnet18, resnet50
+    from deeplearning_mpi_b200.parallel import dist
+    from deeplearning_mpi_b200.parallel.ddp import DistributedDataParallel
+
+    dist.init_process_group("nccl")
+    local_rank = int(os.environ["LOCAL_RANK"])
+    device = torch.device(f"cuda:{local_rank}")
+    torch.manual_seed(0)
+    if args.model == "unet":
+        model = UNet(out_classes=1)
+    elif args.model == "resnet18":
+        model = resnet18(num_classes=10)
+    else:
+        model = resnet50(num_classes=1000)
+    model = model.to(device)
+    ddp = DistributedDataParallel(model, device_ids=[local_rank], output_device=local_rank)
+    if args.model == "unet":
+        opt = optim.Adam(ddp.parameters(), lr=1e-4)
+        crit = dnn.BCEWithLogitsLoss()
+
+        def step(x, y):
+            pred = ddp(x)
+            if pred.dim() == 4:
+                pred = pred.squeeze(1)
+            loss = crit(pred, y)
+            opt.zero_grad()
+            loss.backward()
+            dnn.clip_grad_norm_(ddp.parameters(), max_norm=1.0)
+            opt.step()
+            return loss
+    else:
+        opt = optim.SGD(ddp.parameters(), lr=0.1 if args.model == "resnet18" else 0.05, momentum=0.9, weight_decay=1e-5)
+        crit = dnn.CrossEntropyLoss()
+
+        def step(x, y):
+            opt.zero_grad()
+            loss = crit(ddp(x), y)
+            loss.backward()
+            opt.step()
+            return loss
+
+    def max_over_ranks(v: float) -> float:
+        st = dist._require()
+        if st.world == 1:
+            return v
+        if st.kind == "p2p":
+            max_over_ranks.n += 1
+            vals = st.store.all_gather(f"bench_max{max_over_ranks.n}", st.rank, st.world, repr(v).encode())
+            return max(float(b.decode()) for b in vals)
+        import torch.distributed as tdist
+
+        t = torch.tensor([v], device=device)
+        tdist.all_reduce(t, op=tdist.ReduceOp.MAX)
+        return float(t.item())
+
+    max_over_ranks.n = 0
+
+    def launches() -> int:
+        from deeplearning_mpi_b200 import _native
+
+        return _native.launches()
+
+    return dict(step=step, device=device, barrier=dist.barrier, max_over_ranks=max_over_ranks, launches=launches,
+                finish=dist.destroy_process_group, rank=dist.get_rank(), world=dist.get_world_size(),
+                backend=dist.get_backend())
+
+
+# ---------------------------------------------------------------------------------------------- reference arm
+def build_reference(args, batch, size):
+    """The reference's own code path: modules imported UNMODIFIED from baseline/_ref (installed from /root/reference),
+    stock torch.distributed NCCL + torch.nn.parallel.DistributedDataParallel + cuDNN/cuBLAS + torch.optim, with the
+    exact wrap kwargs / optimizer / loss of ref:pytorch/resnet/main.py:36-54,113-132 and
+    ref:pytorch/unet/train.py:60-75,160-196.  BASELINE.json names bf16, so the forward runs under
+    torch.autocast(bfloat16) (the stock way to get bf16 out of these scripts); ResNet-50 replaces the script's
+    hard-coded resnet18 constructor because BASELINE.json names ResNet-50."""
+    ref_root = os.path.join(ROOT, "baseline", "_ref")
+    if not os.path.isdir(os.path.join(ref_root, "pytorch")):
+        print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref is empty (reference not installed)"}))
+        sys.exit(0)
+    sys.path.insert(0, ref_root)
+    sys.path.insert(0, os.path.join(ref_root, "pytorch", "unet"))
+    import torch
+    import torch.distributed as tdist
+    import torch.nn as nn
+    import torch.optim as toptim
+    import torchvision
+
+    local_rank = int(os.environ["LOCAL_RANK"])
+    device = torch.device(f"cuda:{local_rank}")
+    if args.model == "unet":
+        import pytorch.unet.train as ref_train  # noqa: F401  (env parsing + helpers, unmodified)
+
+        ref_train.set_random_seeds(42)
+        tdist.init_process_group("nccl")
+        ddp = ref_train.build_model(False, "unused.pth")          # UNet(out_classes=1) -> .to(device) -> DDP
+        opt = toptim.Adam(ddp.parameters(), lr=1e-4)
+        crit = nn.BCEWithLogitsLoss()
+
+        def step(x, y):
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                pred = ddp(x)
+                if pred.dim() == 4:
+                    pred = pred.squeeze(1)
+                loss = crit(pred.float(), y)
+            opt.zero_grad()
+            loss.backward()
+            torch.nn.utils.clip_grad_norm_(ddp.parameters(), max_norm=1.0)
+            opt.step()
+            return loss
+    else:
+        import pytorch.resnet.main as ref_main
+
+        ref_main.random_seed = 0
+        ref_main.resume = False
+        ref_main.model_filepath = "unused.pth"
+        ref_main.set_random_seeds()                                # cudnn.benchmark = True etc.
+        tdist.init_process_group("nccl")
+        if args.model == "resnet18":
+            ddp = ref_main.build_model()                           # the script's own builder, verbatim
+        else:
+            model = torchvision.models.resnet50(weights=None).to(device)
+            ddp = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local_rank], output_device=local_rank)
+        opt = toptim.SGD(ddp.parameters(), lr=0.1 if args.model == "resnet18" else 0.05, momentum=0.9, weight_decay=1e-5)
+        crit = nn.CrossEntropyLoss()
+
+        def step(x, y):
+            opt.zero_grad()
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                out = ddp(x)
+                loss = crit(out.float(), y)
+            loss.backward()
+            opt.step()
+            return loss
+
+    def max_over_ranks(v: float) -> float:
+        if tdist.get_world_size() == 1:
+            return v
+        t = torch.tensor([v], device=device)
+        tdist.all_reduce(t, op=tdist.ReduceOp.MAX)
+        return float(t.item())
+
+    return dict(step=step, device=device, barrier=tdist.barrier, max_over_ranks=max_over_ranks, launches=lambda: 0,
+                finish=tdist.destroy_process_group, rank=tdist.get_rank(), world=tdist.get_world_size(),
+                backend="nccl")
+
+
+# ---------------------------------------------------------------------------------------------- measurement
+def main():
+    args = parse_args()
+    setup_env(args)
+    import torch
+
+    if not torch.cuda.is_available():
+        print(json.dumps({"impl": args.impl, "unavailable": "no CUDA device"}))
+        return
+    batch, size = model_defaults(args)
+    arm = (build_ours if args.impl == "ours" else build_reference)(args, batch, size)
+    step, device = arm["step"], arm["device"]
+    world, rank = arm["world"], arm["rank"]
+    host = make_host_batches(args, batch, size)
+    x_dev = host[0][0].to(device)
+    y_dev = host[0][1].to(device)
+
+    # ---- device-timed: inputs resident on the device
+    for _ in range(args.warmup):
+        step(x_dev, y_dev)
+    torch.cuda.synchronize()
+    arm["barrier"]()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(device.index or 0)
+    if rank == 0:
+        sampler.start()
+    l0 = arm["launches"]()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        loss = step(x_dev, y_dev)
+    e1.record()
+    torch.cuda.synchronize()
+    arm["barrier"]()
+    torch.cuda.synchronize()
+    launches = arm["launches"]() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    ms_total = arm["max_over_ranks"](e0.elapsed_time(e1))
+    ms_per_step = ms_total / args.steps
+    value = world * batch * args.steps / (ms_total / 1e3)
+    final_loss = float(loss.item())
+
+    # ---- end to end: pinned host batch -> device every step (look-ahead prefetch in our arm; the reference's
+    #      synchronous .to(device) in its arm) and the loss read back to the host every step
+    e2e = None
+    if not args.no_e2e:
+        n_e2e = args.steps
+        if args.impl == "ours":
+            from deeplearning_mpi_b200.utils.data import CudaPrefetcher
+
+            loader = CudaPrefetcher(Cycle(host, n_e2e + 2), device)
+        else:
+            loader = Cycle(host, n_e2e + 2)
+        h2d = sum(t.numel() * t.element_size() for t in host[0])
+        it = iter(loader)
+        for _ in range(2):  # warm the pipeline
+            xb, yb = next(it)
+            if args.impl == "reference":
+                xb, yb = xb.to(device), yb.to(device)
+            step(xb, yb).item()
+        torch.cuda.synchronize()
+        arm["barrier"]()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for xb, yb in it:
+            if args.impl == "reference":
+                xb, yb = xb.to(device), yb.to(device)     # ref:pytorch/resnet/main.py:126
+            step(xb, yb).item()                            # ref:pytorch/resnet/main.py:130 (loss.item() every step)
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        arm["barrier"]()
+        s_total = arm["max_over_ranks"](t1 - t0)
+        e2e = {"value": world * batch * n_e2e / s_total, "unit": "images/s", "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": 4, "ms_per_step": 1e3 * s_total / n_e2e}
+
+    if rank == 0:
+        par = f"dp{world}"
+        rec = {
+            "metric": "train_images_per_sec", "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": args.impl,
+            "config": {"model": args.model, "global_batch": batch * world, "per_gpu_batch": batch, "image_size": size,
+                       "seq_len": None, "parallelism": par, "backend": arm["backend"],
+                       "optimizer": "adam+clip" if args.model == "unet" else "sgd_momentum",
+                       "l2_policy": "per-step inputs and activations exceed the 126 MB L2; no explicit flush"},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "final_loss": final_loss,
+        }
+        print(json.dumps(rec))
+    arm["finish"]()
+
+
+if __name__ == "__main__":
+    main()

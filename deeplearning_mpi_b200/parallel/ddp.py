@@ -1,0 +1,262 @@
+"""DistributedDataParallel-compatible wrapper.
+
+    ddp_model = DistributedDataParallel(model, device_ids=[LOCAL_RANK], output_device=LOCAL_RANK)
+
+is the exact call of ref:pytorch/resnet/main.py:44-46 and ref:pytorch/unet/train.py:68-70; ``.train() / .eval() /
+.parameters() / .state_dict()`` (``module.``-prefixed keys) / ``.load_state_dict()`` / ``__call__`` behave the same.
+
+What happens underneath is different from c10d:
+
+* wrap time: parameters, gradients and buffers are re-homed into ONE peer-mapped symmetric arena
+  (``[grads | params | buffers]``); shapes are verified across ranks by exchanging a layout hash through the store;
+  rank 0's parameters and buffers are pushed to every peer by the NVLink broadcast kernel.
+* buckets are contiguous byte ranges of the gradient arena in reverse registration order (1 MiB first bucket,
+  then ``bucket_cap_mb``).  Gradients are produced *in* the bucket (wgrad kernels accumulate into their slot), the
+  C++ reducer counts readiness and launches the fused (sum * 1/world) all-reduce kernel for bucket b on a
+  high-priority comm stream as soon as buckets 0..b are complete — overlapping the rest of backward.
+* every training forward re-broadcasts rank 0's buffers (BatchNorm running statistics) like
+  ``broadcast_buffers=True`` does — with ONE kernel over the contiguous buffer range.  Forwards under
+  ``torch.no_grad()`` never communicate, so a rank-0-only evaluation between epochs
+  (ref:pytorch/resnet/main.py:136-139) cannot dead-lock the other ranks.
+* ``no_sync()`` accumulates locally.  On gloo / NCCL-fallback groups the same reducer drives
+  ``torch.distributed.all_reduce`` on the flat bucket views.
+"""
+from __future__ import annotations
+
+import contextlib
+import ctypes as C
+from typing import List, Optional
+
+import torch
+import torch.nn as nn
+
+from .. import _native as N
+from ..utils.arena import ParamArena, _round_up, ensure_arena
+from . import dist as D
+
+_MIB = 1 << 20
+
+
+class DistributedDataParallel(nn.Module):
+    def __init__(self, module: nn.Module, device_ids: Optional[List[int]] = None, output_device=None,
+                 broadcast_buffers: bool = True, bucket_cap_mb: float = 25.0, first_bucket_mb: float = 1.0,
+                 find_unused_parameters: bool = False, gradient_as_bucket_view: bool = True, **_ignored):
+        super().__init__()
+        st = D._require()
+        self.module = module
+        self.broadcast_buffers = broadcast_buffers
+        self.require_backward_grad_sync = True
+        self._st = st
+        self.world, self.rank = st.world, st.rank
+        if find_unused_parameters:
+            raise NotImplementedError("find_unused_parameters is not used by the reference and not supported")
+        params = [p for p in module.parameters() if p.requires_grad]
+        if not params:
+            raise RuntimeError("DistributedDataParallel is not needed when a module doesn't have any parameter "
+                               "that requires a gradient.")
+        self._is_cuda = params[0].is_cuda
+        if st.kind == "p2p" and not self._is_cuda:
+            raise RuntimeError("the p2p/nccl backend needs the module on its CUDA device before wrapping "
+                               "(model.to(device), ref:pytorch/resnet/main.py:42)")
+        # ---- re-home params / grads / buffers
+        self._comm = None
+        if st.kind == "p2p":
+            total = sum(_round_up(p.numel()) for p in module.parameters())
+            buf_bytes = sum(b.numel() * b.element_size() + 16 for b in module.buffers()) + 512
+            g_bytes = _round_up(total * 4, 256)
+            p_bytes = g_bytes
+            b_bytes = _round_up(buf_bytes, 256)
+            self._comm = st.new_comm(g_bytes + p_bytes + b_bytes)
+            self._off = {"grads": 0, "params": g_bytes, "buffers": g_bytes + p_bytes}
+            self._sizes = {"grads": g_bytes, "params": p_bytes, "buffers": b_bytes}
+            comm = self._comm
+
+            def alloc(name: str, nbytes: int) -> torch.Tensor:
+                assert nbytes <= self._sizes[name], (name, nbytes, self._sizes[name])
+                return comm.tensor(self._off[name], nbytes)
+
+            self.arena: ParamArena = ensure_arena(module, alloc)
+        else:
+            self.arena = ensure_arena(module)
+        arena = self.arena
+        # ---- bucket plan (arena slots are already in bucket-fill order)
+        sizes = (C.c_int64 * len(arena.slots))(*[_round_up(s.numel) * 4 for s in arena.slots])
+        bucket_of = (C.c_int * len(arena.slots))()
+        host = N.host()
+        self.n_buckets = host.dmpi_plan_buckets(sizes, len(arena.slots), int(first_bucket_mb * _MIB),
+                                                int(bucket_cap_mb * _MIB), bucket_of)
+        self.bucket_of = list(bucket_of)
+        self.bucket_ranges = []  # (element offset, element count) per bucket
+        for b in range(self.n_buckets):
+            idx = [i for i, bb in enumerate(self.bucket_of) if bb == b]
+            lo = arena.slots[idx[0]].offset
+            hi = arena.slots[idx[-1]].offset + _round_up(arena.slots[idx[-1]].numel)
+            self.bucket_ranges.append((lo, hi - lo))
+        # ---- verify the layout on every rank (N5), then sync state from rank 0 (N6)
+        logical = (C.c_int64 * len(arena.slots))(*[s.numel for s in arena.slots])
+        self.plan_hash = int(host.dmpi_plan_hash(logical, bucket_of, len(arena.slots)))
+        self._verify_across_ranks()
+        self._sync_module_states()
+        # ---- reducer
+        self._reducer = host.dmpi_reducer_create(len(arena.slots), bucket_of, self.n_buckets)
+        self._cuda_red = None
+        if st.kind == "p2p":
+            lib = N.cuda()
+            offs = (C.c_int64 * self.n_buckets)(*[self._off["grads"] + lo * 4 for lo, _ in self.bucket_ranges])
+            nbytes = (C.c_int64 * self.n_buckets)(*[n * 4 for _, n in self.bucket_ranges])
+            self._cuda_red = lib.dmpi_reducer_cuda_create(self._comm.ptrs, self.n_buckets, offs, nbytes,
+                                                          1.0 / self.world, st.oneshot_max_bytes,
+                                                          self._comm.slot_bytes, 32, 0)
+            host.dmpi_reducer_set_launch_cb(self._reducer, lib.dmpi_reducer_cuda_launch_fn(), self._cuda_red)
+        self._out_buckets = (C.c_int * max(self.n_buckets, 1))()
+        self._pending_work = []
+        self._armed = False
+        self._finalize_queued = False
+        self._marked = bytearray(len(arena.slots))
+        self._install_hooks()
+
+    # ------------------------------------------------------------------ construction helpers
+    def _verify_across_ranks(self) -> None:
+        st = self._st
+        if self.world == 1:
+            return
+        if st.kind == "p2p":
+            tag = f"verify{st.n_comms}"
+            all_h = st.store.all_gather(tag, self.rank, self.world, str(self.plan_hash).encode())
+            if any(h != all_h[0] for h in all_h):
+                raise RuntimeError("DDP: parameter shapes / bucket plan differ across ranks "
+                                   f"(hashes {[h.decode() for h in all_h]})")
+        else:
+            import torch.distributed as tdist
+
+            h = torch.tensor([self.plan_hash & 0x7FFFFFFFFFFFFFFF], dtype=torch.int64,
+                             device=self.arena.device if self._is_cuda else "cpu")
+            ref = h.clone()
+            tdist.broadcast(ref, 0)
+            if int(ref.item()) != int(h.item()):
+                raise RuntimeError("DDP: parameter shapes / bucket plan differ from rank 0")
+
+    def _sync_module_states(self) -> None:
+        """Wrap-time broadcast of parameters and buffers from rank 0 (c10d: _sync_module_states)."""
+        if self.world == 1:
+            return
+        st = self._st
+        if st.kind == "p2p":
+            self._comm.broadcast(self._off["params"], self._sizes["params"] + self._sizes["buffers"], 0, nblocks=32)
+            torch.cuda.current_stream().synchronize()
+            self.arena.refresh_shadows(force=True)
+        else:
+            import torch.distributed as tdist
+
+            with torch.no_grad():
+                tdist.broadcast(self.arena.flat_p, 0)
+                tdist.broadcast(self.arena.flat_b, 0)
+
+    def _install_hooks(self) -> None:
+        arena = self.arena
+        for i, slot in enumerate(arena.slots):
+            slot.ready_cb = (lambda idx=i: self._mark_ready(idx))
+            if slot.param.requires_grad:
+                # parameters whose gradient comes from stock autograd (not from our fused backward)
+                slot.param.register_post_accumulate_grad_hook(lambda p, idx=i: self._autograd_hook(idx))
+
+    # ------------------------------------------------------------------ per-iteration machinery
+    def _autograd_hook(self, idx: int) -> None:
+        slot = self.arena.slots[idx]
+        g = slot.param.grad
+        base = self.arena.flat_g.data_ptr() + slot.offset * 4
+        if g is not None and g.data_ptr() != base:
+            # autograd installed a fresh tensor (e.g. after zero_grad(set_to_none=True)): copy into the bucket view
+            from ..utils.arena import _logical_view
+
+            view = _logical_view(self.arena.flat_g, slot)
+            view.copy_(g)
+            slot.param.grad = view
+        if self._marked[idx]:
+            return  # the fused backward already published this slot in this iteration
+        self._mark_ready(idx)
+
+    def _mark_ready(self, idx: int) -> None:
+        if not self._armed:
+            return
+        if not self._finalize_queued:
+            self._finalize_queued = True
+            torch.autograd.Variable._execution_engine.queue_callback(self._finalize_backward)
+        self._marked[idx] = 1
+        n = N.host().dmpi_reducer_mark_ready(self._reducer, idx, self._out_buckets, self.n_buckets)
+        if n == -1:
+            raise RuntimeError(f"DDP: parameter '{self.arena.slots[idx].name}' was marked ready twice in one "
+                               "backward pass (shared module used twice?)")
+        if n > 0:
+            if self._cuda_red is not None:
+                N.count_launch(n if self.world > 1 else 0)
+            else:
+                self._launch_torch_buckets([self._out_buckets[i] for i in range(n)])
+
+    def _launch_torch_buckets(self, buckets: List[int]) -> None:
+        import torch.distributed as tdist
+
+        for b in buckets:
+            lo, n = self.bucket_ranges[b]
+            view = self.arena.flat_g[lo: lo + n]
+            if self.world > 1:
+                view.div_(self.world)
+                self._pending_work.append(tdist.all_reduce(view, async_op=True))
+
+    def _finalize_backward(self) -> None:
+        self._finalize_queued = False
+        if not self._armed:
+            return
+        self._armed = False
+        pending = N.host().dmpi_reducer_pending(self._reducer)
+        if pending != 0:
+            raise RuntimeError(f"DDP: backward finished with {pending} gradient bucket(s) incomplete — some "
+                               "parameters did not receive a gradient (unused parameters are not supported)")
+        if self._cuda_red is not None:
+            rc = N.cuda().dmpi_reducer_cuda_finalize(self._cuda_red)
+            if rc != 0:
+                raise RuntimeError(f"DDP: all-reduce launch failed ({rc})")
+        for w in self._pending_work:
+            w.wait()
+        self._pending_work.clear()
+
+    def _sync_buffers(self) -> None:
+        if self.world == 1 or not self.broadcast_buffers or self.arena.buffer_bytes == 0:
+            return
+        if self._st.kind == "p2p":
+            self._comm.broadcast(self._off["buffers"], _round_up(self.arena.buffer_bytes, 256), 0, nblocks=4)
+        else:
+            import torch.distributed as tdist
+
+            tdist.broadcast(self.arena.flat_b, 0)
+
+    @contextlib.contextmanager
+    def no_sync(self):
+        old = self.require_backward_grad_sync
+        self.require_backward_grad_sync = False
+        try:
+            yield
+        finally:
+            self.require_backward_grad_sync = old
+
+    def forward(self, *inputs, **kwargs):
+        if torch.is_grad_enabled() and self.training:
+            self._sync_buffers()
+            if self.require_backward_grad_sync:
+                N.host().dmpi_reducer_reset(self._reducer)
+                if self._cuda_red is not None:
+                    N.cuda().dmpi_reducer_cuda_begin(self._cuda_red, N.stream_ptr())
+                self._armed = True
+                self._marked = bytearray(len(self.arena.slots))
+            else:
+                self._armed = False
+        return self.module(*inputs, **kwargs)
+
+    def __del__(self):  # pragma: no cover
+        try:
+            if getattr(self, "_reducer", None):
+                N.host().dmpi_reducer_destroy(self._reducer)
+            if getattr(self, "_cuda_red", None):
+                N.cuda().dmpi_reducer_cuda_destroy(self._cuda_red)
+        except Exception:
+            pass
