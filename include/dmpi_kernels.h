@@ -1,0 +1,76 @@
+/* C ABI of the non-GEMM sm_100a kernels (csrc/kernels/{norm,pool,loss,optim,misc}).
+ *
+ * Conventions: activations are NHWC bf16 with a uniform pixel stride `ld*` (elements), per-channel vectors are fp32,
+ * `stream` is a cudaStream_t passed as void*, every function returns 0 on success or a negative code, and nothing
+ * here allocates: outputs and scratch are supplied by the caller.
+ */
+#ifndef DMPI_KERNELS_H_
+#define DMPI_KERNELS_H_
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- BatchNorm2d (+residual) (+ReLU)   (ref:pytorch/unet/model.py:10-11,13-14; torchvision resnet bn/relu) */
+/* out = relu?( (y - mean) * invstd * gamma + beta [+ res] ).  training != 0: mean/var come from sum/sqsum over the M
+ * rows (as produced by the igemm epilogue or dmpi_bn_stats), save_mean/save_invstd are written, running stats and
+ * num_batches_tracked are updated like torch (momentum EMA, unbiased running_var).  training == 0: running stats. */
+int dmpi_bn_forward(const void* y, const void* res, void* out, long long M, int C, long long ldy, long long ldr,
+                    long long ldo, const float* sum, const float* sqsum, const float* gamma, const float* beta,
+                    float* save_mean, float* save_invstd, float* running_mean, float* running_var,
+                    long long* num_batches_tracked, float eps, float momentum, int training, int relu, void* stream);
+/* dy = gamma*invstd*(dz - mean(dz) - xhat*mean(dz*xhat)), dz = dout * (act > 0) (act == NULL: no ReLU);
+ * dres (optional) = dz; dgamma += sum(dz*xhat); dbeta += sum(dz).
+ * `acc` is caller-provided scratch of 2*C floats that MUST be zero on entry (it is left dirty). */
+int dmpi_bn_backward(const void* dout, const void* y, const void* act, void* dy, void* dres, long long M, int C,
+                     long long ld_dout, long long ldy, long long ld_act, long long ld_dy, long long ld_dres,
+                     const float* mean, const float* invstd, const float* gamma, float* acc, float* dgamma,
+                     float* dbeta, void* stream);
+/* sum[c] += sum_rows y, sqsum[c] += sum_rows y*y */
+int dmpi_bn_stats(const void* y, long long M, int C, long long ld, float* sum, float* sqsum, void* stream);
+
+/* ---- pooling (ref:pytorch/unet/model.py:25; torchvision resnet maxpool/avgpool) */
+int dmpi_maxpool_forward(const void* x, void* y, void* idx /* uint8 arg-max tap or NULL */, int N, int H, int W, int C,
+                         int OH, int OW, int k, int s, int p, long long xsn, long long xsh, long long xsw,
+                         long long ysn, long long ysh, long long ysw, void* stream);
+int dmpi_maxpool_backward(const void* dy, const void* idx, void* dx, int N, int H, int W, int C, int OH, int OW, int k,
+                          int s, int p, long long dsn, long long dsh, long long dsw, long long xsn, long long xsh,
+                          long long xsw, void* stream);
+int dmpi_avgpool_forward(const void* x, void* y, int N, int HW, int C, void* stream);
+int dmpi_avgpool_backward(const void* dy, void* dx, int N, int HW, int C, void* stream);
+
+/* ---- losses, forward value + input gradient in one pass (ref:pytorch/resnet/main.py:113; ref:pytorch/unet/train.py:162) */
+int dmpi_softmax_xent(const float* logits, const long long* labels, void* dlogits_f32, float* loss_sum, int M, int N,
+                      long long ld, long long ldd, int ldd_cols, float grad_scale, void* stream);
+int dmpi_bce_logits(const float* x, const float* t, float* dx, float* loss_sum, long long M, float grad_scale,
+                    void* stream);
+/* narrow 1x1 conv head, K <= 8 output classes (ref:pytorch/unet/model.py:68) */
+int dmpi_head_forward(const void* x, const float* w, const float* b, float* y, long long M, int C, int K, long long ldx,
+                      void* stream);
+int dmpi_head_backward(const float* dy, const void* x, const float* w, void* dx, float* dw, float* db, long long M,
+                       int C, int K, long long ldx, long long ld_dx, void* stream);
+
+/* ---- flat-arena optimizers (ref:pytorch/resnet/main.py:114; ref:pytorch/unet/train.py:160-161,194) */
+int dmpi_sgd_step(float* p, const float* g, float* mom, void* bf16_shadow, long long n, float lr, float momentum,
+                  float dampening, float wd, int first_step, const float* clip_sumsq, float max_norm, void* stream);
+int dmpi_adam_step(float* p, const float* g, float* m, float* v, void* bf16_shadow, long long n, float lr, float beta1,
+                   float beta2, float eps, float wd, float bias_corr1, float bias_corr2, const float* clip_sumsq,
+                   float max_norm, void* stream);
+int dmpi_sumsq(const float* g, long long n, float* out, void* stream);
+int dmpi_scale_by_clip(float* g, long long n, const float* sumsq, float max_norm, void* stream);
+int dmpi_cast_bf16(const float* src, void* dst, long long n, void* stream);
+
+/* ---- layout / staging (ref:pytorch/resnet/main.py:126 input .to(device)) */
+int dmpi_nchw_to_nhwc8_padded(const float* x, void* out, int N, int C, int H, int W, int pad, int Hp, int Wp,
+                              void* stream);
+int dmpi_nchw_to_nhwc(const float* x, void* out, int N, int C, int HW, void* stream);
+int dmpi_nhwc_to_nchw(const void* x, float* out, int N, int C, int HW, long long ldx, void* stream);
+int dmpi_transpose_table(const void* table, int n_entries, int total_tiles, void* stream);
+int dmpi_stem_pack(const float* w, void* out, int K, int R, int S, int C, void* stream);
+int dmpi_stem_unpack_grad(const float* dwin, float* dw, int K, int R, int S, int C, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
