@@ -22,10 +22,12 @@ ROOT = Path(__file__).resolve().parent
 LIB_DIR = ROOT / "deeplearning_mpi_b200" / "_lib"
 OBJ_DIR = ROOT / "build" / "obj"
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-CXX = os.environ.get("CXX", "g++")
+# The system g++ links libstdc++ dynamically.  (Do NOT honour $CXX blindly: a toolchain that links libstdc++ statically
+# makes our .so export a private copy of std:: symbols, which other libraries in the process — cuDNN — then bind to.)
+CXX = os.environ.get("DMPI_CXX") or ("/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++")
 
 NVCC_FLAGS = [
-    "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+    "-ccbin", CXX, "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC", "-Xptxas", "-v",
 ]
 CXX_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-Wall", "-pthread"]
@@ -96,7 +98,7 @@ def build(force: bool = False, verbose: bool = False) -> dict[str, str]:
         newest = max(os.path.getmtime(i) for i in inputs)
         if not force and out.exists() and os.path.getmtime(out) >= newest:
             return
-        cmd = [CXX, "-shared", "-o", str(out)] + inputs + extra
+        cmd = [CXX, "-shared", "-Wl,--exclude-libs,ALL", "-o", str(out)] + inputs + extra
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed: {' '.join(cmd)}\n{r.stderr}")

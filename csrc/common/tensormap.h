@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 namespace dmpi {
@@ -18,6 +19,7 @@ inline EncodeTiledFn get_encode_tiled() {
   static EncodeTiledFn fn = nullptr;
   if (!fn) {
     void* p = nullptr;
+    if (getenv("DMPI_TRACE")) fprintf(stderr, "[dmpi] resolving cuTensorMapEncodeTiled\n");
     cudaDriverEntryPointQueryResult q;
     cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q);
     if (e != cudaSuccess || q != cudaDriverEntryPointSuccess || !p) {

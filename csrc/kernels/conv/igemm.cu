@@ -17,6 +17,7 @@
 // Replaces cuDNN fprop/dgrad and cuBLAS GEMM behind ref:pytorch/unet/model.py:8-14,37-38,68 and
 // torchvision's resnet conv/fc.
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <mutex>
@@ -328,6 +329,7 @@ static int launch_igemm(const ConvKernelParams& kp, int num_sms, cudaStream_t st
   if (!attr_set) {
     cudaError_t e =
         cudaFuncSetAttribute(igemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, IgemmCfg<BN>::kSmemBytes);
+    if (getenv("DMPI_TRACE")) fprintf(stderr, "[dmpi] cudaFuncSetAttribute: %s\n", cudaGetErrorString(e));
     if (e != cudaSuccess) {
       set_err(cudaGetErrorString(e));
       return -10;
@@ -339,8 +341,14 @@ static int launch_igemm(const ConvKernelParams& kp, int num_sms, cudaStream_t st
   // A grid that is a multiple of the N-tile count keeps n_blk fixed per CTA, so the BatchNorm partial sums stay
   // in registers for the whole kernel (one atomic flush per CTA).
   if (grid == num_sms && kp.num_n_tiles > 1 && kp.num_n_tiles <= num_sms) grid = (num_sms / kp.num_n_tiles) * kp.num_n_tiles;
+  if (getenv("DMPI_TRACE")) fprintf(stderr, "[dmpi] launch grid=%d smem=%d params=%zu bytes\n", grid, IgemmCfg<BN>::kSmemBytes, sizeof(kp));
   igemm_kernel<BN><<<grid, kThreads, IgemmCfg<BN>::kSmemBytes, stream>>>(kp);
   cudaError_t e = cudaGetLastError();
+  if (getenv("DMPI_TRACE")) {
+    fprintf(stderr, "[dmpi] launched: %s\n", cudaGetErrorString(e));
+    cudaError_t se = cudaDeviceSynchronize();
+    fprintf(stderr, "[dmpi] synced: %s\n", cudaGetErrorString(se));
+  }
   if (e != cudaSuccess) {
     set_err(cudaGetErrorString(e));
     return -11;
@@ -408,6 +416,8 @@ extern "C" int dmpi_igemm_run(dmpi_conv_plan* plan, const void* a, const void* b
                               float* stat_sum, float* stat_sqsum, void* stream) {
   const dmpi_conv_desc& d = plan->desc;
   ConvKernelParams& kp = plan->params;
+  static const bool trace = getenv("DMPI_TRACE") != nullptr;
+  if (trace) fprintf(stderr, "[dmpi] igemm_run plan=%p a=%p b=%p out=%p bn=%d rows=%d\n", (void*)plan, a, b, out, d.bn, kp.rows);
   if (kp.rows < 1 || kp.rows > kTileM) {
     set_err("igemm: pixel box must hold 1..128 rows");
     return -1;
@@ -463,7 +473,9 @@ extern "C" int dmpi_igemm_run(dmpi_conv_plan* plan, const void* a, const void* b
     set_err("igemm: stat_mod set but statistics pointers are null");
     return -8;
   }
+  if (trace) fprintf(stderr, "[dmpi] maps encoded\n");
   if (plan->num_sms == 0) plan->num_sms = device_sm_count();
+  if (trace) fprintf(stderr, "[dmpi] sms=%d launching\n", plan->num_sms);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   switch (d.bn) {
     case 64: return launch_igemm<64>(kp, plan->num_sms, s);

@@ -67,7 +67,7 @@ def _load(name: str):
     path = _LIB_DIR / name
     if not path.exists():
         raise FileNotFoundError(f"{path} not found — run `python build.py` (or __graft_entry__.build()) first")
-    return C.CDLL(str(path), mode=C.RTLD_GLOBAL)
+    return C.CDLL(str(path))  # RTLD_LOCAL: never interpose symbols of other libraries
 
 
 def host():
