@@ -366,3 +366,77 @@ extern "C" int dmpi_bn_stats(const void* y, long long M, int C, long long ld, fl
       static_cast<const __nv_bfloat16*>(y), M, C, ld, sum, sqsum);
   return cudaGetLastError() == cudaSuccess ? 0 : -2;
 }
+
+// ------------------------------------------------------------------------------------------------------------
+// BatchNorm backward for callers that must not allocate.
+//
+// dmpi_bn_backward() above needs 2*C floats of zeroed scratch from its caller.  Some callers have nowhere to get it:
+//   * a host program that gave the whole GPU to its own memory pool at start-up, so a later cudaMalloc simply fails;
+//   * code on a latency-critical path, where cudaMalloc / cudaFree would stall every stream of the device;
+//   * a plug-in running inside somebody else's callback that may neither call the CUDA allocator nor borrow the host
+//     framework's one (so no torch tensors either).
+// For them the scratch lives inside the library image instead: one file-scope __device__ array, 16 KiB, present on
+// every GPU that loads libdmpi_cuda.so for as long as the process lives.  The limit that follows is C <= 2048
+// channels (the largest BatchNorm in ResNet-50/101/152 and in the UNet has 2048).
+//
+// Things a caller has to know:
+//   * The first call on each device looks the array's device address up (cudaGetSymbolAddress) and remembers it.
+//     Make that first call during set-up, with the right device current and before you start capturing any stream.
+//   * Every call clears the 2*C floats it is about to use (an async memset on `stream`) and leaves them dirty.
+//   * All calls on one GPU share the one array.  Two calls whose kernels can overlap on the GPU (different streams
+//     without an ordering between them, or different host threads doing the same) corrupt each other's sums; keep
+//     calls on a device stream-ordered.
+//   * Nothing is allocated or freed: no cudaMalloc / cudaFree / cudaMallocAsync, no library workspace.
+// Return codes: 0 ok; -1 C not a positive multiple of 8; -2 launch failure; -4 C above the 2048-channel limit;
+// -5 / -6 the device or the scratch symbol could not be resolved (a message is also written to stderr).
+#include <stdio.h>
+
+#include <mutex>
+
+namespace dmpi {
+constexpr int kNoAllocMaxChannels = 2048;
+constexpr int kNoAllocMaxDevices = 64;
+// Host code must never use this name as a pointer: on the host it is only a handle for cudaGetSymbolAddress.
+static __device__ __align__(256) float g_bn_bwd_static_scratch[2 * kNoAllocMaxChannels];
+static std::mutex g_noalloc_mutex;
+static float* g_noalloc_scratch_addr[kNoAllocMaxDevices] = {nullptr};
+}  // namespace dmpi
+
+extern "C" int dmpi_bn_backward_noalloc(const void* dout, const void* y, const void* act, void* dy, void* dres,
+                                        long long M, int C, long long ld_dout, long long ldy, long long ld_act,
+                                        long long ld_dy, long long ld_dres, const float* mean, const float* invstd,
+                                        const float* gamma, float* dgamma, float* dbeta, void* stream) {
+  if (C <= 0 || C % 8 != 0) return -1;
+  if (C > dmpi::kNoAllocMaxChannels) {
+    fprintf(stderr, "[dmpi] dmpi_bn_backward_noalloc: C=%d exceeds the built-in scratch (max %d channels); "
+                    "use dmpi_bn_backward with caller-provided scratch\n", C, dmpi::kNoAllocMaxChannels);
+    return -4;
+  }
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= dmpi::kNoAllocMaxDevices) {
+    fprintf(stderr, "[dmpi] dmpi_bn_backward_noalloc: cannot identify the current device\n");
+    return -5;
+  }
+  float* acc = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(dmpi::g_noalloc_mutex);
+    acc = dmpi::g_noalloc_scratch_addr[dev];
+    if (acc == nullptr) {  // first call on this device: resolve the device address of the static array
+      void* p = nullptr;
+      const cudaError_t e = cudaGetSymbolAddress(&p, dmpi::g_bn_bwd_static_scratch);
+      if (e != cudaSuccess || p == nullptr) {
+        fprintf(stderr, "[dmpi] dmpi_bn_backward_noalloc: cudaGetSymbolAddress failed on device %d: %s\n", dev,
+                cudaGetErrorString(e));
+        return -6;
+      }
+      acc = static_cast<float*>(p);
+      dmpi::g_noalloc_scratch_addr[dev] = acc;
+    }
+  }
+  // the reduce pass accumulates with atomics, so the part of the shared array used by this call must start at zero
+  if (cudaMemsetAsync(acc, 0, 2 * static_cast<size_t>(C) * sizeof(float), static_cast<cudaStream_t>(stream)) !=
+      cudaSuccess)
+    return -2;
+  return dmpi_bn_backward(dout, y, act, dy, dres, M, C, ld_dout, ldy, ld_act, ld_dy, ld_dres, mean, invstd, gamma, acc,
+                          dgamma, dbeta, stream);
+}

@@ -27,6 +27,20 @@ int dmpi_bn_backward(const void* dout, const void* y, const void* act, void* dy,
                      long long ld_dout, long long ldy, long long ld_act, long long ld_dy, long long ld_dres,
                      const float* mean, const float* invstd, const float* gamma, float* acc, float* dgamma,
                      float* dbeta, void* stream);
+/* Same computation for callers that cannot allocate the scratch (GPU memory fully owned by the host application's
+ * pool, latency-critical paths where cudaMalloc/cudaFree would stall the device, plug-ins barred from any allocator).
+ * This entry point has no counterpart in the reference; it exists for such embedders only.
+ * The 2*C floats live in a 16 KiB __device__ array inside libdmpi_cuda.so (held by every GPU that loads the library
+ * until the process exits), hence the limit C <= 2048: larger C returns -4 with a message on stderr.
+ * The first call on a device resolves the array's address (cudaGetSymbolAddress): make it during set-up, with that
+ * device current, before any stream capture.  Each call clears the floats it uses and leaves them dirty.  All calls
+ * on a GPU share the array, so calls whose kernels may overlap on the GPU race: keep them stream-ordered.
+ * Allocates nothing (no cudaMalloc / cudaFree / library workspace).  Codes: 0, -1 bad C, -2 launch, -4 too large,
+ * -5 / -6 device or symbol lookup failed. */
+int dmpi_bn_backward_noalloc(const void* dout, const void* y, const void* act, void* dy, void* dres, long long M, int C,
+                             long long ld_dout, long long ldy, long long ld_act, long long ld_dy, long long ld_dres,
+                             const float* mean, const float* invstd, const float* gamma, float* dgamma, float* dbeta,
+                             void* stream);
 /* sum[c] += sum_rows y, sqsum[c] += sum_rows y*y */
 int dmpi_bn_stats(const void* y, long long M, int C, long long ld, float* sum, float* sqsum, void* stream);
 
