@@ -45,19 +45,20 @@ class _FlatOptimizer:
         self.step_count = 0
 
     # -- arena discovery is lazy: the model may be wrapped / moved after the optimizer is built
-    def _resolve_arena(self) -> Optional[ParamArena]:
+    def _resolve_arena(self, cuda_only: bool = True) -> Optional[ParamArena]:
         if self._arena is not None:
             s = self._arena.slots[0]
-            if s.param.data_ptr() == self._arena.flat_p.data_ptr() + s.offset * 4:
-                return self._arena
-            self._arena = None
-        a = _find_arena(self.params)
-        if a is not None and a.is_cuda:
-            self._arena = a
-        return self._arena
+            if s.param.data_ptr() != self._arena.flat_p.data_ptr() + s.offset * 4:
+                self._arena = None
+        if self._arena is None:
+            self._arena = _find_arena(self.params)
+        a = self._arena
+        if a is not None and cuda_only and not a.is_cuda:
+            return None
+        return a
 
     def zero_grad(self, set_to_none: bool = False) -> None:
-        a = self._resolve_arena()
+        a = self._resolve_arena(cuda_only=False)
         if a is not None:
             a.zero_grad()
             return
@@ -66,7 +67,7 @@ class _FlatOptimizer:
                 if set_to_none:
                     p.grad = None
                 else:
-                    p.grad.detach_()
+                    p.grad = p.grad.detach()
                     p.grad.zero_()
 
     def fuse_clip_grad_norm(self, max_norm: float) -> torch.Tensor:

@@ -131,10 +131,10 @@ class DistributedDataParallel(nn.Module):
 
             h = torch.tensor([self.plan_hash & 0x7FFFFFFFFFFFFFFF], dtype=torch.int64,
                              device=self.arena.device if self._is_cuda else "cpu")
-            ref = h.clone()
-            tdist.broadcast(ref, 0)
-            if int(ref.item()) != int(h.item()):
-                raise RuntimeError("DDP: parameter shapes / bucket plan differ from rank 0")
+            parts = [torch.zeros_like(h) for _ in range(self.world)]
+            tdist.all_gather(parts, h)  # symmetric: every rank sees every hash, so all ranks raise together
+            if any(int(p.item()) != int(parts[0].item()) for p in parts):
+                raise RuntimeError("DDP: parameter shapes / bucket plan differ across ranks")
 
     def _sync_module_states(self) -> None:
         """Wrap-time broadcast of parameters and buffers from rank 0 (c10d: _sync_module_states)."""
@@ -150,7 +150,7 @@ class DistributedDataParallel(nn.Module):
 
             with torch.no_grad():
                 tdist.broadcast(self.arena.flat_p, 0)
-                tdist.broadcast(self.arena.flat_b, 0)
+            self._broadcast_buffers_torch()
 
     def _install_hooks(self) -> None:
         arena = self.arena
@@ -226,9 +226,27 @@ class DistributedDataParallel(nn.Module):
         if self._st.kind == "p2p":
             self._comm.broadcast(self._off["buffers"], _round_up(self.arena.buffer_bytes, 256), 0, nblocks=4)
         else:
-            import torch.distributed as tdist
+            self._broadcast_buffers_torch()
 
-            tdist.broadcast(self.arena.flat_b, 0)
+    def _broadcast_buffers_torch(self) -> None:
+        """gloo / NCCL-fallback groups: coalesce per dtype, broadcast from rank 0, scatter back."""
+        import torch.distributed as tdist
+
+        arena = self.arena
+        with torch.no_grad():
+            if arena.flat_b is not None:
+                tdist.broadcast(arena.flat_b, 0)
+                return
+            for dtype in (torch.float32, torch.int64):
+                group = [b for b in arena.buffer_list if b.dtype == dtype]
+                if not group:
+                    continue
+                flat = torch.cat([b.reshape(-1) for b in group])
+                tdist.broadcast(flat, 0)
+                o = 0
+                for b in group:
+                    b.copy_(flat[o: o + b.numel()].view(b.shape))
+                    o += b.numel()
 
     @contextlib.contextmanager
     def no_sync(self):

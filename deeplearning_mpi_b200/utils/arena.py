@@ -143,9 +143,17 @@ class ParamArena:
         nb_f32 = sum(_round_up(b.numel(), 4) for _, b in f32)
         nb_i64 = sum(b.numel() for _, b in i64)
         self.buffer_bytes = _round_up(nb_f32 * 4 + nb_i64 * 8, 256)
-        self.flat_b = alloc("buffers", max(self.buffer_bytes, 256))
-        fb32 = self.flat_b[: nb_f32 * 4].view(torch.float32)
-        fb64 = self.flat_b[nb_f32 * 4: nb_f32 * 4 + nb_i64 * 8].view(torch.int64)
+        self.buffer_list = [b for _, b in f32] + [b for _, b in i64]
+        if not self.is_cuda:
+            # Stock autograd saves BatchNorm buffers for backward and checks their version counters; views of one flat
+            # storage would share a single counter, so on the CPU (stock-module) path buffers stay separate tensors and
+            # DDP coalesces them on the fly.
+            self.flat_b = None
+            f32, i64 = [], []
+        else:
+            self.flat_b = alloc("buffers", max(self.buffer_bytes, 256))
+        fb32 = self.flat_b[: nb_f32 * 4].view(torch.float32) if self.flat_b is not None else None
+        fb64 = self.flat_b[nb_f32 * 4: nb_f32 * 4 + nb_i64 * 8].view(torch.int64) if self.flat_b is not None else None
         o = 0
         with torch.no_grad():
             for name, b in f32:

@@ -1,0 +1,165 @@
+"""UNet binary-segmentation data-parallel trainer — the capability of ref:pytorch/unet/train.py.
+
+Same CLI (--num_epochs --batch_size --learning_rate --random_seed --model_dir --model_filename --resume); UNet(out_classes=1),
+images from data/images + data/masks scaled x0.2, 80/20 split, DistributedSampler, Adam, BCEWithLogits, grad-clip 1.0,
+per-epoch loss + duration in logs/training_log_<timestamp>.log, Dice + checkpoint every 10 epochs on LOCAL_RANK 0 and
+a final evaluation / summary block.  Deliberate fixes: only rank 0 writes the log header (Q6); a
+non-finite loss skips the step on *all* ranks together (Q4); exceptions propagate with a non-zero exit code (Q5).
+
+    torchrun --nproc_per_node 8 --nnodes 1 --master_addr 127.0.0.1 --master_port 29500 examples/unet/train.py --synthetic
+"""
+import os
+import sys
+import time
+from datetime import datetime
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+import _bootstrap  # noqa: F401,E402
+
+import torch  # noqa: E402
+from torch.utils.data import DataLoader, random_split  # noqa: E402
+from tqdm import tqdm  # noqa: E402
+
+import deeplearning_mpi_b200.nn as dnn  # noqa: E402
+from deeplearning_mpi_b200 import optim  # noqa: E402
+from deeplearning_mpi_b200.models import UNet  # noqa: E402
+from deeplearning_mpi_b200.parallel import dist  # noqa: E402
+from deeplearning_mpi_b200.parallel.ddp import DistributedDataParallel  # noqa: E402
+from deeplearning_mpi_b200.parallel.sampler import DistributedSampler  # noqa: E402
+from deeplearning_mpi_b200.utils.checkpoint import load_checkpoint, save_checkpoint  # noqa: E402
+from deeplearning_mpi_b200.utils.data import CarvanaDataset, CudaPrefetcher, SyntheticSegmentation  # noqa: E402
+from deeplearning_mpi_b200.utils.metrics import evaluate_dice  # noqa: E402
+from deeplearning_mpi_b200.utils.runtime import (TrainConfig, create_log_file, log_to_file, set_random_seeds,  # noqa: E402
+                                                 system_information, torchrun_env)
+
+LOCAL_RANK, WORLD_SIZE, WORLD_RANK = torchrun_env()
+
+
+def build_model(cfg, device):
+    model = UNet(out_classes=1).to(device)
+    ddp_model = DistributedDataParallel(model, device_ids=[LOCAL_RANK], output_device=LOCAL_RANK)
+    if cfg.resume:
+        load_checkpoint(ddp_model, cfg.model_filepath, LOCAL_RANK)
+    return ddp_model
+
+
+def build_data_loaders(cfg, args):
+    if cfg.synthetic:
+        dataset = SyntheticSegmentation(args.synthetic_size, (args.image_size, args.image_size), seed=cfg.random_seed)
+        workers = 0
+    else:
+        dataset = CarvanaDataset(images_dir=os.path.join("data", "images"), mask_dir=os.path.join("data", "masks"), scale=0.2)
+        workers = int((os.cpu_count() or 2) // 2)
+    train_size = int(0.8 * len(dataset))
+    # the split uses the global torch RNG, identical on every rank thanks to the shared seed
+    train_dataset, test_dataset = random_split(dataset, [train_size, len(dataset) - train_size])
+    loader_args = dict(batch_size=cfg.batch_size, num_workers=workers, pin_memory=torch.cuda.is_available())
+    train_loader = DataLoader(train_dataset, sampler=DistributedSampler(train_dataset), **loader_args)
+    test_loader = DataLoader(test_dataset, shuffle=False, **loader_args)
+    return train_loader, test_loader
+
+
+def _all_finite(loss: torch.Tensor) -> bool:
+    """Collective decision so that every rank skips (or keeps) the step together."""
+    flag = torch.isfinite(loss.detach()).float().reshape(1)
+    if WORLD_SIZE > 1:
+        dist.all_reduce(flag)
+        return float(flag.item()) == WORLD_SIZE
+    return bool(flag.item())
+
+
+def train_model(model, train_loader, test_loader, device, cfg, log_file):
+    if LOCAL_RANK == 0:
+        print(f"Logging training progress to: {log_file}")
+        log_to_file(log_file, f"Started training at {datetime.now()}")
+    optimizer = optim.Adam(model.parameters(), lr=cfg.learning_rate)
+    criterion = dnn.BCEWithLogitsLoss()
+    on_gpu = device.type == "cuda"
+    for epoch in range(cfg.num_epochs):
+        start_time = time.time()
+        model.train()
+        epoch_loss, num_batches = 0.0, 0
+        batches = CudaPrefetcher(train_loader, device) if on_gpu else train_loader
+        loop = tqdm(batches, desc=f"Epoch {epoch + 1}/{cfg.num_epochs}", unit="batch", disable=LOCAL_RANK != 0)
+        for step, batch in enumerate(loop):
+            if cfg.steps_per_epoch and step >= cfg.steps_per_epoch:
+                break
+            images = batch["image"].to(device, dtype=torch.float32)
+            true_masks = batch["mask"].to(device, dtype=torch.float32)
+            predicted_masks = model(images)
+            if predicted_masks.dim() == 4:
+                predicted_masks = predicted_masks.squeeze(1)
+            loss = criterion(predicted_masks, true_masks)
+            if not _all_finite(loss):
+                print(f"Warning: Invalid loss detected: {loss.item()}")
+                optimizer.zero_grad()
+                continue
+            optimizer.zero_grad()
+            loss.backward()
+            dnn.clip_grad_norm_(model.parameters(), max_norm=1.0)
+            optimizer.step()
+            value = loss.item()
+            epoch_loss += value
+            num_batches += 1
+            loop.set_postfix(loss=value)
+        avg_loss = epoch_loss / max(num_batches, 1)
+        print(f"Epoch {epoch + 1} finished with loss: {avg_loss:.4f}")
+        duration = time.time() - start_time
+        if LOCAL_RANK == 0:
+            log_to_file(log_file, f"Epoch {epoch + 1} | Loss: {avg_loss:.4f} | Duration: {duration:.2f}s")
+        if (epoch + 1) % 10 == 0 and LOCAL_RANK == 0:
+            dice = evaluate_dice(model, device, test_loader)
+            save_checkpoint(model, cfg.model_filepath)
+            print("-" * 75)
+            print(f"Epoch {epoch + 1} Dice Score: {dice:.4f}")
+            print("-" * 75)
+            log_to_file(log_file, f"Epoch {epoch + 1} | Dice Score: {dice:.4f}")
+    if LOCAL_RANK == 0:
+        print("\n" + "=" * 80 + "\nTRAINING COMPLETED - FINAL EVALUATION\n" + "=" * 80)
+        final_dice = evaluate_dice(model, device, test_loader)
+        save_checkpoint(model, cfg.model_filepath)
+        print(f"FINAL DICE COEFFICIENT: {final_dice:.4f}\n" + "=" * 80 + "\n")
+        for line in ("=" * 80, "FINAL TRAINING RESULTS", "=" * 80,
+                     f"TRAINING COMPLETED | Final Dice Coefficient: {final_dice:.4f} | Training finished at: {datetime.now()}",
+                     f"Total training epochs: {cfg.num_epochs}", f"Final learning rate: {cfg.learning_rate}",
+                     f"Model saved to: {cfg.model_filepath}", "=" * 80):
+            log_to_file(log_file, line)
+
+
+def initialize_processes(cfg, args, log_file):
+    dist.init_process_group(cfg.backend)
+    try:
+        train_loader, test_loader = build_data_loaders(cfg, args)
+        print("Data loaders built.")
+        device = torch.device(f"cuda:{LOCAL_RANK}") if cfg.backend != "gloo" else torch.device("cpu")
+        model = build_model(cfg, device)
+        print("Model built. Starting training.")
+        train_model(model, train_loader, test_loader, device, cfg, log_file)
+    finally:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    defaults = TrainConfig(num_epochs=100, batch_size=16, learning_rate=0.0001, random_seed=42, model_dir="saved_models",
+                           model_filename="model.pth")
+    parser = TrainConfig.parser(defaults)
+    parser.add_argument("--image_size", type=int, default=256, help="side of the synthetic images (multiple of 16)")
+    parser.add_argument("--synthetic_size", type=int, default=64)
+    ns = parser.parse_args()
+    cfg = TrainConfig.from_args(ns)
+    if cfg.backend != "gloo" and not torch.cuda.is_available():
+        raise SystemError("You should have a GPU available to run this script (or pass --backend gloo).")
+    if not cfg.synthetic and not os.path.exists(os.path.join(os.getcwd(), "data")):
+        raise OSError("The 'data' directory does not exist. Please create it before running the script.")
+    if not os.path.exists(os.path.join(os.getcwd(), "logs")):
+        raise OSError("The 'logs' directory does not exist. Please create it before running the script.")
+    if not os.path.exists(cfg.model_dir):
+        raise OSError("The model directory does not exist. Please create it before running the script.")
+    log_file = create_log_file()
+    if WORLD_RANK == 0:
+        for line in (f"Batch size: {cfg.batch_size}", f"Number of workers: {os.cpu_count()}",
+                     f"Learning rate: {cfg.learning_rate}", f"Number of epochs: {cfg.num_epochs}",
+                     system_information(LOCAL_RANK, WORLD_SIZE)):
+            log_to_file(log_file, line)
+    set_random_seeds(cfg.random_seed)
+    initialize_processes(cfg, ns, log_file)

@@ -1,0 +1,216 @@
+"""CPU-only unit tests: store, bucket planner, reducer state machine, sampler parity, state_dict parity, conv lowering
+helpers.  (No GPU needed; the native host library is built by build.py / __graft_entry__.build().)"""
+import ctypes as C
+import threading
+
+import pytest
+import torch
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _built():
+    import build
+
+    build.build()
+
+
+def test_tcp_store_set_get_add_wait():
+    from deeplearning_mpi_b200.parallel.store import TCPStore
+
+    master = TCPStore("127.0.0.1", 0, True, timeout_s=10)
+    client = TCPStore("127.0.0.1", master.port, False, timeout_s=10)
+    master.set("k", b"hello")
+    assert client.get("k") == b"hello"
+    assert client.add("ctr", 3) == 3 and master.add("ctr", 4) == 7
+    assert not client.check("missing") and client.check("k")
+    with pytest.raises(TimeoutError):
+        client.get("missing", timeout_s=0.2)
+    # a blocked get is released by a later set from another client
+    got = {}
+    t = threading.Thread(target=lambda: got.setdefault("v", client.get("late", timeout_s=5)))
+    t.start()
+    master.set("late", b"x" * 100000)
+    t.join(5)
+    assert got["v"] == b"x" * 100000
+    # barrier + all_gather across two "ranks"
+    res = [None, None]
+
+    def rank(r, st):
+        res[r] = st.all_gather("g", r, 2, f"r{r}".encode())
+        st.barrier("b", r, 2)
+
+    ts = [threading.Thread(target=rank, args=(0, master)), threading.Thread(target=rank, args=(1, client))]
+    [x.start() for x in ts]
+    [x.join(10) for x in ts]
+    assert res[0] == res[1] == [b"r0", b"r1"]
+    client.close()
+    master.close()
+
+
+def test_bucket_planner_matches_torch():
+    import torch.distributed as tdist
+    import torchvision
+
+    from deeplearning_mpi_b200 import _native as N
+
+    model = torchvision.models.resnet18(weights=None)
+    params = list(reversed(list(model.parameters())))
+    sizes = [p.numel() * 4 for p in params]
+    arr = (C.c_int64 * len(sizes))(*sizes)
+    out = (C.c_int * len(sizes))()
+    nb = N.host().dmpi_plan_buckets(arr, len(sizes), 1 << 20, 25 << 20, out)
+    ref, _ = tdist._compute_bucket_assignment_by_size(params, [1 << 20, 25 << 20])
+    mine = [[i for i, b in enumerate(out) if b == k] for k in range(nb)]
+    assert mine == [list(b) for b in ref]
+
+
+def test_reducer_state_machine_in_order_launch():
+    from deeplearning_mpi_b200 import _native as N
+
+    host = N.host()
+    bucket_of = (C.c_int * 6)(0, 0, 1, 1, 1, 2)
+    r = host.dmpi_reducer_create(6, bucket_of, 3)
+    out = (C.c_int * 3)()
+    host.dmpi_reducer_reset(r)
+    # bucket 2 completes first but must wait for buckets 0 and 1
+    assert host.dmpi_reducer_mark_ready(r, 5, out, 3) == 0
+    assert host.dmpi_reducer_mark_ready(r, 2, out, 3) == 0
+    assert host.dmpi_reducer_mark_ready(r, 0, out, 3) == 0
+    assert host.dmpi_reducer_mark_ready(r, 1, out, 3) == 1 and out[0] == 0
+    assert host.dmpi_reducer_mark_ready(r, 3, out, 3) == 0
+    assert host.dmpi_reducer_pending(r) == 2
+    assert host.dmpi_reducer_mark_ready(r, 4, out, 3) == 2 and list(out)[:2] == [1, 2]
+    assert host.dmpi_reducer_pending(r) == 0
+    assert host.dmpi_reducer_mark_ready(r, 4, out, 3) == -1  # double mark
+    order = (C.c_int * 6)()
+    assert host.dmpi_reducer_ready_order(r, order, 6) == 6 and list(order) == [5, 2, 0, 1, 3, 4]
+    host.dmpi_reducer_reset(r)
+    assert host.dmpi_reducer_pending(r) == 3
+    host.dmpi_reducer_destroy(r)
+
+
+@pytest.mark.parametrize("n,world,drop_last,shuffle", [(103, 4, False, True), (103, 4, True, True), (10, 3, False, False),
+                                                       (3, 8, False, True), (50000, 8, False, True)])
+def test_sampler_matches_torch(n, world, drop_last, shuffle):
+    from torch.utils.data.distributed import DistributedSampler as TorchSampler
+
+    from deeplearning_mpi_b200.parallel.sampler import DistributedSampler
+
+    ds = list(range(n))
+    for rank in range(world):
+        for epoch in (0, 3):
+            a = DistributedSampler(ds, num_replicas=world, rank=rank, shuffle=shuffle, seed=7, drop_last=drop_last)
+            b = TorchSampler(ds, num_replicas=world, rank=rank, shuffle=shuffle, seed=7, drop_last=drop_last)
+            a.set_epoch(epoch)
+            b.set_epoch(epoch)
+            assert list(a) == list(b) and len(a) == len(b)
+
+
+def test_state_dict_parity_with_reference_models():
+    import os
+    import sys
+
+    import torchvision
+
+    from deeplearning_mpi_b200.models import UNet, resnet18, resnet50
+
+    t = torchvision.models.resnet18(weights=None)
+    t.fc = torch.nn.Linear(512, 10)
+    m = resnet18(num_classes=10)
+    assert list(m.state_dict().keys()) == list(t.state_dict().keys()) and len(m.state_dict()) == 122
+    assert [tuple(v.shape) for v in m.state_dict().values()] == [tuple(v.shape) for v in t.state_dict().values()]
+    m.load_state_dict(t.state_dict())
+    x = torch.randn(2, 3, 32, 32)
+    m.eval(), t.eval()
+    assert torch.allclose(m(x), t(x), atol=1e-5)
+    assert list(resnet50().state_dict().keys()) == list(torchvision.models.resnet50(weights=None).state_dict().keys())
+    ref_dir = "/root/reference/pytorch/unet"
+    if os.path.isdir(ref_dir):
+        sys.path.insert(0, ref_dir)
+        from model import UNet as RefUNet
+
+        r = RefUNet(out_classes=1)
+        u = UNet(out_classes=1)
+        assert list(u.state_dict().keys()) == list(r.state_dict().keys()) and len(u.state_dict()) == 136
+        u.load_state_dict(r.state_dict())
+        u.eval(), r.eval()
+        xi = torch.randn(1, 3, 32, 32)
+        assert torch.allclose(u(xi), r(xi), atol=1e-5)
+    with pytest.raises(ValueError):
+        UNet(up_sample_mode="nearest")
+    assert UNet(out_classes=2, up_sample_mode="bilinear")(torch.randn(1, 3, 32, 32)).shape == (1, 2, 32, 32)
+
+
+def test_cpu_arena_and_optimizers_match_torch():
+    """On CPU the arena re-homes params/grads and the optimizers follow torch.optim step for step."""
+    import copy
+
+    import deeplearning_mpi_b200.nn as dnn
+    from deeplearning_mpi_b200 import optim
+    from deeplearning_mpi_b200.models import resnet18
+    from deeplearning_mpi_b200.utils.arena import ensure_arena
+
+    torch.manual_seed(0)
+    ours = resnet18(num_classes=10)
+    ref = copy.deepcopy(ours)
+    # eval-mode BatchNorm keeps the comparison well conditioned (training-mode BN with 4 samples amplifies the 1e-7
+    # differences between channels_last and contiguous CPU conv kernels); gradients still flow to every parameter
+    ours.eval()
+    ref.eval()
+    arena = ensure_arena(ours)
+    assert arena.flat_p.numel() >= sum(p.numel() for p in ours.parameters())
+    o1 = optim.SGD(ours.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-5)
+    o2 = torch.optim.SGD(ref.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-5)
+    x, y = torch.randn(4, 3, 32, 32), torch.randint(0, 10, (4,))
+    for _ in range(3):
+        o1.zero_grad()
+        o2.zero_grad()
+        dnn.cross_entropy(ours(x), y).backward()
+        torch.nn.functional.cross_entropy(ref(x), y).backward()
+        o1.step()
+        o2.step()
+    for (n, a), (_, b) in zip(ours.named_parameters(), ref.named_parameters()):
+        assert torch.allclose(a, b, atol=1e-4, rtol=1e-3), n
+    # Adam + clip
+    a1 = optim.Adam(ours.parameters(), lr=1e-3)
+    a2 = torch.optim.Adam(ref.parameters(), lr=1e-3)
+    for _ in range(2):
+        a1.zero_grad()
+        a2.zero_grad()
+        dnn.cross_entropy(ours(x), y).backward()
+        torch.nn.functional.cross_entropy(ref(x), y).backward()
+        n1 = dnn.clip_grad_norm_(ours.parameters(), 1.0)
+        n2 = torch.nn.utils.clip_grad_norm_(ref.parameters(), 1.0)
+        assert torch.allclose(n1, n2, rtol=1e-4)
+        a1.step()
+        a2.step()
+    for (n, a), (_, b) in zip(ours.named_parameters(), ref.named_parameters()):
+        assert torch.allclose(a, b, atol=2e-3, rtol=1e-2), n
+
+
+def test_choose_box_and_dice_and_dataset(tmp_path):
+    import numpy as np
+    from PIL import Image
+
+    from deeplearning_mpi_b200.ops.conv import choose_box, smallc_geometry
+    from deeplearning_mpi_b200.utils.data import CarvanaDataset
+    from deeplearning_mpi_b200.utils.metrics import dice_scores
+
+    for (w, h, n) in [(56, 56, 256), (28, 28, 256), (7, 7, 256), (512, 512, 4), (14, 14, 3)]:
+        bw, bh, bn = choose_box(w, h, n)
+        assert 1 <= bw * bh * bn <= 128
+        ew, eh, en = choose_box(w, h, n, rows=64, exact=True)
+        assert ew * eh * en == 64
+    assert smallc_geometry(224, 224, 7, 7, 2, 3) == (112, 112, 230, 230)
+    d = dice_scores(torch.tensor([[[1, 0], [0, 0]], [[0, 0], [0, 0]]]), torch.tensor([[[1, 1], [0, 0]], [[0, 0], [0, 0]]]))
+    assert abs(d[0] - 2 / 3) < 1e-6 and d[1] == 1.0
+    (tmp_path / "images").mkdir()
+    (tmp_path / "masks").mkdir()
+    rng = np.random.default_rng(0)
+    for i in range(3):
+        Image.fromarray(rng.integers(0, 255, (20, 30, 3), dtype=np.uint8)).save(tmp_path / "images" / f"im{i}.png")
+        Image.fromarray(((rng.random((20, 30)) > 0.5) * 255).astype(np.uint8)).save(tmp_path / "masks" / f"im{i}.png")
+    ds = CarvanaDataset(str(tmp_path / "images"), str(tmp_path / "masks"), scale=0.5)
+    item = ds[0]
+    assert item["image"].shape == (3, 10, 15) and item["mask"].shape == (10, 15)
+    assert item["image"].max() <= 1.0 and set(item["mask"].unique().tolist()) <= {0.0, 1.0}
