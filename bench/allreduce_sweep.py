@@ -1,0 +1,74 @@
+"""All-reduce sweep 1 KB - 1 GB (BASELINE.json config 5): this framework's NVLink P2P kernels vs NCCL, same buffers.
+Launch with torchrun, one rank per GPU.  Device-timed (CUDA events), max over ranks, bus bandwidth = 2(W-1)/W * S / t.
+Writes gpurun_out/allreduce_sweep_w<W>.json on rank 0."""
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import torch.distributed as tdist
+
+from deeplearning_mpi_b200.parallel import dist
+
+dist.init_process_group("nccl")
+rank, world = dist.get_rank(), dist.get_world_size()
+dev = torch.device("cuda", int(os.environ["LOCAL_RANK"]))
+tdist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+st = dist._require()
+max_bytes = int(os.environ.get("SWEEP_MAX_BYTES", str(1 << 30)))
+comm = st.new_comm(max_bytes)
+stage = comm.tensor(0, max_bytes).view(torch.float32)
+nccl_buf = torch.empty(max_bytes // 4, device=dev)
+flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+
+def timed(fn, iters):
+    ts = []
+    for _ in range(iters):
+        flush.zero_()
+        tdist.barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b))
+    t = torch.tensor([sorted(ts)[len(ts) // 2]], device=dev)
+    tdist.all_reduce(t, op=tdist.ReduceOp.MAX)
+    return t.item() * 1e-3
+
+
+rows = []
+sizes = [1 << k for k in range(10, 31) if (1 << k) <= max_bytes]
+sizes += [int(9.0 * 2**20), int(25.3 * 2**20), int(42.65 * 2**20), int(97.49 * 2**20), int(141.0 * 2**20)]
+for nbytes in sorted(set(s - s % 16 for s in sizes if s <= max_bytes)):
+    iters = 20 if nbytes <= (8 << 20) else 6
+    res = {"bytes": nbytes}
+    for algo in ("oneshot", "oneshot_bf16", "twoshot"):
+        if algo != "twoshot" and nbytes > comm.slot_bytes:
+            continue
+        for nb in (16, 32, 64):
+            for _ in range(2):
+                comm.allreduce(0, nbytes, 1.0 / world, algo=algo, nblocks=nb)
+            t = timed(lambda: comm.allreduce(0, nbytes, 1.0 / world, algo=algo, nblocks=nb), iters)
+            res[f"{algo}_b{nb}_us"] = t * 1e6
+    view = nccl_buf[: nbytes // 4]
+    for _ in range(2):
+        tdist.all_reduce(view)
+    t = timed(lambda: tdist.all_reduce(view), iters)
+    res["nccl_us"] = t * 1e6
+    best = min(v for k, v in res.items() if k.endswith("_us") and not k.startswith("nccl"))
+    res["ours_best_us"] = best
+    res["ours_busbw_GBs"] = 2 * (world - 1) / world * nbytes / (best * 1e-6) / 1e9
+    res["nccl_busbw_GBs"] = 2 * (world - 1) / world * nbytes / (res["nccl_us"] * 1e-6) / 1e9
+    rows.append(res)
+    if rank == 0:
+        print(f"{nbytes:>11d} B  ours {best:9.1f} us ({res['ours_busbw_GBs']:7.1f} GB/s)   nccl {res['nccl_us']:9.1f} us "
+              f"({res['nccl_busbw_GBs']:7.1f} GB/s)", flush=True)
+if rank == 0:
+    os.makedirs("gpurun_out", exist_ok=True)
+    json.dump({"world": world, "rows": rows}, open(f"gpurun_out/allreduce_sweep_w{world}.json", "w"), indent=1)
+tdist.barrier()
+tdist.destroy_process_group()
+dist.destroy_process_group()

@@ -261,14 +261,18 @@ class DistributedDataParallel(nn.Module):
         if torch.is_grad_enabled() and self.training:
             self._sync_buffers()
             if self.require_backward_grad_sync:
-                N.host().dmpi_reducer_reset(self._reducer)
-                if self._cuda_red is not None:
-                    N.cuda().dmpi_reducer_cuda_begin(self._cuda_red, N.stream_ptr())
-                self._armed = True
-                self._marked = bytearray(len(self.arena.slots))
+                self._arm()
             else:
                 self._armed = False
         return self.module(*inputs, **kwargs)
+
+    def _arm(self) -> None:
+        """Prepare the reducer for one synchronising backward pass (c10d: prepare_for_backward)."""
+        N.host().dmpi_reducer_reset(self._reducer)
+        if self._cuda_red is not None:
+            N.cuda().dmpi_reducer_cuda_begin(self._cuda_red, N.stream_ptr())
+        self._armed = True
+        self._marked = bytearray(len(self.arena.slots))
 
     def __del__(self):  # pragma: no cover
         try:
