@@ -324,9 +324,16 @@ def main():
         sampler.start()
     l0 = arm["launches"]()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    profile_last = os.environ.get("DMPI_PROFILE_STEP") == "1"  # ncu --profile-from-start off captures one step
     e0.record()
-    for _ in range(args.steps):
+    for i in range(args.steps):
+        if profile_last and i == args.steps - 1:
+            torch.cuda.synchronize()
+            torch.cuda.profiler.start()
         loss = step(x_dev, y_dev)
+    if profile_last:
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
     e1.record()
     torch.cuda.synchronize()
     arm["barrier"]()

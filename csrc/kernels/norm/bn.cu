@@ -70,30 +70,50 @@ __global__ void __launch_bounds__(kBnThreads) bn_fwd_kernel(const BnFwdArgs a) {
   if (blockIdx.x == 0 && threadIdx.x == 0 && a.training && a.num_batches_tracked) *a.num_batches_tracked += 1;
   __syncthreads();
 
-  const int vecC = a.C >> 3;  // 8 channels (16 bytes) per thread
-  const long long total = a.M * vecC;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const long long row = i / vecC;
-    const int c0 = static_cast<int>(i - row * vecC) << 3;
-    const uint4 v = *reinterpret_cast<const uint4*>(a.y + row * a.ldy + c0);
-    uint4 r = make_uint4(0, 0, 0, 0);
-    if (a.res) r = *reinterpret_cast<const uint4*>(a.res + row * a.ldr + c0);
-    const uint32_t vi[4] = {v.x, v.y, v.z, v.w};
-    const uint32_t ri[4] = {r.x, r.y, r.z, r.w};
-    uint32_t oi[4];
+  // Thread (tx, ty): tx owns 8 consecutive channels (16 bytes) for the whole kernel -> scale/shift in registers,
+  // ty strides the rows; two rows per iteration with all loads issued up front.
+  const int vecC = a.C >> 3;
+  const int tx = threadIdx.x % vecC;
+  const int ty = threadIdx.x / vecC;
+  const int rows_per_block = blockDim.x / vecC;
+  if (ty >= rows_per_block) return;
+  const int c0 = tx << 3;
+  float sc[8], sh[8];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int c = c0 + 2 * j;
-      float lo = fmaf(bf16lo(vi[j]), scale[c], shift[c]) + bf16lo(ri[j]);
-      float hi = fmaf(bf16hi(vi[j]), scale[c + 1], shift[c + 1]) + bf16hi(ri[j]);
-      if (a.relu) {
-        lo = fmaxf(lo, 0.f);
-        hi = fmaxf(hi, 0.f);
-      }
-      oi[j] = pack_bf16x2(lo, hi);
+  for (int j = 0; j < 8; ++j) {
+    sc[j] = scale[c0 + j];
+    sh[j] = shift[c0 + j];
+  }
+  const long long stride = static_cast<long long>(gridDim.x) * rows_per_block;
+  for (long long row = blockIdx.x * static_cast<long long>(rows_per_block) + ty; row < a.M; row += 2 * stride) {
+    const long long row2 = row + stride;
+    const bool has2 = row2 < a.M;
+    uint4 v[2], r[2];
+    r[0] = r[1] = make_uint4(0, 0, 0, 0);
+    v[0] = *reinterpret_cast<const uint4*>(a.y + row * a.ldy + c0);
+    if (a.res) r[0] = *reinterpret_cast<const uint4*>(a.res + row * a.ldr + c0);
+    if (has2) {
+      v[1] = *reinterpret_cast<const uint4*>(a.y + row2 * a.ldy + c0);
+      if (a.res) r[1] = *reinterpret_cast<const uint4*>(a.res + row2 * a.ldr + c0);
     }
-    *reinterpret_cast<uint4*>(a.out + row * a.ldo + c0) = make_uint4(oi[0], oi[1], oi[2], oi[3]);
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (u == 1 && !has2) break;
+      const uint32_t vi[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+      const uint32_t ri[4] = {r[u].x, r[u].y, r[u].z, r[u].w};
+      uint32_t oi[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float lo = fmaf(bf16lo(vi[j]), sc[2 * j], sh[2 * j]) + bf16lo(ri[j]);
+        float hi = fmaf(bf16hi(vi[j]), sc[2 * j + 1], sh[2 * j + 1]) + bf16hi(ri[j]);
+        if (a.relu) {
+          lo = fmaxf(lo, 0.f);
+          hi = fmaxf(hi, 0.f);
+        }
+        oi[j] = pack_bf16x2(lo, hi);
+      }
+      *reinterpret_cast<uint4*>(a.out + (u == 0 ? row : row2) * a.ldo + c0) = make_uint4(oi[0], oi[1], oi[2], oi[3]);
+    }
   }
 }
 
@@ -172,51 +192,64 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_reduce_kernel(const BnBwdAr
 
 // Pass 2: dy = gamma * invstd * (dz - mean(dz) - xhat * mean(dz * xhat)); block 0 also emits dgamma/dbeta.
 __global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_kernel(const BnBwdArgs a) {
-  extern __shared__ float sm[];  // k1[C] = gamma*invstd, k2[C] = mean(dz), k3[C] = mean(dz*xhat), mean[C], istd[C]
-  float* k1 = sm;
-  float* k2 = sm + a.C;
-  float* k3 = sm + 2 * a.C;
-  float* mu = sm + 3 * a.C;
-  float* is = sm + 4 * a.C;
+  // Thread (tx, ty): tx owns 8 consecutive channels for the whole kernel, so the per-channel constants live in
+  // registers and the streaming loop is pure load / FMA / store:  dy = A*dz + B*y + D  with
+  //   A = gamma*invstd,  B = -A*invstd*mean(dz*xhat),  D = -A*mean(dz) - B*mean.
+  const int vecC = a.C >> 3;
+  const int tx = threadIdx.x % vecC;
+  const int ty = threadIdx.x / vecC;
+  const int rows_per_block = blockDim.x / vecC;
+  const int c0 = tx << 3;
   const float invM = 1.f / static_cast<float>(a.M);
-  for (int c = threadIdx.x; c < a.C; c += blockDim.x) {
+  float kA[8], kB[8], kD[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int c = c0 + j;
     const float sdz = a.acc[c], sdzx = a.acc[a.C + c];
     const float g = a.gamma ? a.gamma[c] : 1.f;
-    k1[c] = g * a.invstd[c];
-    k2[c] = sdz * invM;
-    k3[c] = sdzx * invM;
-    mu[c] = a.mean[c];
-    is[c] = a.invstd[c];
-    if (blockIdx.x == 0) {
+    const float istd = a.invstd[c], mean = a.mean[c];
+    kA[j] = g * istd;
+    kB[j] = -kA[j] * istd * (sdzx * invM);
+    kD[j] = -kA[j] * (sdz * invM) - kB[j] * mean;
+    if (blockIdx.x == 0 && ty == 0) {
       if (a.dgamma) a.dgamma[c] += sdzx;
       if (a.dbeta) a.dbeta[c] += sdz;
     }
   }
-  __syncthreads();
-  const int vecC = a.C >> 3;
-  const long long total = a.M * vecC;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const long long row = i / vecC;
-    const int c0 = static_cast<int>(i - row * vecC) << 3;
-    const uint4 g = *reinterpret_cast<const uint4*>(a.dout + row * a.ld_dout + c0);
-    const uint4 yv = *reinterpret_cast<const uint4*>(a.y + row * a.ldy + c0);
-    uint4 av = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);
-    if (a.act) av = *reinterpret_cast<const uint4*>(a.act + row * a.ld_act + c0);
-    const uint32_t gi[4] = {g.x, g.y, g.z, g.w}, yi[4] = {yv.x, yv.y, yv.z, yv.w}, ai[4] = {av.x, av.y, av.z, av.w};
-    uint32_t oi[4], ri[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int c = c0 + 2 * j;
-      const float d0 = bf16lo(ai[j]) > 0.f ? bf16lo(gi[j]) : 0.f;
-      const float d1 = bf16hi(ai[j]) > 0.f ? bf16hi(gi[j]) : 0.f;
-      const float x0 = (bf16lo(yi[j]) - mu[c]) * is[c];
-      const float x1 = (bf16hi(yi[j]) - mu[c + 1]) * is[c + 1];
-      oi[j] = pack_bf16x2(k1[c] * (d0 - k2[c] - x0 * k3[c]), k1[c + 1] * (d1 - k2[c + 1] - x1 * k3[c + 1]));
-      ri[j] = pack_bf16x2(d0, d1);
+  if (ty >= rows_per_block) return;
+  const long long stride = static_cast<long long>(gridDim.x) * rows_per_block;
+  for (long long row = blockIdx.x * static_cast<long long>(rows_per_block) + ty; row < a.M; row += 2 * stride) {
+    // two rows per iteration: all loads are issued before the first use
+    const long long row2 = row + stride;
+    const bool has2 = row2 < a.M;
+    uint4 g[2], yv[2], av[2];
+    g[0] = *reinterpret_cast<const uint4*>(a.dout + row * a.ld_dout + c0);
+    yv[0] = *reinterpret_cast<const uint4*>(a.y + row * a.ldy + c0);
+    av[0] = av[1] = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);
+    if (a.act) av[0] = *reinterpret_cast<const uint4*>(a.act + row * a.ld_act + c0);
+    if (has2) {
+      g[1] = *reinterpret_cast<const uint4*>(a.dout + row2 * a.ld_dout + c0);
+      yv[1] = *reinterpret_cast<const uint4*>(a.y + row2 * a.ldy + c0);
+      if (a.act) av[1] = *reinterpret_cast<const uint4*>(a.act + row2 * a.ld_act + c0);
     }
-    *reinterpret_cast<uint4*>(a.dy + row * a.ld_dy + c0) = make_uint4(oi[0], oi[1], oi[2], oi[3]);
-    if (a.dres) *reinterpret_cast<uint4*>(a.dres + row * a.ld_dres + c0) = make_uint4(ri[0], ri[1], ri[2], ri[3]);
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (u == 1 && !has2) break;
+      const long long r = u == 0 ? row : row2;
+      const uint32_t gi[4] = {g[u].x, g[u].y, g[u].z, g[u].w}, yi[4] = {yv[u].x, yv[u].y, yv[u].z, yv[u].w},
+                     ai[4] = {av[u].x, av[u].y, av[u].z, av[u].w};
+      uint32_t oi[4], ri[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float d0 = bf16lo(ai[j]) > 0.f ? bf16lo(gi[j]) : 0.f;
+        const float d1 = bf16hi(ai[j]) > 0.f ? bf16hi(gi[j]) : 0.f;
+        oi[j] = pack_bf16x2(fmaf(kA[2 * j], d0, fmaf(kB[2 * j], bf16lo(yi[j]), kD[2 * j])),
+                            fmaf(kA[2 * j + 1], d1, fmaf(kB[2 * j + 1], bf16hi(yi[j]), kD[2 * j + 1])));
+        ri[j] = pack_bf16x2(d0, d1);
+      }
+      *reinterpret_cast<uint4*>(a.dy + r * a.ld_dy + c0) = make_uint4(oi[0], oi[1], oi[2], oi[3]);
+      if (a.dres) *reinterpret_cast<uint4*>(a.dres + r * a.ld_dres + c0) = make_uint4(ri[0], ri[1], ri[2], ri[3]);
+    }
   }
 }
 
@@ -266,6 +299,15 @@ __global__ void __launch_bounds__(kBnThreads) bn_stats_kernel(const __nv_bfloat1
   }
 }
 
+// Row-streaming kernels: each block handles rows_per_block rows per step and two steps per loop iteration; enough
+// blocks to fill the machine (8 resident 256-thread blocks on each of the 148 SMs) but no more than there is work.
+static int stream_grid(long long rows, int rows_per_block) {
+  long long blocks = (rows + 2LL * rows_per_block - 1) / (2LL * rows_per_block);
+  const long long cap = 148LL * 8;
+  if (blocks > cap) blocks = cap;
+  return blocks < 1 ? 1 : static_cast<int>(blocks);
+}
+
 static int grid_for(long long work_items, int threads) {
   long long blocks = (work_items + threads - 1) / threads;
   const long long cap = 148LL * 8;
@@ -283,7 +325,7 @@ extern "C" int dmpi_bn_forward(const void* y, const void* res, void* out, long l
                                const float* beta, float* save_mean, float* save_invstd, float* running_mean,
                                float* running_var, long long* num_batches_tracked, float eps, float momentum,
                                int training, int relu, void* stream) {
-  if (C % 8 != 0 || C > kMaxC * 4) return -1;
+  if (C % 8 != 0 || C > kMaxC) return -1;
   BnFwdArgs a;
   a.y = static_cast<const __nv_bfloat16*>(y);
   a.res = static_cast<const __nv_bfloat16*>(res);
@@ -306,8 +348,11 @@ extern "C" int dmpi_bn_forward(const void* y, const void* res, void* out, long l
   a.momentum = momentum;
   a.training = training;
   a.relu = relu;
-  const int grid = grid_for(M * (C / 8), kBnThreads);
-  bn_fwd_kernel<<<grid, kBnThreads, 2 * C * sizeof(float), static_cast<cudaStream_t>(stream)>>>(a);
+  const int vecC = C / 8;
+  if (vecC > kBnThreads) return -3;
+  const int threads = (kBnThreads / vecC) * vecC;  // a whole number of rows per block
+  const int grid = stream_grid(M, threads / vecC);
+  bn_fwd_kernel<<<grid, threads, 2 * C * sizeof(float), static_cast<cudaStream_t>(stream)>>>(a);
   return cudaGetLastError() == cudaSuccess ? 0 : -2;
 }
 
@@ -347,8 +392,7 @@ extern "C" int dmpi_bn_backward(const void* dout, const void* y, const void* act
   if (blocks > 148 * 8) blocks = 148 * 8;
   if (blocks < 1) blocks = 1;
   bn_bwd_reduce_kernel<<<static_cast<int>(blocks), threads, threads * 16 * sizeof(float), s>>>(a);
-  const int grid = grid_for(M * vecC, kBnThreads);
-  bn_bwd_apply_kernel<<<grid, kBnThreads, 5 * C * sizeof(float), s>>>(a);
+  bn_bwd_apply_kernel<<<stream_grid(M, rows_per_block), threads, 0, s>>>(a);
   return cudaGetLastError() == cudaSuccess ? 0 : -2;
 }
 
