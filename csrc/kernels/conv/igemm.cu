@@ -37,10 +37,12 @@ constexpr int kABytes = kTileM * kBlockK * 2;
 
 template <int BN>
 struct IgemmCfg {
-  static constexpr int kStages = BN == 256 ? 3 : (BN == 128 ? 4 : 6);
+  // Pipeline depth is what hides the ~1000-cycle L2/HBM latency of the TMA loads: one stage is only 128 (BN=64),
+  // 256 (BN=128) or 512 (BN=256) tensor-core cycles of work, so the narrow tiles need the most stages.
+  static constexpr int kStages = BN == 256 ? 3 : (BN == 128 ? 6 : 8);
   static constexpr int kBBytes = BN * kBlockK * 2;
   static constexpr int kOutBytes = kTileM * BN * 2;
-  static constexpr int kOutBufs = BN == 256 ? 1 : 2;  // staged output tiles (double buffered when they fit)
+  static constexpr int kOutBufs = BN == 64 ? 2 : 1;  // staged output tiles (double buffered when they fit)
   static constexpr int kSmemBytes =
       kStages * (kABytes + kBBytes) + kOutBufs * kOutBytes + 1024 /*align slack*/ + 256 /*barriers*/;
   static constexpr int kTmemCols = 2 * BN;

@@ -3,9 +3,11 @@
 // The reduction runs over pixels, which is the *strided* axis of both NHWC operands, so both UMMA
 // operands are MN-major: a TMA box of 64 pixels x 64 channels lands in shared memory as 64 rows of
 // 128 bytes (128B swizzle) and is consumed directly as a [K=64 pixels] x [MN=64 channels] atom.
-//   M side: dY channels (k), 2 atoms = 128 rows.     N side: X channels (c), BN/64 atoms.
-// Each CTA owns one (k tile, c tile, tap) output tile and one slice of the pixel range (split-K);
-// partial results are added into the fp32 gradient with red.global.add.v4.f32, i.e. straight into
+//   M side: dY channels (k), 2 atoms = 128 rows.     N side: X channels (c), BN/64 atoms per tap.
+// Each CTA owns one (k tile, c tile, tap GROUP) and one slice of the pixel range (split-K).  A group of G filter
+// taps shares every dY tile: one dY load feeds G accumulators (G*BN TMEM columns), which divides the L2 -> SM
+// operand traffic of the narrow-channel layers (C = 64, 128) that are otherwise bound by it.
+// Partial results are added into the fp32 gradient with red.global.add.v4.f32, i.e. straight into
 // the parameter's slot of the gradient bucket that the all-reduce kernel later reads.
 //
 // Replaces cuDNN wgrad / cuBLAS dW GEMMs.
@@ -22,27 +24,30 @@ constexpr int kPix = 64;                    // pixels per pipeline stage (GEMM K
 constexpr int kAtomBytes = kPix * 128;      // 64 pixels x 64 bf16
 constexpr int kWABytes = 2 * kAtomBytes;    // M = 128
 
-template <int BN>
+constexpr int pow2_cols(int c) { return c <= 32 ? 32 : c <= 64 ? 64 : c <= 128 ? 128 : c <= 256 ? 256 : 512; }
+
+template <int BN, int G>
 struct WgradCfg {
-  static constexpr int kBBytes = (BN / 64) * kAtomBytes;
-  static constexpr int kStages = BN == 256 ? 4 : (BN == 128 ? 6 : 8);
-  static constexpr int kSmemBytes = kStages * (kWABytes + kBBytes) + 1024 + 256;
-  static constexpr int kTmemCols = BN;
+  static constexpr int kBTapBytes = (BN / 64) * kAtomBytes;
+  static constexpr int kStageBytes = kWABytes + G * kBTapBytes;
+  static constexpr int kStages = (220 * 1024) / kStageBytes > 8 ? 8 : (220 * 1024) / kStageBytes;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256;
+  static constexpr int kTmemCols = pow2_cols(G * BN);
+  static_assert(G * BN <= 512, "accumulators exceed TMEM");
+  static_assert(kStages >= 2, "pipeline too shallow");
 };
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
-template <int BN>
+template <int BN, int G>
 __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_constant__ ConvKernelParams p) {
-  using Cfg = WgradCfg<BN>;
+  using Cfg = WgradCfg<BN, G>;
   constexpr int S = Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* smem_a = smem;
-  uint8_t* smem_b = smem_a + S * kWABytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_b + S * Cfg::kBBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S * Cfg::kStageBytes);
   uint64_t* full = bars;
   uint64_t* empty = bars + S;
   uint64_t* tfull = bars + 2 * S;
@@ -51,10 +56,11 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
-  // tile decode: blockIdx.x = ((tap * num_k_tiles + k_blk) * num_c_tiles + c_blk), blockIdx.y = split
+  // tile decode: blockIdx.x = ((tap_group * num_k_tiles + k_blk) * num_c_tiles + c_blk), blockIdx.y = split
   const int c_blk = blockIdx.x % p.num_c_tiles;
   const int k_blk = (blockIdx.x / p.num_c_tiles) % p.num_k_tiles;
-  const int tap = blockIdx.x / (p.num_c_tiles * p.num_k_tiles);
+  const int tap0 = (blockIdx.x / (p.num_c_tiles * p.num_k_tiles)) * G;
+  const int ntap = (p.ntaps - tap0) < G ? (p.ntaps - tap0) : G;
   const int split = blockIdx.y;
   const int pt_total = p.num_m_tiles;
   const int pt_begin = static_cast<int>((static_cast<long long>(pt_total) * split) / p.splits);
@@ -62,7 +68,7 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
   const int num_it = pt_end - pt_begin;
 
   if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&p.a_map[p.tap_view[tap]]);
+    tma_prefetch_desc(&p.a_map[p.tap_view[tap0]]);
     tma_prefetch_desc(&p.b_map);
   }
   if (warp == 1 && lane == 0) {
@@ -82,9 +88,7 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
   if (num_it > 0) {
     if (warp == 0) {
       if (lane == 0) {
-        const CUtensorMap* xmap = &p.a_map[p.tap_view[tap]];
-        const int dw = p.tap_dw[tap], dh = p.tap_dh[tap];
-        constexpr uint32_t tx_bytes = kWABytes + Cfg::kBBytes;
+        const uint32_t tx_bytes = kWABytes + static_cast<uint32_t>(ntap) * Cfg::kBTapBytes;
         int stage = 0;
         uint32_t phase = 0;
         for (int it = 0; it < num_it; ++it) {
@@ -95,14 +99,22 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
           const int w0 = tw * p.box_w, h0 = th * p.box_h, n0 = tn * p.box_n;
           mbar_wait(&empty[stage], phase ^ 1u);
           mbar_arrive_expect_tx(&full[stage], tx_bytes);
-          uint8_t* sa = smem_a + stage * kWABytes;
-          uint8_t* sb = smem_b + stage * Cfg::kBBytes;
+          uint8_t* sa = smem + stage * Cfg::kStageBytes;
+          uint8_t* sb = sa + kWABytes;
 #pragma unroll
           for (int j = 0; j < 2; ++j)
             tma_load_4d(sa + j * kAtomBytes, &p.b_map, &full[stage], k_blk * 128 + j * 64, w0, h0, n0);
 #pragma unroll
-          for (int j = 0; j < BN / 64; ++j)
-            tma_load_4d(sb + j * kAtomBytes, xmap, &full[stage], c_blk * BN + j * 64, w0 + dw, h0 + dh, n0);
+          for (int g = 0; g < G; ++g) {
+            if (g < ntap) {
+              const int t = tap0 + g;
+              const CUtensorMap* xmap = &p.a_map[p.tap_view[t]];
+#pragma unroll
+              for (int j = 0; j < BN / 64; ++j)
+                tma_load_4d(sb + g * Cfg::kBTapBytes + j * kAtomBytes, xmap, &full[stage], c_blk * BN + j * 64,
+                            w0 + p.tap_dw[t], h0 + p.tap_dh[t], n0);
+            }
+          }
           if (++stage == S) {
             stage = 0;
             phase ^= 1u;
@@ -118,15 +130,20 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
         for (int it = 0; it < num_it; ++it) {
           mbar_wait(&full[stage], phase);
           tc_fence_after_sync();
-          const uint32_t a_addr = smem_u32(smem_a + stage * kWABytes);
-          const uint32_t b_addr = smem_u32(smem_b + stage * Cfg::kBBytes);
+          const uint32_t a_addr = smem_u32(smem + stage * Cfg::kStageBytes);
+          const uint32_t b_addr = a_addr + kWABytes;
 #pragma unroll
-          for (int k = 0; k < kPix / 16; ++k) {
-            // MN-major, 128B swizzle: LBO = stride between 64-channel atoms, SBO = stride between
-            // 8-pixel groups; one MMA consumes 16 pixels = 2048 bytes of every atom.
-            const uint64_t adesc = umma_smem_desc(a_addr + k * 2048, kAtomBytes, 1024);
-            const uint64_t bdesc = umma_smem_desc(b_addr + k * 2048, kAtomBytes, 1024);
-            umma_bf16(tmem_base, adesc, bdesc, idesc, (it | k) != 0 ? 1u : 0u);
+          for (int g = 0; g < G; ++g) {
+            if (g < ntap) {
+#pragma unroll
+              for (int k = 0; k < kPix / 16; ++k) {
+                // MN-major, 128B swizzle: LBO = stride between 64-channel atoms, SBO = stride between
+                // 8-pixel groups; one MMA consumes 16 pixels = 2048 bytes of every atom.
+                const uint64_t adesc = umma_smem_desc(a_addr + k * 2048, kAtomBytes, 1024);
+                const uint64_t bdesc = umma_smem_desc(b_addr + g * Cfg::kBTapBytes + k * 2048, kAtomBytes, 1024);
+                umma_bf16(tmem_base + g * BN, adesc, bdesc, idesc, (it | k) != 0 ? 1u : 0u);
+              }
+            }
           }
           umma_commit(&empty[stage]);
           if (++stage == S) {
@@ -143,19 +160,22 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
       mbar_wait(tfull, 0);
       tc_fence_after_sync();
       const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-      float* dst_row = p.dw + static_cast<long long>(krow) * p.w_ld + p.tap_woff[tap] + c_blk * BN;
 #pragma unroll 1
-      for (int chunk = 0; chunk < BN / 32; ++chunk) {
-        uint32_t v[32];
-        tmem_ld_32x32(t_addr + chunk * 32, v);
-        tmem_ld_wait();
-        if (krow < p.k_out) {
-          const int c0 = c_blk * BN + chunk * 32;
+      for (int g = 0; g < ntap; ++g) {
+        float* dst_row = p.dw + static_cast<long long>(krow) * p.w_ld + p.tap_woff[tap0 + g] + c_blk * BN;
+#pragma unroll 1
+        for (int chunk = 0; chunk < BN / 32; ++chunk) {
+          uint32_t v[32];
+          tmem_ld_32x32(t_addr + g * BN + chunk * 32, v);
+          tmem_ld_wait();
+          if (krow < p.k_out) {
+            const int c0 = c_blk * BN + chunk * 32;
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            if (c0 + j < p.c_total)
-              red_add_v4(dst_row + chunk * 32 + j, __uint_as_float(v[j]), __uint_as_float(v[j + 1]),
-                         __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+            for (int j = 0; j < 32; j += 4) {
+              if (c0 + j < p.c_total)
+                red_add_v4(dst_row + chunk * 32 + j, __uint_as_float(v[j]), __uint_as_float(v[j + 1]),
+                           __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+            }
           }
         }
       }
@@ -166,17 +186,18 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
   if (warp == 2) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
 }
 
-template <int BN>
+template <int BN, int G>
 static int launch_wgrad(const ConvKernelParams& kp, cudaStream_t stream) {
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e =
-        cudaFuncSetAttribute(wgrad_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, WgradCfg<BN>::kSmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(wgrad_kernel<BN, G>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         WgradCfg<BN, G>::kSmemBytes);
     if (e != cudaSuccess) return -10;
     attr_set = true;
   }
-  dim3 grid(kp.ntaps * kp.num_k_tiles * kp.num_c_tiles, kp.splits, 1);
-  wgrad_kernel<BN><<<grid, kWThreads, WgradCfg<BN>::kSmemBytes, stream>>>(kp);
+  const int groups = (kp.ntaps + G - 1) / G;
+  dim3 grid(groups * kp.num_k_tiles * kp.num_c_tiles, kp.splits, 1);
+  wgrad_kernel<BN, G><<<grid, kWThreads, WgradCfg<BN, G>::kSmemBytes, stream>>>(kp);
   return cudaGetLastError() == cudaSuccess ? 0 : -11;
 }
 
@@ -212,9 +233,16 @@ extern "C" int dmpi_wgrad_run(dmpi_conv_plan* plan, const void* dy, const void* 
     cudaDeviceGetAttribute(&plan->num_sms, cudaDevAttrMultiProcessorCount, dev);
     if (plan->num_sms <= 0) plan->num_sms = 148;
   }
+  // taps per CTA: narrow N tiles share the dY tile between several taps
+  int G = 1;
+  if (kp.ntaps > 1) {
+    if (d.bn == 64) G = (kp.ntaps % 3 == 0) ? 3 : 4;
+    else if (d.bn == 128) G = 3;
+  }
+  const int groups = (kp.ntaps + G - 1) / G;
   int splits = d.splits;
   if (splits <= 0) {
-    const int tiles = kp.ntaps * kp.num_k_tiles * kp.num_c_tiles;
+    const int tiles = groups * kp.num_k_tiles * kp.num_c_tiles;
     splits = (2 * plan->num_sms + tiles - 1) / tiles;
     const int max_splits = kp.num_m_tiles / 4 > 0 ? kp.num_m_tiles / 4 : 1;
     if (splits > max_splits) splits = max_splits;
@@ -223,9 +251,11 @@ extern "C" int dmpi_wgrad_run(dmpi_conv_plan* plan, const void* dy, const void* 
   if (splits > kp.num_m_tiles) splits = kp.num_m_tiles > 0 ? kp.num_m_tiles : 1;
   kp.splits = splits;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  switch (d.bn) {
-    case 64: return launch_wgrad<64>(kp, s);
-    case 128: return launch_wgrad<128>(kp, s);
-    default: return launch_wgrad<256>(kp, s);
+  if (d.bn == 64) {
+    if (G == 3) return launch_wgrad<64, 3>(kp, s);
+    if (G == 4) return launch_wgrad<64, 4>(kp, s);
+    return launch_wgrad<64, 1>(kp, s);
   }
+  if (d.bn == 128) return G == 3 ? launch_wgrad<128, 3>(kp, s) : launch_wgrad<128, 1>(kp, s);
+  return launch_wgrad<256, 1>(kp, s);
 }

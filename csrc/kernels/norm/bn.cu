@@ -132,38 +132,64 @@ struct BnBwdArgs {
   float* acc;     // scratch [2*C]: sum(dz), sum(dz * xhat); must be zero on entry of the reduce pass
   float* dgamma;  // parameter gradients, accumulated (+=) by the apply pass
   float* dbeta;
+  const float* beta;  // only for relu_from_y
+  int relu_from_y;    // ReLU mask recomputed as (y*scale + shift > 0) instead of being read from `act`: exact for a
+                      // BatchNorm+ReLU without residual (same fp32 fma as the forward) and saves one tensor read per pass
 };
 
 // Pass 1: per-channel reductions.  Thread (tx, ty): tx owns 8 consecutive channels, ty strides rows.
-__global__ void __launch_bounds__(kBnThreads) bn_bwd_reduce_kernel(const BnBwdArgs a) {
+__global__ void __launch_bounds__(kBnThreads, 4) bn_bwd_reduce_kernel(const BnBwdArgs a) {
   const int vecC = a.C >> 3;
   const int tx = threadIdx.x % vecC;  // host guarantees vecC divides or is <= blockDim
   const int ty = threadIdx.x / vecC;
   const int rows_per_block = blockDim.x / vecC;
   const int c0 = tx << 3;
-  float s1[8], s2[8], mean[8], istd[8];
+  // s2 accumulates dz * (y - mean); the common factor invstd is applied once per block after the reduction.
+  float s1[8], s2[8], mean[8], sc[8], sh[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     s1[j] = s2[j] = 0.f;
     mean[j] = a.mean[c0 + j];
-    istd[j] = a.invstd[c0 + j];
+    sc[j] = sh[j] = 0.f;
+    if (a.relu_from_y) {
+      const float g = a.gamma ? a.gamma[c0 + j] : 1.f;
+      const float b = a.beta ? a.beta[c0 + j] : 0.f;
+      const float istd = a.invstd[c0 + j];
+      sc[j] = g * istd;
+      sh[j] = b - mean[j] * g * istd;
+    }
   }
   if (ty < rows_per_block) {
-    for (long long row = blockIdx.x * static_cast<long long>(rows_per_block) + ty; row < a.M;
-         row += static_cast<long long>(gridDim.x) * rows_per_block) {
-      const uint4 g = *reinterpret_cast<const uint4*>(a.dout + row * a.ld_dout + c0);
-      const uint4 yv = *reinterpret_cast<const uint4*>(a.y + row * a.ldy + c0);
-      uint4 av = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);
-      if (a.act) av = *reinterpret_cast<const uint4*>(a.act + row * a.ld_act + c0);
-      const uint32_t gi[4] = {g.x, g.y, g.z, g.w}, yi[4] = {yv.x, yv.y, yv.z, yv.w}, ai[4] = {av.x, av.y, av.z, av.w};
+    const long long stride = static_cast<long long>(gridDim.x) * rows_per_block;
+    for (long long row = blockIdx.x * static_cast<long long>(rows_per_block) + ty; row < a.M; row += 2 * stride) {
+      const long long row2 = row + stride;
+      const bool has2 = row2 < a.M;
+      uint4 g[2], yv[2], av[2];
+      av[0] = av[1] = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);
+      g[0] = *reinterpret_cast<const uint4*>(a.dout + row * a.ld_dout + c0);
+      yv[0] = *reinterpret_cast<const uint4*>(a.y + row * a.ldy + c0);
+      if (a.act) av[0] = *reinterpret_cast<const uint4*>(a.act + row * a.ld_act + c0);
+      if (has2) {
+        g[1] = *reinterpret_cast<const uint4*>(a.dout + row2 * a.ld_dout + c0);
+        yv[1] = *reinterpret_cast<const uint4*>(a.y + row2 * a.ldy + c0);
+        if (a.act) av[1] = *reinterpret_cast<const uint4*>(a.act + row2 * a.ld_act + c0);
+      }
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float d0 = bf16lo(ai[j]) > 0.f ? bf16lo(gi[j]) : 0.f;
-        const float d1 = bf16hi(ai[j]) > 0.f ? bf16hi(gi[j]) : 0.f;
-        s1[2 * j] += d0;
-        s1[2 * j + 1] += d1;
-        s2[2 * j] = fmaf(d0, (bf16lo(yi[j]) - mean[2 * j]) * istd[2 * j], s2[2 * j]);
-        s2[2 * j + 1] = fmaf(d1, (bf16hi(yi[j]) - mean[2 * j + 1]) * istd[2 * j + 1], s2[2 * j + 1]);
+      for (int u = 0; u < 2; ++u) {
+        if (u == 1 && !has2) break;
+        const uint32_t gi[4] = {g[u].x, g[u].y, g[u].z, g[u].w}, yi[4] = {yv[u].x, yv[u].y, yv[u].z, yv[u].w},
+                       ai[4] = {av[u].x, av[u].y, av[u].z, av[u].w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const bool m0 = a.relu_from_y ? fmaf(bf16lo(yi[j]), sc[2 * j], sh[2 * j]) > 0.f : bf16lo(ai[j]) > 0.f;
+          const bool m1 = a.relu_from_y ? fmaf(bf16hi(yi[j]), sc[2 * j + 1], sh[2 * j + 1]) > 0.f : bf16hi(ai[j]) > 0.f;
+          const float d0 = m0 ? bf16lo(gi[j]) : 0.f;
+          const float d1 = m1 ? bf16hi(gi[j]) : 0.f;
+          s1[2 * j] += d0;
+          s1[2 * j + 1] += d1;
+          s2[2 * j] = fmaf(d0, bf16lo(yi[j]) - mean[2 * j], s2[2 * j]);
+          s2[2 * j + 1] = fmaf(d1, bf16hi(yi[j]) - mean[2 * j + 1], s2[2 * j + 1]);
+        }
       }
     }
   }
@@ -186,7 +212,7 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_reduce_kernel(const BnBwdAr
       t2 += r2[(r * vecC + ctx) * 8 + cj];
     }
     atomicAdd(a.acc + c, t1);
-    atomicAdd(a.acc + a.C + c, t2);
+    atomicAdd(a.acc + a.C + c, t2 * a.invstd[c]);
   }
 }
 
@@ -201,13 +227,15 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_kernel(const BnBwdArg
   const int rows_per_block = blockDim.x / vecC;
   const int c0 = tx << 3;
   const float invM = 1.f / static_cast<float>(a.M);
-  float kA[8], kB[8], kD[8];
+  float kA[8], kB[8], kD[8], sc[8], sh[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     const int c = c0 + j;
     const float sdz = a.acc[c], sdzx = a.acc[a.C + c];
     const float g = a.gamma ? a.gamma[c] : 1.f;
     const float istd = a.invstd[c], mean = a.mean[c];
+    sc[j] = g * istd;
+    sh[j] = (a.relu_from_y && a.beta ? a.beta[c] : 0.f) - mean * g * istd;
     kA[j] = g * istd;
     kB[j] = -kA[j] * istd * (sdzx * invM);
     kD[j] = -kA[j] * (sdz * invM) - kB[j] * mean;
@@ -241,8 +269,10 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_kernel(const BnBwdArg
       uint32_t oi[4], ri[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const float d0 = bf16lo(ai[j]) > 0.f ? bf16lo(gi[j]) : 0.f;
-        const float d1 = bf16hi(ai[j]) > 0.f ? bf16hi(gi[j]) : 0.f;
+        const bool m0 = a.relu_from_y ? fmaf(bf16lo(yi[j]), sc[2 * j], sh[2 * j]) > 0.f : bf16lo(ai[j]) > 0.f;
+        const bool m1 = a.relu_from_y ? fmaf(bf16hi(yi[j]), sc[2 * j + 1], sh[2 * j + 1]) > 0.f : bf16hi(ai[j]) > 0.f;
+        const float d0 = m0 ? bf16lo(gi[j]) : 0.f;
+        const float d1 = m1 ? bf16hi(gi[j]) : 0.f;
         oi[j] = pack_bf16x2(fmaf(kA[2 * j], d0, fmaf(kB[2 * j], bf16lo(yi[j]), kD[2 * j])),
                             fmaf(kA[2 * j + 1], d1, fmaf(kB[2 * j + 1], bf16hi(yi[j]), kD[2 * j + 1])));
         ri[j] = pack_bf16x2(d0, d1);
@@ -357,10 +387,27 @@ extern "C" int dmpi_bn_forward(const void* y, const void* res, void* out, long l
 }
 
 // Launches the reduce and apply passes.  `acc` is scratch of 2*C floats that must be zero on entry.
+// Extended form: with relu_from_y != 0 (and act == NULL) the ReLU mask is recomputed from y, gamma, beta and the saved
+// statistics instead of being read from the forward output.
+extern "C" int dmpi_bn_backward_ex(const void* dout, const void* y, const void* act, void* dy, void* dres, long long M,
+                                   int C, long long ld_dout, long long ldy, long long ld_act, long long ld_dy,
+                                   long long ld_dres, const float* mean, const float* invstd, const float* gamma,
+                                   const float* beta, int relu_from_y, float* acc, float* dgamma, float* dbeta,
+                                   void* stream);
+
 extern "C" int dmpi_bn_backward(const void* dout, const void* y, const void* act, void* dy, void* dres, long long M,
                                 int C, long long ld_dout, long long ldy, long long ld_act, long long ld_dy,
                                 long long ld_dres, const float* mean, const float* invstd, const float* gamma,
                                 float* acc, float* dgamma, float* dbeta, void* stream) {
+  return dmpi_bn_backward_ex(dout, y, act, dy, dres, M, C, ld_dout, ldy, ld_act, ld_dy, ld_dres, mean, invstd, gamma,
+                             nullptr, 0, acc, dgamma, dbeta, stream);
+}
+
+extern "C" int dmpi_bn_backward_ex(const void* dout, const void* y, const void* act, void* dy, void* dres, long long M,
+                                   int C, long long ld_dout, long long ldy, long long ld_act, long long ld_dy,
+                                   long long ld_dres, const float* mean, const float* invstd, const float* gamma,
+                                   const float* beta, int relu_from_y, float* acc, float* dgamma, float* dbeta,
+                                   void* stream) {
   if (C % 8 != 0) return -1;
   const int vecC = C / 8;
   BnBwdArgs a;
@@ -382,6 +429,8 @@ extern "C" int dmpi_bn_backward(const void* dout, const void* y, const void* act
   a.acc = acc;
   a.dgamma = dgamma;
   a.dbeta = dbeta;
+  a.beta = beta;
+  a.relu_from_y = (relu_from_y && act == nullptr) ? 1 : 0;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   // reduce: block = vecC * rows_per_block threads (vecC <= 256 for C <= 2048)
   int threads = kBnThreads;

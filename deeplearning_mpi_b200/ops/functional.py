@@ -72,8 +72,11 @@ class ConvBnAct(torch.autograd.Function):
             dout = dout.to(torch.bfloat16).contiguous()
         dy = torch.empty_like(y)
         dres = torch.empty_like(y) if ctx.has_res else None
-        K.bn_backward(dout, y, out if ctx.relu else None, dy, dres, mean, invstd, gamma.detach(), arena.bn_acc(bn),
-                      arena.grad_physical(gamma), arena.grad_physical(beta))
+        # Without a residual the ReLU gate is a function of y alone: recompute it instead of reading `out` again.
+        from_y = ctx.relu and not ctx.has_res
+        K.bn_backward(dout, y, out if (ctx.relu and not from_y) else None, dy, dres, mean, invstd, gamma.detach(),
+                      arena.bn_acc(bn), arena.grad_physical(gamma), arena.grad_physical(beta), beta=beta.detach(),
+                      relu_from_y=from_y)
         arena.grad_ready(gamma)
         arena.grad_ready(beta)
         if bias is not None:

@@ -46,16 +46,17 @@ def bn_forward(y, res, out, ssum, ssq, gamma, beta, save_mean, save_invstd, runn
     _chk(rc, "dmpi_bn_forward")
 
 
-def bn_backward(dout, y, act, dy, dres, mean, invstd, gamma, acc, dgamma, dbeta) -> None:
+def bn_backward(dout, y, act, dy, dres, mean, invstd, gamma, acc, dgamma, dbeta, beta=None, relu_from_y=False) -> None:
+    """``relu_from_y`` (with ``act=None``): the ReLU mask is recomputed from y instead of read from the forward output."""
     M, ld_dout = _rows_ld(dout)
     _, ldy = _rows_ld(y)
     ld_act = _rows_ld(act)[1] if act is not None else 0
     _, ld_dy = _rows_ld(dy)
     ld_dres = _rows_ld(dres)[1] if dres is not None else 0
     C = y.shape[-1]
-    rc = N.cuda().dmpi_bn_backward(_p(dout), _p(y), _p(act), _p(dy), _p(dres), M, C, ld_dout, ldy, ld_act, ld_dy,
-                                   ld_dres, _p(mean), _p(invstd), _p(gamma), _p(acc), _p(dgamma), _p(dbeta),
-                                   N.stream_ptr())
+    rc = N.cuda().dmpi_bn_backward_ex(_p(dout), _p(y), _p(act), _p(dy), _p(dres), M, C, ld_dout, ldy, ld_act, ld_dy,
+                                      ld_dres, _p(mean), _p(invstd), _p(gamma), _p(beta), int(relu_from_y), _p(acc),
+                                      _p(dgamma), _p(dbeta), N.stream_ptr())
     N.count_launch(2)
     _chk(rc, "dmpi_bn_backward")
 

@@ -27,6 +27,12 @@ int dmpi_bn_backward(const void* dout, const void* y, const void* act, void* dy,
                      long long ld_dout, long long ldy, long long ld_act, long long ld_dy, long long ld_dres,
                      const float* mean, const float* invstd, const float* gamma, float* acc, float* dgamma,
                      float* dbeta, void* stream);
+/* Extended form: relu_from_y != 0 with act == NULL recomputes the ReLU gate as (y*gamma*invstd + beta - mean*gamma*invstd > 0)
+ * - exact for BatchNorm+ReLU without a residual, and one tensor read less per pass. */
+int dmpi_bn_backward_ex(const void* dout, const void* y, const void* act, void* dy, void* dres, long long M, int C,
+                        long long ld_dout, long long ldy, long long ld_act, long long ld_dy, long long ld_dres,
+                        const float* mean, const float* invstd, const float* gamma, const float* beta, int relu_from_y,
+                        float* acc, float* dgamma, float* dbeta, void* stream);
 /* Same computation for callers that cannot allocate the scratch (GPU memory fully owned by the host application's
  * pool, latency-critical paths where cudaMalloc/cudaFree would stall the device, plug-ins barred from any allocator).
  * This entry point has no counterpart in the reference; it exists for such embedders only.

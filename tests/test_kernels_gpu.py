@@ -71,6 +71,15 @@ def test_bn_forward_backward(shape, res, relu):
     _close(dbeta, b_ref.grad, 1e-2, "bn_dbeta")
     if res:
         _close(dres, rr.grad.permute(0, 2, 3, 1), 1e-2, "bn_dres")
+    if relu and not res:
+        # the gate recomputed from y must reproduce the gate read from the forward output exactly
+        dy2 = torch.empty_like(y)
+        acc2 = torch.zeros(2 * c, device=DEV)
+        dg2, db2 = torch.zeros(c, device=DEV), torch.zeros(c, device=DEV)
+        K.bn_backward(dout, y, None, dy2, None, mean, invstd, gamma, acc2, dg2, db2, beta=beta, relu_from_y=True)
+        # (not bit-equal: the two runs accumulate their reductions with atomics; a flipped gate would be an O(1) error)
+        _close(dy2, dy, 1e-2, "bn_dy_from_y")
+        _close(dg2, dgamma, 1e-5, "bn_dgamma_from_y")
 
 
 def test_bn_eval():
