@@ -42,6 +42,10 @@ def parse_args():
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default: 256 resnet, 16 unet)")
     ap.add_argument("--size", type=int, default=0, help="image side (default: 224 resnet50/18, 512 unet)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-graph", dest="graph", action="store_false",
+                    help="ours: launch eagerly instead of replaying the CUDA graph of the whole iteration "
+                         "(deeplearning_mpi_b200.utils.graph.GraphedTrainStep, the default)")
+    ap.set_defaults(graph=True)
     return ap.parse_args()
 
 
@@ -312,6 +316,10 @@ def main():
     host = make_host_batches(args, batch, size)
     x_dev = host[0][0].to(device)
     y_dev = host[0][1].to(device)
+    if args.graph and args.impl == "ours":
+        from deeplearning_mpi_b200.utils.graph import GraphedTrainStep
+
+        step = GraphedTrainStep(step, (x_dev, y_dev))
 
     # ---- device-timed: inputs resident on the device
     for _ in range(args.warmup):
@@ -387,6 +395,7 @@ def main():
             "config": {"model": args.model, "global_batch": batch * world, "per_gpu_batch": batch, "image_size": size,
                        "seq_len": None, "parallelism": par, "backend": arm["backend"],
                        "optimizer": "adam+clip" if args.model == "unet" else "sgd_momentum",
+                       "cuda_graph": bool(args.graph and args.impl == "ours"),
                        "l2_policy": "per-step inputs and activations exceed the 126 MB L2; no explicit flush"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "final_loss": final_loss,
         }

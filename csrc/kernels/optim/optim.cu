@@ -63,7 +63,12 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
                                                    float* __restrict__ m, float* __restrict__ v,
                                                    __nv_bfloat16* __restrict__ shadow, long long n, float lr,
                                                    float beta1, float beta2, float eps, float wd, float bc1, float bc2,
-                                                   const float* sumsq, float max_norm) {
+                                                   const float* sumsq, float max_norm, const float* step_dev) {
+  if (step_dev) {  // step count kept on the device (CUDA-graph replay): bias corrections computed here
+    const float t = *step_dev;
+    bc1 = 1.f - powf(beta1, t);
+    bc2 = 1.f - powf(beta2, t);
+  }
   const float coef = clip_coef(sumsq, max_norm);
   const float step_size = lr / bc1;
   const float inv_sqrt_bc2 = rsqrtf(bc2);
@@ -175,7 +180,18 @@ extern "C" int dmpi_adam_step(float* p, const float* g, float* m, float* v, void
   if (n % 4) return -1;
   adam_kernel<<<flat_grid(n), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       p, g, m, v, static_cast<__nv_bfloat16*>(shadow), n, lr, beta1, beta2, eps, wd, bias_corr1, bias_corr2, sumsq,
-      max_norm);
+      max_norm, nullptr);
+  return cudaGetLastError() == cudaSuccess ? 0 : -2;
+}
+
+// Same update with the step count t read from device memory (bias corrections 1 - beta^t computed in the kernel), so
+// that a captured CUDA graph of the training step stays correct across replays.
+extern "C" int dmpi_adam_step_dev(float* p, const float* g, float* m, float* v, void* shadow, long long n, float lr,
+                                  float beta1, float beta2, float eps, float wd, const float* step_dev,
+                                  const float* sumsq, float max_norm, void* stream) {
+  if (n % 4 || !step_dev) return -1;
+  adam_kernel<<<flat_grid(n), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      p, g, m, v, static_cast<__nv_bfloat16*>(shadow), n, lr, beta1, beta2, eps, wd, 1.f, 1.f, sumsq, max_norm, step_dev);
   return cudaGetLastError() == cudaSuccess ? 0 : -2;
 }
 

@@ -156,6 +156,7 @@ def _bind_cuda(lib) -> None:
     # optim
     _sig(lib, "dmpi_sgd_step", I, [VP, VP, VP, VP, I64, F, F, F, F, I, VP, F, VP])
     _sig(lib, "dmpi_adam_step", I, [VP, VP, VP, VP, VP, I64, F, F, F, F, F, F, F, VP, F, VP])
+    _sig(lib, "dmpi_adam_step_dev", I, [VP, VP, VP, VP, VP, I64, F, F, F, F, F, VP, VP, F, VP])
     _sig(lib, "dmpi_sumsq", I, [VP, I64, VP, VP])
     _sig(lib, "dmpi_scale_by_clip", I, [VP, I64, VP, F, VP])
     _sig(lib, "dmpi_cast_bf16", I, [VP, VP, I64, VP])

@@ -173,6 +173,14 @@ def adam_step(p, g, m, v, shadow, n, lr, b1, b2, eps, wd, bc1, bc2, sumsq=None, 
     _chk(rc, "dmpi_adam_step")
 
 
+def adam_step_dev(p, g, m, v, shadow, n, lr, b1, b2, eps, wd, step_t, sumsq=None, max_norm=0.0) -> None:
+    """Adam with the step count read from the device tensor ``step_t`` (fp32 scalar) — CUDA-graph safe."""
+    rc = N.cuda().dmpi_adam_step_dev(_p(p), _p(g), _p(m), _p(v), _p(shadow), n, lr, b1, b2, eps, wd, _p(step_t),
+                                     _p(sumsq), float(max_norm), N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_adam_step_dev")
+
+
 def sumsq(g, n, out) -> None:
     rc = N.cuda().dmpi_sumsq(_p(g), n, _p(out), N.stream_ptr())
     N.count_launch()

@@ -156,9 +156,12 @@ class Adam(_FlatOptimizer):
             if "exp_avg" not in self.state:
                 self.state["exp_avg"] = torch.zeros_like(a.flat_p)
                 self.state["exp_avg_sq"] = torch.zeros_like(a.flat_p)
+                # the step count also lives on the device so that a captured CUDA graph of the step stays correct
+                self.state["step_t"] = torch.full((), float(t - 1), dtype=torch.float32, device=a.device)
+            self.state["step_t"] += 1.0
             ss, mn = self._take_clip()
-            K.adam_step(a.flat_p, a.flat_g, self.state["exp_avg"], self.state["exp_avg_sq"], a.flat_s, a.total, lr, b1,
-                        b2, eps, wd, bc1, bc2, ss, mn)
+            K.adam_step_dev(a.flat_p, a.flat_g, self.state["exp_avg"], self.state["exp_avg_sq"], a.flat_s, a.total, lr,
+                            b1, b2, eps, wd, self.state["step_t"], ss, mn)
             a.refresh_derived()
             a.mark_shadows_fresh()
         else:

@@ -77,6 +77,10 @@ int dmpi_sgd_step(float* p, const float* g, float* mom, void* bf16_shadow, long 
 int dmpi_adam_step(float* p, const float* g, float* m, float* v, void* bf16_shadow, long long n, float lr, float beta1,
                    float beta2, float eps, float wd, float bias_corr1, float bias_corr2, const float* clip_sumsq,
                    float max_norm, void* stream);
+/* Adam with the step count t read from device memory (bias corrections computed in-kernel): CUDA-graph safe. */
+int dmpi_adam_step_dev(float* p, const float* g, float* m, float* v, void* bf16_shadow, long long n, float lr,
+                       float beta1, float beta2, float eps, float wd, const float* step_dev, const float* clip_sumsq,
+                       float max_norm, void* stream);
 int dmpi_sumsq(const float* g, long long n, float* out, void* stream);
 int dmpi_scale_by_clip(float* g, long long n, const float* sumsq, float max_norm, void* stream);
 int dmpi_cast_bf16(const float* src, void* dst, long long n, void* stream);
