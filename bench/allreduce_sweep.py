@@ -45,8 +45,10 @@ sizes += [int(9.0 * 2**20), int(25.3 * 2**20), int(42.65 * 2**20), int(97.49 * 2
 for nbytes in sorted(set(s - s % 16 for s in sizes if s <= max_bytes)):
     iters = 20 if nbytes <= (8 << 20) else 6
     res = {"bytes": nbytes}
-    for algo in ("oneshot", "oneshot_bf16", "twoshot"):
-        if algo != "twoshot" and nbytes > comm.slot_bytes:
+    for algo in ("oneshot", "oneshot_bf16", "twoshot", "nvls"):
+        if algo.startswith("oneshot") and nbytes > comm.slot_bytes:
+            continue
+        if algo == "nvls" and not comm.has_multicast:
             continue
         for nb in (16, 32, 64):
             for _ in range(2):
@@ -64,9 +66,12 @@ for nbytes in sorted(set(s - s % 16 for s in sizes if s <= max_bytes)):
     res["nccl_busbw_GBs"] = 2 * (world - 1) / world * nbytes / (res["nccl_us"] * 1e-6) / 1e9
     rows.append(res)
     if rank == 0:
-        print(f"{nbytes:>11d} B  ours {best:9.1f} us ({res['ours_busbw_GBs']:7.1f} GB/s)   nccl {res['nccl_us']:9.1f} us "
+        nv = min([v for k, v in res.items() if k.startswith("nvls")], default=float("nan"))
+        ts = min([v for k, v in res.items() if k.startswith("twoshot")], default=float("nan"))
+        print(f"{nbytes:>11d} B  twoshot {ts:8.1f} nvls {nv:8.1f} | ours {best:9.1f} us ({res['ours_busbw_GBs']:7.1f} GB/s)   nccl {res['nccl_us']:9.1f} us "
               f"({res['nccl_busbw_GBs']:7.1f} GB/s)", flush=True)
 if rank == 0:
+    print("multicast (NVLS) mapping:", comm.has_multicast)
     os.makedirs("gpurun_out", exist_ok=True)
     json.dump({"world": world, "rows": rows}, open(f"gpurun_out/allreduce_sweep_w{world}.json", "w"), indent=1)
 tdist.barrier()

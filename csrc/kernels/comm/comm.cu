@@ -218,6 +218,51 @@ __global__ void __launch_bounds__(kCommThreads) allreduce_oneshot_kernel(const d
   if (threadIdx.x == 0) p.epoch[rank][blk] = e + 1;
 }
 
+// NVLS: the reduction happens inside the NVSwitch.  `mc_data` is the multicast mapping of the data region; a
+// multimem.ld_reduce on it returns the sum over every rank's copy, a multimem.st writes every rank's copy.  Rank r
+// handles slice r, so each element crosses this GPU's link once inbound (already reduced) and once outbound.
+template <bool kBf16>
+__global__ void __launch_bounds__(kCommThreads) allreduce_nvls_kernel(const dmpi_comm_ptrs p, long long off_bytes,
+                                                                      long long nvec, float scale) {
+  const int rank = p.rank_base;
+  const int blk = blockIdx.x;
+  const int W = p.world;
+  const uint32_t e = p.epoch[rank][blk];
+  block_barrier(p, rank, blk, e + 1);
+  char* mc = static_cast<char*>(p.mc_data) + off_bytes;
+  const long long v_begin = nvec * rank / W, v_end = nvec * (rank + 1) / W;
+  for (long long i = v_begin + static_cast<long long>(blk) * blockDim.x + threadIdx.x; i < v_end;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    char* addr = mc + i * 16;
+    if (kBf16) {
+      uint32_t a, b, c, d;
+      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+                   : "=r"(a), "=r"(b), "=r"(c), "=r"(d)
+                   : "l"(addr)
+                   : "memory");
+      a = pack_bf16x2(bf16lo(a) * scale, bf16hi(a) * scale);
+      b = pack_bf16x2(bf16lo(b) * scale, bf16hi(b) * scale);
+      c = pack_bf16x2(bf16lo(c) * scale, bf16hi(c) * scale);
+      d = pack_bf16x2(bf16lo(d) * scale, bf16hi(d) * scale);
+      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(__uint_as_float(a)),
+                   "f"(__uint_as_float(b)), "f"(__uint_as_float(c)), "f"(__uint_as_float(d))
+                   : "memory");
+    } else {
+      float a, b, c, d;
+      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                   : "=f"(a), "=f"(b), "=f"(c), "=f"(d)
+                   : "l"(addr)
+                   : "memory");
+      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a * scale),
+                   "f"(b * scale), "f"(c * scale), "f"(d * scale)
+                   : "memory");
+    }
+  }
+  __threadfence_system();
+  block_barrier(p, rank, blk, e + 2);
+  if (threadIdx.x == 0) p.epoch[rank][blk] = e + 2;
+}
+
 // ------------------------------------------------------------------------------------------------ broadcast
 __global__ void __launch_bounds__(kCommThreads) broadcast_kernel(const dmpi_comm_ptrs p, long long off_bytes,
                                                                  long long nvec, int root) {
@@ -306,6 +351,18 @@ extern "C" int dmpi_allreduce_twoshot(const dmpi_comm_ptrs* ptrs, long long off_
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (dtype == DMPI_BF16) allreduce_twoshot_kernel<true><<<grid, kCommThreads, 0, s>>>(*ptrs, off_bytes, nvec, scale);
   else allreduce_twoshot_kernel<false><<<grid, kCommThreads, 0, s>>>(*ptrs, off_bytes, nvec, scale);
+  return cudaGetLastError() == cudaSuccess ? 0 : -2;
+}
+
+extern "C" int dmpi_allreduce_nvls(const dmpi_comm_ptrs* ptrs, long long off_bytes, long long nbytes, int dtype, float scale,
+                                   int nblocks, void* stream) {
+  if (nbytes % 16 || off_bytes % 16) return -1;
+  if (!ptrs->mc_data) return -4;  // no multicast mapping on this host
+  const long long nvec = nbytes / 16;
+  const int nb = clamp_blocks(nblocks, (nvec + ptrs->world - 1) / ptrs->world);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (dtype == DMPI_BF16) allreduce_nvls_kernel<true><<<nb, kCommThreads, 0, s>>>(*ptrs, off_bytes, nvec, scale);
+  else allreduce_nvls_kernel<false><<<nb, kCommThreads, 0, s>>>(*ptrs, off_bytes, nvec, scale);
   return cudaGetLastError() == cudaSuccess ? 0 : -2;
 }
 

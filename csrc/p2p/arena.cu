@@ -11,6 +11,7 @@
 //   [ MAX_COMM_BLOCKS * MAX_RANKS * 4 ]              signal pad
 //   [ MAX_COMM_BLOCKS * 4 ]                          per-block epochs (local use)
 //   [ MAX_RANKS * 4 ] [ MAX_RANKS * 4 ]              send/recv sequence and acknowledge flags
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -20,7 +21,7 @@
 
 #include "../../include/dmpi_comm.h"
 
-static thread_local char g_arena_err[256] = {0};
+thread_local char g_arena_err[256] = {0};
 #define ARENA_CHECK(expr)                                                                              \
   do {                                                                                                 \
     cudaError_t _e = (expr);                                                                           \
@@ -30,19 +31,9 @@ static thread_local char g_arena_err[256] = {0};
     }                                                                                                  \
   } while (0)
 
-static long long align256(long long v) { return (v + 255) & ~255LL; }
+#include "arena_internal.h"
 
-struct dmpi_arena {
-  int rank, world;
-  bool emulated;
-  long long data_bytes, stage_slot_bytes, mailbox_bytes;
-  long long off_stage, off_mail, off_sig, off_epoch, off_seq, off_ack, total;
-  void* base[DMPI_MAX_RANKS];  // mapped base of every rank's arena (own = local allocation)
-  bool opened[DMPI_MAX_RANKS];
-  dmpi_comm_ptrs ptrs;
-};
-
-static void layout(dmpi_arena* a) {
+void dmpi_arena_layout(dmpi_arena* a) {
   a->off_stage = align256(a->data_bytes);
   a->off_mail = a->off_stage + align256(2LL * DMPI_MAX_RANKS * a->stage_slot_bytes);
   a->off_sig = a->off_mail + align256(1LL * DMPI_MAX_RANKS * a->mailbox_bytes);
@@ -52,7 +43,7 @@ static void layout(dmpi_arena* a) {
   a->total = a->off_ack + align256(4LL * DMPI_MAX_RANKS);
 }
 
-static void fill_ptrs(dmpi_arena* a) {
+void dmpi_arena_fill_ptrs(dmpi_arena* a) {
   memset(&a->ptrs, 0, sizeof(a->ptrs));
   a->ptrs.world = a->world;
   a->ptrs.rank_base = a->emulated ? 0 : a->rank;
@@ -64,6 +55,7 @@ static void fill_ptrs(dmpi_arena* a) {
     a->ptrs.sig[r] = reinterpret_cast<uint32_t*>(b + a->off_sig);
     a->ptrs.epoch[r] = reinterpret_cast<uint32_t*>(b + a->off_epoch);
   }
+  a->ptrs.mc_data = (a->vmm && a->mc_va) ? reinterpret_cast<void*>(a->mc_va) : nullptr;
 }
 
 static dmpi_arena* make(int rank, int world, long long data_bytes, long long slot, long long mailbox, bool emulated) {
@@ -80,7 +72,7 @@ static dmpi_arena* make(int rank, int world, long long data_bytes, long long slo
   a->data_bytes = align256(data_bytes);
   a->stage_slot_bytes = align256(slot);
   a->mailbox_bytes = align256(mailbox);
-  layout(a);
+  dmpi_arena_layout(a);
   const int n_local = emulated ? world : 1;
   for (int i = 0; i < n_local; ++i) {
     const int r = emulated ? i : rank;
@@ -97,7 +89,7 @@ static dmpi_arena* make(int rank, int world, long long data_bytes, long long slo
     }
     a->base[r] = p;
   }
-  fill_ptrs(a);
+  dmpi_arena_fill_ptrs(a);
   return a;
 }
 
@@ -111,8 +103,15 @@ extern "C" dmpi_arena* dmpi_arena_create_emulated(int world, long long data_byte
   return make(0, world, data_bytes, stage_slot_bytes, mailbox_bytes, true);
 }
 
+void dmpi_arena_vmm_destroy(dmpi_arena* a);
+
 extern "C" void dmpi_arena_destroy(dmpi_arena* a) {
   if (!a) return;
+  if (a->vmm) {
+    dmpi_arena_vmm_destroy(a);
+    delete a;
+    return;
+  }
   for (int r = 0; r < DMPI_MAX_RANKS; ++r) {
     if (!a->base[r]) continue;
     if (a->opened[r]) cudaIpcCloseMemHandle(a->base[r]);
@@ -140,7 +139,7 @@ extern "C" int dmpi_arena_open_peers(dmpi_arena* a, const void* handles) {
     a->base[r] = p;
     a->opened[r] = true;
   }
-  fill_ptrs(a);
+  dmpi_arena_fill_ptrs(a);
   return 0;
 }
 

@@ -171,6 +171,19 @@ def _bind_cuda(lib) -> None:
     _sig(lib, "dmpi_arena_create", VP, [I, I, I64, I64, I64])
     _sig(lib, "dmpi_arena_create_emulated", VP, [I, I64, I64, I64])
     _sig(lib, "dmpi_arena_destroy", None, [VP])
+    _sig(lib, "dmpi_arena_create_vmm", VP, [I, I, I64, I64, I64])
+    _sig(lib, "dmpi_arena_multicast_supported", I, [])
+    _sig(lib, "dmpi_arena_export_fd", I, [VP])
+    _sig(lib, "dmpi_arena_import_peer_fd", I, [VP, I, I])
+    _sig(lib, "dmpi_arena_mc_create", I, [VP])
+    _sig(lib, "dmpi_arena_mc_import", I, [VP, I])
+    _sig(lib, "dmpi_arena_mc_add_device", I, [VP])
+    _sig(lib, "dmpi_arena_mc_bind_map", I, [VP])
+    _sig(lib, "dmpi_fd_listen", I, [C.c_char_p])
+    _sig(lib, "dmpi_fd_send", I, [C.c_char_p, I, I])
+    _sig(lib, "dmpi_fd_recv", I, [I, C.POINTER(I), I])
+    _sig(lib, "dmpi_fd_close", None, [I])
+    _sig(lib, "dmpi_allreduce_nvls", I, [VP, I64, I64, I, F, I, VP])
     _sig(lib, "dmpi_arena_ipc_handle", I, [VP, VP])
     _sig(lib, "dmpi_arena_open_peers", I, [VP, VP])
     _sig(lib, "dmpi_arena_ptrs", VP, [VP])

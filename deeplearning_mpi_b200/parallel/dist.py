@@ -39,18 +39,12 @@ class P2PComm:
         lib = N.cuda()
         self.lib, self.state = lib, state
         self.rank, self.world = state.rank, state.world
-        self.handle = lib.dmpi_arena_create(self.rank, self.world, int(data_bytes), _STAGE_SLOT_BYTES, _MAILBOX_BYTES)
+        self.has_multicast = False
+        self.handle = None
+        if self.world > 1 and os.environ.get("DMPI_VMM", "1") == "1":
+            self._create_vmm(int(data_bytes), tag)
         if not self.handle:
-            raise RuntimeError("arena allocation failed: " + (lib.dmpi_arena_last_error() or b"").decode())
-        if self.world > 1:
-            h = C.create_string_buffer(64)
-            if lib.dmpi_arena_ipc_handle(self.handle, h) != 0:
-                raise RuntimeError("cudaIpcGetMemHandle failed: " + lib.dmpi_arena_last_error().decode())
-            all_h = state.store.all_gather(f"ipc/{tag}", self.rank, self.world, h.raw)
-            blob = C.create_string_buffer(b"".join(all_h), 64 * self.world)
-            if lib.dmpi_arena_open_peers(self.handle, blob) != 0:
-                raise RuntimeError("cudaIpcOpenMemHandle failed: " + lib.dmpi_arena_last_error().decode())
-            state.store.barrier(f"ipc_open/{tag}", self.rank, self.world)
+            self._create_ipc(int(data_bytes), tag)
         self.ptrs = lib.dmpi_arena_ptrs(self.handle)
         self.data_ptr = lib.dmpi_arena_data(self.handle, self.rank)
         self.data_bytes = int(data_bytes)
@@ -58,6 +52,94 @@ class P2PComm:
         self.mailbox_bytes = lib.dmpi_arena_mailbox_bytes(self.handle)
         self._send_seq: Dict[int, int] = {}
         self._recv_seq: Dict[int, int] = {}
+
+    def _err(self) -> str:
+        return (self.lib.dmpi_arena_last_error() or b"").decode()
+
+    def _create_ipc(self, data_bytes: int, tag: str) -> None:
+        """cudaMalloc arena shared through cudaIpc handles (exchanged via the TCP store)."""
+        lib, state = self.lib, self.state
+        self.handle = lib.dmpi_arena_create(self.rank, self.world, data_bytes, _STAGE_SLOT_BYTES, _MAILBOX_BYTES)
+        if not self.handle:
+            raise RuntimeError("arena allocation failed: " + self._err())
+        if self.world > 1:
+            h = C.create_string_buffer(64)
+            if lib.dmpi_arena_ipc_handle(self.handle, h) != 0:
+                raise RuntimeError("cudaIpcGetMemHandle failed: " + self._err())
+            all_h = state.store.all_gather(f"ipc/{tag}", self.rank, self.world, h.raw)
+            blob = C.create_string_buffer(b"".join(all_h), 64 * self.world)
+            if lib.dmpi_arena_open_peers(self.handle, blob) != 0:
+                raise RuntimeError("cudaIpcOpenMemHandle failed: " + self._err())
+            state.store.barrier(f"ipc_open/{tag}", self.rank, self.world)
+
+    def _create_vmm(self, data_bytes: int, tag: str) -> None:
+        """cuMemCreate arena shared as POSIX fds (SCM_RIGHTS) and, where the host exposes it, bound to an NVSwitch
+        multicast object (NVLS).  Every rank takes the same decisions (agreed through the store); any failure falls
+        back, on all ranks together, to the cudaIpc arena."""
+        lib, st = self.lib, self.state
+        store, rank, world = st.store, self.rank, self.world
+        uid = store.get("__run_uid__").decode() if store.check("__run_uid__") else "0"
+        name = lambda r: f"dmpi-{uid}-{tag}-{r}".encode()  # noqa: E731
+        handle = lib.dmpi_arena_create_vmm(rank, world, data_bytes, _STAGE_SLOT_BYTES, _MAILBOX_BYTES)
+        sock = lib.dmpi_fd_listen(name(rank)) if handle else -1
+        ok = bool(handle) and sock >= 0
+        votes = store.all_gather(f"vmm_ok/{tag}", rank, world, b"1" if ok else b"0")
+        if not all(v == b"1" for v in votes):
+            if sock >= 0:
+                lib.dmpi_fd_close(sock)
+            if handle:
+                lib.dmpi_arena_destroy(handle)
+            return
+        try:
+            fd = lib.dmpi_arena_export_fd(handle)
+            ok = fd >= 0
+            if ok:
+                for r in range(world):
+                    if r != rank and lib.dmpi_fd_send(name(r), fd, rank) != 0:
+                        ok = False
+                os.close(fd)
+                for _ in range(world - 1):
+                    t = C.c_int(-1)
+                    pfd = lib.dmpi_fd_recv(sock, C.byref(t), 30000)
+                    if pfd < 0 or lib.dmpi_arena_import_peer_fd(handle, t.value, pfd) != 0:
+                        ok = False
+                        break
+            votes = store.all_gather(f"vmm_mapped/{tag}", rank, world, b"1" if ok else b"0")
+            if not all(v == b"1" for v in votes):
+                raise RuntimeError("peer mapping failed: " + self._err())
+            # ---- optional multicast object
+            mc = lib.dmpi_arena_multicast_supported() == 1 and os.environ.get("DMPI_NVLS", "1") == "1"
+            votes = store.all_gather(f"mc_cap/{tag}", rank, world, b"1" if mc else b"0")
+            if all(v == b"1" for v in votes):
+                ok = True
+                if rank == 0:
+                    mfd = lib.dmpi_arena_mc_create(handle)
+                    ok = mfd >= 0
+                    if ok:
+                        for r in range(1, world):
+                            ok = ok and lib.dmpi_fd_send(name(r), mfd, 1000) == 0
+                        os.close(mfd)
+                votes0 = store.all_gather(f"mc_created/{tag}", rank, world, b"1" if ok else b"0")
+                if votes0[0] == b"1":
+                    if rank != 0:
+                        t = C.c_int(-1)
+                        mfd = lib.dmpi_fd_recv(sock, C.byref(t), 30000)
+                        ok = mfd >= 0 and lib.dmpi_arena_mc_import(handle, mfd) == 0
+                    ok = ok and lib.dmpi_arena_mc_add_device(handle) == 0
+                    votes = store.all_gather(f"mc_added/{tag}", rank, world, b"1" if ok else b"0")
+                    if all(v == b"1" for v in votes):
+                        ok = lib.dmpi_arena_mc_bind_map(handle) == 0
+                        votes = store.all_gather(f"mc_bound/{tag}", rank, world, b"1" if ok else b"0")
+                        self.has_multicast = all(v == b"1" for v in votes)
+                        if not self.has_multicast and ok:
+                            raise RuntimeError("multicast bind failed on a peer")  # mixed state: start over with IPC
+            self.handle = handle
+        except RuntimeError:
+            lib.dmpi_arena_destroy(handle)
+            self.handle = None
+        finally:
+            lib.dmpi_fd_close(sock)
+        store.barrier(f"vmm_done/{tag}", rank, world)
 
     def tensor(self, offset: int, nbytes: int) -> torch.Tensor:
         from ..utils.arena import tensor_from_ptr
@@ -71,8 +153,13 @@ class P2PComm:
         if self.world == 1:
             return
         if algo == "auto":
-            algo = "oneshot" if (dtype == 0 and nbytes <= self.state.oneshot_max_bytes) else "twoshot"
-        if algo == "oneshot":
+            if dtype == 0 and nbytes <= self.state.oneshot_max_bytes:
+                algo = "oneshot"
+            else:
+                algo = "nvls" if (self.has_multicast and nbytes >= self.state.nvls_min_bytes) else "twoshot"
+        if algo == "nvls":
+            rc = self.lib.dmpi_allreduce_nvls(self.ptrs, off, nbytes, dtype, scale, nblocks, s)
+        elif algo == "oneshot":
             rc = self.lib.dmpi_allreduce_oneshot(self.ptrs, off, nbytes, 0, scale, self.slot_bytes, nblocks, 0, s)
         elif algo == "oneshot_bf16":
             rc = self.lib.dmpi_allreduce_oneshot(self.ptrs, off, nbytes, 1, scale, self.slot_bytes, nblocks, 0, s)
@@ -135,6 +222,7 @@ class GroupState:
     n_comms: int = 0
     barrier_count: int = 0
     oneshot_max_bytes: int = 256 << 10   # crossover one-shot -> two-shot; bench/allreduce_sweep.py measures it
+    nvls_min_bytes: int = 1 << 62        # crossover two-shot -> NVLS multicast (set from the sweep; huge = never)
 
     def new_comm(self, data_bytes: int) -> P2PComm:
         tag = f"comm{self.n_comms}"
@@ -256,6 +344,8 @@ def init_process_group(backend: str = "nccl", init_method: Optional[str] = None,
     if thr:
         _state.oneshot_max_bytes = int(thr)
     if world > 1:
+        if rank == 0:
+            store.set("__run_uid__", os.urandom(6).hex().encode())  # namespaces the abstract unix sockets of this job
         store.barrier("init", rank, world)
 
 

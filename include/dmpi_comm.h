@@ -27,6 +27,7 @@ typedef struct {
   uint32_t* epoch[DMPI_MAX_RANKS]; /* per-block epoch counters (a rank only touches its own) */
   int world;
   int rank_base;                   /* this process' rank (0 in single-GPU emulation) */
+  void* mc_data;                   /* NVLS: multicast address of the data region (NULL when the host exposes none) */
 } dmpi_comm_ptrs;
 
 typedef struct dmpi_arena dmpi_arena;
@@ -42,6 +43,31 @@ void dmpi_arena_destroy(dmpi_arena* a);
 int dmpi_arena_ipc_handle(dmpi_arena* a, void* out64);
 /* handles: world * 64 bytes ordered by rank (own entry ignored).  Maps every peer's arena. */
 int dmpi_arena_open_peers(dmpi_arena* a, const void* handles);
+/* ---- VMM / NVLS mode: the arena is a cuMemCreate allocation shared through POSIX file descriptors, which (unlike
+ * cudaMalloc + cudaIpc memory) can also be bound to an NVSwitch multicast object.  Set-up sequence, all ranks:
+ *   a = dmpi_arena_create_vmm(...); fd = dmpi_arena_export_fd(a);            exchange fds (dmpi_fd_* below)
+ *   dmpi_arena_import_peer_fd(a, r, fd_r) for every peer r
+ *   rank 0: mcfd = dmpi_arena_mc_create(a); others: dmpi_arena_mc_import(a, mcfd)
+ *   dmpi_arena_mc_add_device(a); <barrier>; dmpi_arena_mc_bind_map(a); <barrier>
+ * Every step returns 0 or a negative code (dmpi_arena_last_error()); multicast being unavailable is reported by
+ * dmpi_arena_multicast_supported() == 0 and is not an error: the kernels then use the peer-pointer algorithms. */
+dmpi_arena* dmpi_arena_create_vmm(int rank, int world, long long data_bytes, long long stage_slot_bytes,
+                                  long long mailbox_bytes);
+int dmpi_arena_multicast_supported(void);
+int dmpi_arena_export_fd(dmpi_arena* a);
+int dmpi_arena_import_peer_fd(dmpi_arena* a, int peer_rank, int fd);
+int dmpi_arena_mc_create(dmpi_arena* a);
+int dmpi_arena_mc_import(dmpi_arena* a, int fd);
+int dmpi_arena_mc_add_device(dmpi_arena* a);
+int dmpi_arena_mc_bind_map(dmpi_arena* a);
+/* File-descriptor passing between the ranks of one node (SCM_RIGHTS over abstract unix sockets). */
+int dmpi_fd_listen(const char* name);
+int dmpi_fd_send(const char* peer_name, int fd, int tag);
+int dmpi_fd_recv(int sock, int* tag, int timeout_ms);
+void dmpi_fd_close(int sock);
+/* In-place all-reduce through the switch: multimem.ld_reduce of slice r, fused scale, multimem.st to all ranks. */
+int dmpi_allreduce_nvls(const dmpi_comm_ptrs* ptrs, long long off_bytes, long long nbytes, int dtype, float scale,
+                        int nblocks, void* stream);
 const dmpi_comm_ptrs* dmpi_arena_ptrs(dmpi_arena* a);
 void* dmpi_arena_data(dmpi_arena* a, int rank);
 long long dmpi_arena_stage_slot_bytes(dmpi_arena* a);

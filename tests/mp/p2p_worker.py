@@ -29,8 +29,10 @@ stage = comm.tensor(0, comm.data_bytes).view(torch.float32)
 torch.manual_seed(1234 + rank)
 for nbytes in (1024, 4096 + 16, 65536, 1 << 20, (1 << 20) + 48, 25 << 20, 64 << 20):
     n = nbytes // 4
-    for algo in ("twoshot", "oneshot", "oneshot_bf16"):
-        if algo != "twoshot" and nbytes > comm.slot_bytes:
+    for algo in ("twoshot", "oneshot", "oneshot_bf16", "nvls"):
+        if algo.startswith("oneshot") and nbytes > comm.slot_bytes:
+            continue
+        if algo == "nvls" and not comm.has_multicast:
             continue
         for rep in range(3):
             src = torch.randn(n, device=dev)
@@ -181,4 +183,4 @@ all_equal(ddp.arena.flat_p, "parameters diverged after the rank-0-only eval")
 tdist.barrier()
 tdist.destroy_process_group()
 dist.destroy_process_group()
-print(f"P2P_WORKER_OK rank={rank} losses={['%.3f' % l for l in losses]}")
+print(f"P2P_WORKER_OK rank={rank} multicast={comm.has_multicast} losses={['%.3f' % l for l in losses]}")
