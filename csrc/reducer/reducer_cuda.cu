@@ -5,10 +5,12 @@
 //   after the last bucket: record(done) on the comm stream;  finalize(): compute stream waits on done.
 //
 // The all-reduce variant is chosen per bucket size (one-shot push below the threshold measured by
-// bench/allreduce_sweep.py, two-shot above), with the 1/world_size scale fused into the kernel.
+// bench/allreduce_sweep.py; above it the NVSwitch in-switch reduction (multimem) when the arena has a multicast
+// mapping and world > 2, else two-shot), with the 1/world_size scale fused into the kernel.
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include <new>
 #include <vector>
@@ -26,6 +28,7 @@ struct ReducerCuda {
   long long oneshot_max_bytes = 0, slot_bytes = 0;
   int nblocks = 32;
   int wire_bf16 = 0;
+  bool use_nvls = false;
   float scale = 1.f;
   int launched = 0;
   int last_error = 0;
@@ -52,6 +55,9 @@ extern "C" void* dmpi_reducer_cuda_create(const dmpi_comm_ptrs* ptrs, int n_buck
   r->slot_bytes = slot_bytes;
   r->nblocks = nblocks;
   r->wire_bf16 = wire_bf16;
+  // profiles/allreduce_sweep_w8.json: NVLS beats two-shot at every size above the one-shot range at W=8, loses at W=2
+  r->use_nvls = ptrs->mc_data != nullptr && ptrs->world > 2;
+  if (const char* e = getenv("DMPI_NVLS")) r->use_nvls = ptrs->mc_data != nullptr && atoi(e) != 0;
   return r;
 }
 
@@ -81,6 +87,8 @@ extern "C" void dmpi_reducer_cuda_launch(void* h, int bucket) {
     if (r->bytes[bucket] <= r->oneshot_max_bytes && r->bytes[bucket] <= r->slot_bytes)
       rc = dmpi_allreduce_oneshot(&r->ptrs, r->off[bucket], r->bytes[bucket], r->wire_bf16, r->scale, r->slot_bytes,
                                   r->nblocks, 0, r->comm);
+    else if (r->use_nvls)
+      rc = dmpi_allreduce_nvls(&r->ptrs, r->off[bucket], r->bytes[bucket], DMPI_F32, r->scale, r->nblocks, r->comm);
     else
       rc = dmpi_allreduce_twoshot(&r->ptrs, r->off[bucket], r->bytes[bucket], DMPI_F32, r->scale, r->nblocks, 0,
                                   r->comm);

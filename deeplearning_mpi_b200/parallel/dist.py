@@ -156,7 +156,10 @@ class P2PComm:
             if dtype == 0 and nbytes <= self.state.oneshot_max_bytes:
                 algo = "oneshot"
             else:
-                algo = "nvls" if (self.has_multicast and nbytes >= self.state.nvls_min_bytes) else "twoshot"
+                # measured (profiles/allreduce_sweep_w8.json): in-switch reduction wins from the one-shot crossover up at
+                # W=8 (1 GB: 835 vs 724 GB/s NCCL); at W=2 there is nothing for the switch to save and two-shot is faster
+                nvls = self.has_multicast and self.world > 2 and nbytes >= self.state.nvls_min_bytes
+                algo = "nvls" if nvls else "twoshot"
         if algo == "nvls":
             rc = self.lib.dmpi_allreduce_nvls(self.ptrs, off, nbytes, dtype, scale, nblocks, s)
         elif algo == "oneshot":
@@ -222,7 +225,7 @@ class GroupState:
     n_comms: int = 0
     barrier_count: int = 0
     oneshot_max_bytes: int = 256 << 10   # crossover one-shot -> two-shot; bench/allreduce_sweep.py measures it
-    nvls_min_bytes: int = 1 << 62        # crossover two-shot -> NVLS multicast (set from the sweep; huge = never)
+    nvls_min_bytes: int = 256 << 10      # crossover two-shot -> NVLS multicast for world > 2 (from the W=8 sweep)
 
     def new_comm(self, data_bytes: int) -> P2PComm:
         tag = f"comm{self.n_comms}"
