@@ -34,6 +34,10 @@ struct alignas(64) ConvKernelParams {
   float* dw;
   long long w_ld;
   int k_out, c_total, splits, num_k_tiles, num_c_tiles;
+  // igemm: optional tensor added to the result in the epilogue (bf16, same pixel grid as the output, element strides)
+  const void* addend;
+  long long add_sn, add_sh, add_sw;
+  int dbg;  // DMPI_IGEMM_DBG experiment bits (bench only): 1 no TMA store, 2 no statistics
 };
 
 }  // namespace dmpi

@@ -8,11 +8,17 @@
 // * B tiles (BN filters x 64 channels) come from the K-major bf16 weight shadow.
 // * tcgen05.mma (cta_group::1, M=128, N=BN, K=16) accumulates in TMEM; two accumulator stages let the
 //   epilogue of tile i overlap the main loop of tile i+1.
-// * Epilogue warps read TMEM (tcgen05.ld), add bias / ReLU, round to bf16, stage the tile in
-//   128B-swizzled shared memory, issue a TMA store into the (possibly strided / channel-sliced) output
-//   view, and accumulate per-channel sum and sum-of-squares of the stored values for BatchNorm.
+// * The epilogue is a two-stage pipeline of its own, in sub-tiles of min(BN, 128) columns:
+//     converter warps   read TMEM (tcgen05.ld), add bias / a residual tensor / ReLU, round to bf16 and stage the
+//                       sub-tile in 128B-swizzled shared memory (two buffers);
+//     store/stat warps  issue the TMA store into the (possibly strided / channel-sliced) output view and accumulate
+//                       the per-channel sum and sum of squares of the stored values for BatchNorm.
+//   The two groups hand buffers over through mbarriers only, so conversion of sub-tile i+1 overlaps the store and
+//   the statistics of sub-tile i.  (ncu on the K=64 1x1 layers showed the old single-group epilogue, not the main
+//   loop, pacing the kernel: ~740 dependent warp instructions per tile on two warps per scheduler.)
 //
-// Roles: warp 0 = TMA producer, warp 1 = MMA issuer, warp 2 = TMEM allocator, warps 4..11 = epilogue.
+// Roles: warp 0 = TMA producer, warp 1 = MMA issuer, warp 2 = TMEM allocator, warps 4..11 = converters,
+//        warps 12..15 = store + statistics.
 //
 // Replaces cuDNN fprop/dgrad and cuBLAS GEMM behind ref:pytorch/unet/model.py:8-14,37-38,68 and
 // torchvision's resnet conv/fc.
@@ -29,8 +35,11 @@
 
 namespace dmpi {
 
-constexpr int kThreads = 384;       // 4 control warps + 8 epilogue warps
-constexpr int kEpiThreads = 256;
+constexpr int kThreads = 512;       // 4 control warps + 8 converter warps + 4 store/statistics warps
+constexpr int kCvtThreads = 256;
+constexpr int kCvtWarps = 8;
+constexpr int kStatThreads = 128;
+constexpr int kStatWarps = 4;
 constexpr int kTileM = 128;
 constexpr int kBlockK = 64;  // bf16 elements = one 128-byte swizzle row
 constexpr int kABytes = kTileM * kBlockK * 2;
@@ -39,19 +48,70 @@ template <int BN>
 struct IgemmCfg {
   // Pipeline depth is what hides the ~1000-cycle L2/HBM latency of the TMA loads: one stage is only 128 (BN=64),
   // 256 (BN=128) or 512 (BN=256) tensor-core cycles of work, so the narrow tiles need the most stages.
-  static constexpr int kStages = BN == 256 ? 3 : (BN == 128 ? 6 : 8);
+  static constexpr int kStages = BN == 256 ? 3 : (BN == 128 ? 5 : 8);
   static constexpr int kBBytes = BN * kBlockK * 2;
-  static constexpr int kOutBytes = kTileM * BN * 2;
-  static constexpr int kOutBufs = BN == 64 ? 2 : 1;  // staged output tiles (double buffered when they fit)
+  static constexpr int kSubN = BN < 128 ? BN : 128;   // columns per staged sub-tile
+  static constexpr int kSubs = BN / kSubN;            // sub-tiles per tile: 1, 1, 2
+  static constexpr int kOutBytes = kTileM * kSubN * 2;
+  static constexpr int kOutBufs = 2;
   static constexpr int kSmemBytes =
       kStages * (kABytes + kBBytes) + kOutBufs * kOutBytes + 1024 /*align slack*/ + 256 /*barriers*/;
   static constexpr int kTmemCols = 2 * BN;
+};
+
+// Walks the persistent tile sequence tile = blockIdx.x + i * gridDim.x without a division per tile: the grid step is
+// decomposed once into (n_blk, tile_w, tile_h, tile_n) digits and added with carries.
+struct TileWalk {
+  int n_blk, tw, th, tn;
+  int s_nb, s_tw, s_th, s_tn;
+  int remaining;
+  __device__ __forceinline__ void init(const ConvKernelParams& p) {
+    const int total = p.num_m_tiles * p.num_n_tiles;
+    const int first = blockIdx.x, step = gridDim.x;
+    remaining = first < total ? (total - first + step - 1) / step : 0;
+    n_blk = first % p.num_n_tiles;
+    int m = first / p.num_n_tiles;
+    tw = m % p.tiles_w;
+    m /= p.tiles_w;
+    th = m % p.tiles_h;
+    tn = m / p.tiles_h;
+    s_nb = step % p.num_n_tiles;
+    int sm = step / p.num_n_tiles;
+    s_tw = sm % p.tiles_w;
+    sm /= p.tiles_w;
+    s_th = sm % p.tiles_h;
+    s_tn = sm / p.tiles_h;
+  }
+  __device__ __forceinline__ void next(const ConvKernelParams& p) {
+    --remaining;
+    n_blk += s_nb;
+    int c = 0;
+    if (n_blk >= p.num_n_tiles) {
+      n_blk -= p.num_n_tiles;
+      c = 1;
+    }
+    tw += s_tw + c;
+    c = 0;
+    if (tw >= p.tiles_w) {
+      tw -= p.tiles_w;
+      c = 1;
+    }
+    th += s_th + c;
+    c = 0;
+    if (th >= p.tiles_h) {
+      th -= p.tiles_h;
+      c = 1;
+    }
+    tn += s_tn + c;
+  }
 };
 
 template <int BN>
 __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constant__ ConvKernelParams p) {
   using Cfg = IgemmCfg<BN>;
   constexpr int S = Cfg::kStages;
+  constexpr int SN = Cfg::kSubN;
+  constexpr int kSubs = Cfg::kSubs;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_a = smem;
@@ -62,7 +122,9 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
   uint64_t* empty = bars + S;
   uint64_t* tfull = bars + 2 * S;
   uint64_t* tempty = bars + 2 * S + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * S + 4);
+  uint64_t* ofull = bars + 2 * S + 4;   // converters -> store/stat warps: sub-tile staged
+  uint64_t* ofree = bars + 2 * S + 6;   // store/stat warps -> converters: buffer may be overwritten
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * S + 8);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -79,7 +141,9 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);
-      mbar_init(&tempty[i], kEpiThreads);
+      mbar_init(&tempty[i], kCvtWarps);
+      mbar_init(&ofull[i], kCvtWarps);
+      mbar_init(&ofree[i], kStatWarps);
     }
     fence_mbar_init();
   }
@@ -89,7 +153,6 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
   tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int total_tiles = p.num_m_tiles * p.num_n_tiles;
   const int num_kb = p.ntaps * p.cblocks;
 
   if (warp == 0) {
@@ -98,13 +161,9 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
       int stage = 0;
       uint32_t phase = 0;
       const uint32_t tx_bytes = static_cast<uint32_t>(p.rows) * 128u + Cfg::kBBytes;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int n_blk = tile % p.num_n_tiles;
-        const int m_blk = tile / p.num_n_tiles;
-        const int tw = m_blk % p.tiles_w;
-        const int th = (m_blk / p.tiles_w) % p.tiles_h;
-        const int tn = m_blk / (p.tiles_w * p.tiles_h);
-        const int w0 = tw * p.box_w, h0 = th * p.box_h, n0 = tn * p.box_n;
+      TileWalk tk;
+      for (tk.init(p); tk.remaining > 0; tk.next(p)) {
+        const int w0 = tk.tw * p.box_w, h0 = tk.th * p.box_h, n0 = tk.tn * p.box_n;
         for (int t = 0; t < p.ntaps; ++t) {
           const CUtensorMap* amap = &p.a_map[p.tap_view[t]];
           const int cw = w0 + p.tap_dw[t], ch = h0 + p.tap_dh[t], koff = p.tap_koff[t];
@@ -112,7 +171,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
             mbar_wait(&empty[stage], phase ^ 1u);
             mbar_arrive_expect_tx(&full[stage], tx_bytes);
             tma_load_4d(smem_a + stage * kABytes, amap, &full[stage], cb * kBlockK, cw, ch, n0);
-            tma_load_2d(smem_b + stage * Cfg::kBBytes, &p.b_map, &full[stage], koff + cb * kBlockK, n_blk * BN);
+            tma_load_2d(smem_b + stage * Cfg::kBBytes, &p.b_map, &full[stage], koff + cb * kBlockK, tk.n_blk * BN);
             if (++stage == S) {
               stage = 0;
               phase ^= 1u;
@@ -130,6 +189,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
+      const int total_tiles = p.num_m_tiles * p.num_n_tiles;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         mbar_wait(&tempty[acc], acc_phase ^ 1u);
         tc_fence_after_sync();
@@ -157,145 +217,222 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
       }
     }
     __syncwarp();
-  } else if (warp >= 4) {
-    // ------------------------------------------------------------------ epilogue (8 warps)
-    // TMEM lane quadrant q = warp % 4 (hardware rule); the two warps of a quadrant split the columns.
-    constexpr int CH = BN / 64;  // 32-column chunks per thread
+  }
+  else if (warp >= 4 && warp < 4 + kCvtWarps) {
+    // ------------------------------------------------------------------ converters (8 warps)
+    // TMEM lane quadrant q = warp % 4 (hardware rule); the two warps of a quadrant split the columns of a sub-tile.
+    constexpr int CHs = SN / 64;  // 32-column chunks per warp and sub-tile: 1 (BN=64) or 2
     const int q = warp & 3;
     const int hf = (warp - 4) >> 2;
     const int row = q * 32 + lane;
-    const int et = threadIdx.x - 128;  // 0..255
-    int acc = 0;
-    uint32_t acc_phase = 0;
     const int wi = row % p.box_w;
     const int hi = (row / p.box_w) % p.box_h;
     const int ni = row / (p.box_w * p.box_h);
-    // BatchNorm statistics: thread -> (column, row slab); running sums live in registers across tiles.
-    constexpr int kStatSlabs = kEpiThreads / BN > 0 ? kEpiThreads / BN : 1;  // 4, 2, 1
-    constexpr int kStatRows = kTileM / kStatSlabs;
-    const int st_col = et % BN;
-    const int st_r0 = (et / BN) * kStatRows;
-    float st_sum = 0.f, st_sq = 0.f;
-    int st_nblk = -1;
-    int buf = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      const int n_blk = tile % p.num_n_tiles;
-      const int m_blk = tile / p.num_n_tiles;
-      const int tw = m_blk % p.tiles_w;
-      const int th = (m_blk / p.tiles_w) % p.tiles_h;
-      const int tn = m_blk / (p.tiles_w * p.tiles_h);
-      const int w0 = tw * p.box_w, h0 = th * p.box_h, n0 = tn * p.box_n;
+    const uint32_t obase = smem_u32(smem_o);
+    const __nv_bfloat16* addend = static_cast<const __nv_bfloat16*>(p.addend);
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    uint32_t u = 0;  // staged sub-tile counter: buffer u & 1, barrier phase (u >> 1) & 1
+    TileWalk tk;
+    for (tk.init(p); tk.remaining > 0; tk.next(p)) {
+      const int w0 = tk.tw * p.box_w, h0 = tk.th * p.box_h, n0 = tk.tn * p.box_n;
       const bool valid = row < p.rows && (w0 + wi) < p.grid_w && (h0 + hi) < p.grid_h && (n0 + ni) < p.grid_n;
-      uint8_t* obuf = smem_o + buf * Cfg::kOutBytes;
+      const __nv_bfloat16* arow = nullptr;
+      if (addend != nullptr && valid)
+        arow = addend + (n0 + ni) * p.add_sn + (h0 + hi) * p.add_sh + (w0 + wi) * p.add_sw;
 
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after_sync();
-      if (p.out_mode == 0) {
-        // the TMA store that last read this buffer must have drained it
-        if (et == 0) {
-          if (Cfg::kOutBufs == 2) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
-          else tma_store_wait_read0();
-        }
-        named_bar_sync(1, kEpiThreads);
-      }
       const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(acc * BN);
 #pragma unroll
-      for (int ci = 0; ci < CH; ++ci) {
-        const int chunk = hf * CH + ci;
-        uint32_t v[32];
-        tmem_ld_32x32(t_addr + chunk * 32, v);
-        tmem_ld_wait();
-        const int col0 = n_blk * BN + chunk * 32;
-        float f[32];
+      for (int sub = 0; sub < kSubs; ++sub) {
+        const uint32_t b = u & 1u;
+        if (p.out_mode == 0) mbar_wait(&ofree[b], ((u >> 1) & 1u) ^ 1u);
+        const uint32_t obuf = obase + b * Cfg::kOutBytes;
 #pragma unroll
-        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
-        if (p.bias_mod > 0) {
-          const int b0 = col0 % p.bias_mod;  // chunks never straddle a bias period (bias_mod % 32 == 0 or col < n_out)
+        for (int ci = 0; ci < CHs; ++ci) {
+          const int cs = hf * CHs + ci;             // chunk inside the sub-tile
+          const int col_t = sub * SN + cs * 32;     // column inside the tile
+          const int col0 = tk.n_blk * BN + col_t;   // global output column
+          uint32_t v[32];
+          tmem_ld_32x32(t_addr + col_t, v);
+          uint4 ad[4];
+          if (arow != nullptr) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            if (col0 + j < p.n_out) f[j] += __ldg(p.bias + ((b0 + j) < p.bias_mod ? (b0 + j) : (b0 + j - p.bias_mod)));
+            for (int i = 0; i < 4; ++i)
+              ad[i] = (col0 + i * 8 < p.n_out) ? ldg_nc128(arow + col0 + i * 8) : make_uint4(0, 0, 0, 0);
           }
-        }
-        if (p.relu) {
+          tmem_ld_wait();
+          float f[32];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
-        }
-        if (p.out_mode == 0) {
-          if (!valid) {
+          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+          if (p.bias_mod > 0) {
+            const int b0 = col0 % p.bias_mod;  // chunks never straddle a bias period (bias_mod % 32 == 0 or col < n_out)
 #pragma unroll
-            for (int j = 0; j < 32; ++j) f[j] = 0.f;
+            for (int j = 0; j < 32; ++j) {
+              if (col0 + j < p.n_out) f[j] += __ldg(p.bias + ((b0 + j) < p.bias_mod ? (b0 + j) : (b0 + j - p.bias_mod)));
+            }
           }
-          // 128-byte swizzle: 16-byte chunk index XOR (row & 7) inside each 64-channel half.
-          uint8_t* half_base = obuf + (chunk >> 1) * (kTileM * 128) + row * 128;
-          const int c16_0 = (chunk & 1) * 4;
+          if (arow != nullptr) {
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            uint4 pk;
-            pk.x = pack_bf16x2(f[i * 8 + 0], f[i * 8 + 1]);
-            pk.y = pack_bf16x2(f[i * 8 + 2], f[i * 8 + 3]);
-            pk.z = pack_bf16x2(f[i * 8 + 4], f[i * 8 + 5]);
-            pk.w = pack_bf16x2(f[i * 8 + 6], f[i * 8 + 7]);
-            const int c16 = (c16_0 + i) ^ (row & 7);
-            *reinterpret_cast<uint4*>(half_base + c16 * 16) = pk;
-          }
-        } else if (valid) {
-          float* dst = p.out_f32 + static_cast<long long>(w0 + wi) * p.out_ld + col0;
+            for (int i = 0; i < 4; ++i) {
+              const uint32_t w[4] = {ad[i].x, ad[i].y, ad[i].z, ad[i].w};
 #pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (col0 + j < p.n_out) dst[j] = f[j];
-        }
-      }
-      tc_fence_before_sync();
-      mbar_arrive(&tempty[acc]);
-      acc ^= 1;
-      if (acc == 0) acc_phase ^= 1u;
-
-      if (p.out_mode == 0) {
-        fence_proxy_async_smem();
-        named_bar_sync(1, kEpiThreads);
-        if (et == 0) {
-          const CUtensorMap* omap = &p.o_map[n_blk / p.nblk_per_oview];
-          const int ch0 = (n_blk % p.nblk_per_oview) * BN;
-#pragma unroll
-          for (int h = 0; h < BN / 64; ++h) {
-            if (n_blk * BN + h * 64 < p.n_out) tma_store_4d(omap, obuf + h * (kTileM * 128), ch0 + h * 64, w0, h0, n0);
-          }
-          tma_store_commit();
-        }
-        if (p.stat_mod > 0) {
-          // Column sums of the bf16 tile just staged (exactly the values that reach memory).
-          if (n_blk != st_nblk) {
-            if (st_nblk >= 0) {
-              const int gcol = st_nblk * BN + st_col;
-              if (gcol < p.n_out) {
-                atomicAdd(p.stat_sum + (gcol % p.stat_mod), st_sum);
-                atomicAdd(p.stat_sq + (gcol % p.stat_mod), st_sq);
+              for (int j = 0; j < 4; ++j) {
+                f[i * 8 + 2 * j] += bf16lo(w[j]);
+                f[i * 8 + 2 * j + 1] += bf16hi(w[j]);
               }
             }
-            st_sum = st_sq = 0.f;
-            st_nblk = n_blk;
           }
-          const uint8_t* hb = obuf + (st_col >> 6) * (kTileM * 128);
-          const int c16 = (st_col & 63) >> 3, within = (st_col & 7) * 2;
-#pragma unroll 8
-          for (int r = st_r0; r < st_r0 + kStatRows; ++r) {
-            const uint16_t raw = *reinterpret_cast<const uint16_t*>(hb + r * 128 + ((c16 ^ (r & 7)) * 16) + within);
-            const float x = __uint_as_float(static_cast<uint32_t>(raw) << 16);
-            st_sum += x;
-            st_sq = fmaf(x, x, st_sq);
+          if (p.relu) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+          }
+          if (p.out_mode == 0) {
+            // 128-byte swizzle: 16-byte chunk index XOR (row & 7) inside each 64-channel half.
+            const uint32_t half_base = obuf + (cs >> 1) * (kTileM * 128) + row * 128;
+            const int c16_0 = (cs & 1) * 4;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              uint32_t pk[4];
+#pragma unroll
+              for (int j = 0; j < 4; ++j)
+                pk[j] = valid ? pack_bf16x2(f[i * 8 + 2 * j], f[i * 8 + 2 * j + 1]) : 0u;
+              const int c16 = (c16_0 + i) ^ (row & 7);
+              sts128(half_base + c16 * 16, pk[0], pk[1], pk[2], pk[3]);
+            }
+          } else if (valid) {
+            float* dst = p.out_f32 + static_cast<long long>(w0 + wi) * p.out_ld + col0;
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (col0 + j < p.n_out) dst[j] = f[j];
           }
         }
-        buf = (buf + 1) % Cfg::kOutBufs;
+        if (sub == kSubs - 1) {
+          // every TMEM read of this accumulator has completed: hand it back to the MMA issuer
+          tc_fence_before_sync();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tempty[acc]);
+        }
+        if (p.out_mode == 0) {
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&ofull[b]);
+        }
+        ++u;
       }
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1u;
     }
-    if (p.out_mode == 0 && p.stat_mod > 0 && st_nblk >= 0) {
-      const int gcol = st_nblk * BN + st_col;
-      if (gcol < p.n_out) {
-        atomicAdd(p.stat_sum + (gcol % p.stat_mod), st_sum);
-        atomicAdd(p.stat_sq + (gcol % p.stat_mod), st_sq);
+  } else if (warp >= 4 + kCvtWarps) {
+    // ------------------------------------------------------------------ TMA store + BatchNorm statistics (4 warps)
+    // thread -> (8-column chunk, row slab) of a staged sub-tile; running sums stay in registers across tiles and
+    // are reduced over the slabs through shared memory once per CTA.
+    constexpr int kC8 = SN / 8;                   // 16-byte column chunks per sub-tile row: 8 or 16
+    constexpr int kSlabs = kStatThreads / kC8;    // 16 or 8
+    constexpr int kSlabRows = kTileM / kSlabs;    // 8 or 16
+    const int st = threadIdx.x - (4 + kCvtWarps) * 32;
+    const int st_c8 = st % kC8;
+    const int st_slab = st / kC8;
+    const bool do_stats = p.stat_mod > 0 && !(p.dbg & 2);
+    float st_sum[kSubs][8], st_sq[kSubs][8];
+#pragma unroll
+    for (int s = 0; s < kSubs; ++s)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) st_sum[s][j] = st_sq[s][j] = 0.f;
+    int st_nblk = -1;
+    const uint32_t obase = smem_u32(smem_o);
+    if (p.out_mode == 0) {
+      uint32_t u = 0;
+      TileWalk tk;
+      for (tk.init(p); tk.remaining > 0; tk.next(p)) {
+        const int w0 = tk.tw * p.box_w, h0 = tk.th * p.box_h, n0 = tk.tn * p.box_n;
+        if (do_stats && tk.n_blk != st_nblk) {
+          // the CTA moves to another N tile (rare: the grid is a multiple of the N-tile count): flush directly
+          if (st_nblk >= 0) {
+#pragma unroll
+            for (int s = 0; s < kSubs; ++s)
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const int gcol = st_nblk * BN + s * SN + st_c8 * 8 + j;
+                if (gcol < p.n_out) {
+                  atomicAdd(p.stat_sum + (gcol % p.stat_mod), st_sum[s][j]);
+                  atomicAdd(p.stat_sq + (gcol % p.stat_mod), st_sq[s][j]);
+                }
+                st_sum[s][j] = st_sq[s][j] = 0.f;
+              }
+          }
+          st_nblk = tk.n_blk;
+        }
+#pragma unroll
+        for (int sub = 0; sub < kSubs; ++sub) {
+          const uint32_t b = u & 1u;
+          const uint32_t obuf = obase + b * Cfg::kOutBytes;
+          mbar_wait(&ofull[b], (u >> 1) & 1u);
+          if (st == 0 && !(p.dbg & 1)) {
+            const CUtensorMap* omap = &p.o_map[tk.n_blk / p.nblk_per_oview];
+            const int ch0 = (tk.n_blk % p.nblk_per_oview) * BN + sub * SN;
+#pragma unroll
+            for (int h = 0; h < SN / 64; ++h) {
+              if (tk.n_blk * BN + sub * SN + h * 64 < p.n_out)
+                tma_store_4d(omap, smem_o + b * Cfg::kOutBytes + h * (kTileM * 128), ch0 + h * 64, w0, h0, n0);
+            }
+            tma_store_commit();
+          }
+          if (do_stats) {
+            // column sums of the bf16 sub-tile just staged (exactly the values that reach memory), 16 bytes per load
+            const uint32_t hb = obuf + (st_c8 >> 3) * (kTileM * 128);
+            const int c16 = st_c8 & 7;
+#pragma unroll
+            for (int rr = 0; rr < kSlabRows; ++rr) {
+              const int r = st_slab * kSlabRows + rr;
+              const uint4 v = lds128(hb + r * 128 + ((c16 ^ (r & 7)) * 16));
+              const uint32_t vi[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const float x0 = bf16lo(vi[j]), x1 = bf16hi(vi[j]);
+                st_sum[sub][2 * j] += x0;
+                st_sum[sub][2 * j + 1] += x1;
+                st_sq[sub][2 * j] = fmaf(x0, x0, st_sq[sub][2 * j]);
+                st_sq[sub][2 * j + 1] = fmaf(x1, x1, st_sq[sub][2 * j + 1]);
+              }
+            }
+          }
+          if (st == 0) tma_store_wait_read0();  // the store has finished reading the buffer
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&ofree[b]);
+          ++u;
+        }
       }
+      if (do_stats && st_nblk >= 0) {
+        // every buffer has been consumed and drained: reuse the staging area as reduction scratch
+        named_bar_sync(2, kStatThreads);
+        float* red = reinterpret_cast<float*>(smem_o);  // [2][kSubs][kSlabs][SN] floats (<= 16 KB)
+#pragma unroll
+        for (int s = 0; s < kSubs; ++s)
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            red[((0 * kSubs + s) * kSlabs + st_slab) * SN + st_c8 * 8 + j] = st_sum[s][j];
+            red[((1 * kSubs + s) * kSlabs + st_slab) * SN + st_c8 * 8 + j] = st_sq[s][j];
+          }
+        named_bar_sync(2, kStatThreads);
+        for (int c = st; c < BN; c += kStatThreads) {
+          const int s = c / SN, cc = c % SN;
+          float t1 = 0.f, t2 = 0.f;
+#pragma unroll
+          for (int sl = 0; sl < kSlabs; ++sl) {
+            t1 += red[((0 * kSubs + s) * kSlabs + sl) * SN + cc];
+            t2 += red[((1 * kSubs + s) * kSlabs + sl) * SN + cc];
+          }
+          const int gcol = st_nblk * BN + c;
+          if (gcol < p.n_out) {
+            atomicAdd(p.stat_sum + (gcol % p.stat_mod), t1);
+            atomicAdd(p.stat_sq + (gcol % p.stat_mod), t2);
+          }
+        }
+      }
+      if (st == 0) tma_store_wait_all0();
     }
-    if (p.out_mode == 0 && et == 0) tma_store_wait_all0();
   }
 
   tc_fence_before_sync();
@@ -416,6 +553,12 @@ extern "C" int dmpi_conv_last_error(char* buf, int buflen) {
 
 extern "C" int dmpi_igemm_run(dmpi_conv_plan* plan, const void* a, const void* b, void* out, const float* bias,
                               float* stat_sum, float* stat_sqsum, void* stream) {
+  return dmpi_igemm_run_add(plan, a, b, out, bias, stat_sum, stat_sqsum, nullptr, 0, 0, 0, stream);
+}
+
+extern "C" int dmpi_igemm_run_add(dmpi_conv_plan* plan, const void* a, const void* b, void* out, const float* bias,
+                                  float* stat_sum, float* stat_sqsum, const void* addend, long long add_sn,
+                                  long long add_sh, long long add_sw, void* stream) {
   const dmpi_conv_desc& d = plan->desc;
   ConvKernelParams& kp = plan->params;
   static const bool trace = getenv("DMPI_TRACE") != nullptr;
@@ -463,6 +606,17 @@ extern "C" int dmpi_igemm_run(dmpi_conv_plan* plan, const void* a, const void* b
     plan->cached_o = out;
     plan->maps_valid = true;
   }
+  static const int dbg = getenv("DMPI_IGEMM_DBG") ? atoi(getenv("DMPI_IGEMM_DBG")) : 0;
+  kp.dbg = dbg;
+  if (addend != nullptr && (d.out_mode != 0 || (reinterpret_cast<uintptr_t>(addend) & 15) != 0 || add_sn % 8 != 0 ||
+                            add_sh % 8 != 0 || add_sw % 8 != 0)) {
+    set_err("igemm: the residual addend needs the bf16 output mode and 16-byte aligned rows");
+    return -9;
+  }
+  kp.addend = addend;
+  kp.add_sn = add_sn;
+  kp.add_sh = add_sh;
+  kp.add_sw = add_sw;
   kp.bias = bias;
   kp.stat_sum = stat_sum;
   kp.stat_sq = stat_sqsum;

@@ -118,11 +118,16 @@ def _get_plan(key, build):
     return ent[0]
 
 
-def _run_igemm(plan, a, b, out, bias, stats):
+def _run_igemm(plan, a, b, out, bias, stats, addend=None, add_strides=(0, 0, 0)):
     s0 = stats[0].data_ptr() if stats is not None else None
     s1 = stats[1].data_ptr() if stats is not None else None
-    rc = N.cuda().dmpi_igemm_run(plan, a.data_ptr(), b.data_ptr(), out.data_ptr(),
-                                 bias.data_ptr() if bias is not None else None, s0, s1, N.stream_ptr())
+    if addend is None:
+        rc = N.cuda().dmpi_igemm_run(plan, a.data_ptr(), b.data_ptr(), out.data_ptr(),
+                                     bias.data_ptr() if bias is not None else None, s0, s1, N.stream_ptr())
+    else:
+        rc = N.cuda().dmpi_igemm_run_add(plan, a.data_ptr(), b.data_ptr(), out.data_ptr(),
+                                         bias.data_ptr() if bias is not None else None, s0, s1, addend.data_ptr(),
+                                         add_strides[0], add_strides[1], add_strides[2], N.stream_ptr())
     N.count_launch()
     _check(rc, "dmpi_igemm_run")
 
@@ -199,8 +204,12 @@ def conv2d_fprop(x: torch.Tensor, w2d: torch.Tensor, R: int, S: int, stride: int
 
 # --------------------------------------------------------------------------------------- dgrad
 def conv2d_dgrad(dy: torch.Tensor, wt2d: torch.Tensor, R: int, S: int, stride: int, pad: int,
-                 in_hw: Tuple[int, int], out: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """dx[n,ih,iw,c] = sum_{r,s,k} dy[n,(ih+pad-r)/stride,(iw+pad-s)/stride,k] * wt2d[c, (r*S+s)*K + k]."""
+                 in_hw: Tuple[int, int], out: Optional[torch.Tensor] = None,
+                 addend: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """dx[n,ih,iw,c] = sum_{r,s,k} dy[n,(ih+pad-r)/stride,(iw+pad-s)/stride,k] * wt2d[c, (r*S+s)*K + k] (+ addend).
+
+    ``addend`` (stride-1 only): a bf16 NHWC tensor of dx's shape added in the kernel epilogue before rounding — the
+    gradient arriving at the same tensor through the residual branch, so no separate add kernel runs."""
     n, oh, ow, k, sn, sh, sw = _nhwc_meta(dy)
     assert k % 64 == 0
     c = wt2d.shape[0]
@@ -243,10 +252,20 @@ def conv2d_dgrad(dy: torch.Tensor, wt2d: torch.Tensor, R: int, S: int, stride: i
             d.n_out, d.bn = c, bn
             return d
 
-        _run_igemm(_get_plan(key, build), dy, wt2d, out, None, None)
+        if addend is not None:
+            an, ah, aw, ac, asn, ash, asw = _nhwc_meta(addend)
+            assert (an, ah, aw, ac) == (n, ih, iw, c), (addend.shape, (n, ih, iw, c))
+            if flat:
+                assert _is_flat(n, ih, iw, asn, ash, asw)
+                strides = (0, 0, asw)
+            else:
+                strides = (asn, ash, asw)
+            _run_igemm(_get_plan(key, build), dy, wt2d, out, None, None, addend, strides)
+        else:
+            _run_igemm(_get_plan(key, build), dy, wt2d, out, None, None)
         return out
 
-    assert stride == 2
+    assert stride == 2 and addend is None
     # Parity decomposition: input pixels with (ih%2, iw%2) == (a, b) only see taps r == (a+pad) mod 2,
     # s == (b+pad) mod 2; on that sub-grid the gather is a dense stride-1 convolution over dy.
     for a in range(2):

@@ -76,6 +76,12 @@ void dmpi_conv_plan_destroy(dmpi_conv_plan* plan);
 int dmpi_igemm_run(dmpi_conv_plan* plan, const void* a, const void* b, void* out, const float* bias,
                    float* stat_sum, float* stat_sqsum, void* stream);
 
+/* Same, plus `addend` (bf16, element strides of its n / h / w axes, channel stride 1, may be NULL): a tensor on the
+ * output's pixel grid that is added to the result before rounding — the residual-branch gradient in a dgrad. */
+int dmpi_igemm_run_add(dmpi_conv_plan* plan, const void* a, const void* b, void* out, const float* bias,
+                       float* stat_sum, float* stat_sqsum, const void* addend, long long add_sn, long long add_sh,
+                       long long add_sw, void* stream);
+
 /* dW += dY^T (*) X.  `dw` must already hold the value to accumulate onto (zero for a fresh gradient). */
 int dmpi_wgrad_run(dmpi_conv_plan* plan, const void* dy, const void* x, float* dw, void* stream);
 

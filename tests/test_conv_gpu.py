@@ -101,6 +101,42 @@ def test_dgrad(case):
     _close(dx, ref, 1e-2, f"dgrad{case}")
 
 
+@pytest.mark.parametrize("case", [(4, 14, 14, 256, 512, 1, 1, 0), (2, 56, 56, 64, 64, 3, 1, 1),
+                                  (1, 32, 32, 192, 64, 3, 1, 1), (3, 28, 28, 128, 256, 1, 1, 0)])
+def test_dgrad_addend(case):
+    """Residual-branch gradient added in the dgrad epilogue (flat 1x1 and boxed 3x3 layouts)."""
+    from deeplearning_mpi_b200.ops import conv as C
+
+    _torch_setup()
+    n, h, w, c, k, R, stride, pad = case
+    dy = _rand(n, h, w, k)
+    wt = _rand(k, c, R, R, scale=(k * R * R) ** -0.5)
+    add = _rand(n, h, w, c)
+    dx = C.conv2d_dgrad(dy, _wt2d(wt), R, R, stride, pad, (h, w), addend=add)
+    ref = torch.nn.grad.conv2d_input((n, c, h, w), wt.float(), dy.float().permute(0, 3, 1, 2), stride=stride,
+                                     padding=pad).permute(0, 2, 3, 1) + add.float()
+    _close(dx, ref, 1e-2, f"dgrad_addend{case}")
+
+
+def test_fprop_many_tiles_per_cta():
+    """More tiles than SMs x pipeline depth: exercises the persistent loop, both accumulator stages, both staging
+    buffers and the register-resident statistics for every tile width (BN = 64, 128, 256)."""
+    from deeplearning_mpi_b200.ops import conv as C
+
+    _torch_setup()
+    for (n, h, c, k) in [(64, 56, 64, 64), (64, 28, 64, 256), (32, 28, 128, 512)]:
+        x = _rand(n, h, h, c)
+        wt = _rand(k, c, 1, 1, scale=c ** -0.5)
+        ssum = torch.zeros(k, device=_dev())
+        ssq = torch.zeros(k, device=_dev())
+        y = C.conv2d_fprop(x, _w2d(wt), 1, 1, 1, 0, stats=(ssum, ssq))
+        ref = (x.float().view(-1, c) @ wt.float().view(k, c).t()).view(n, h, h, k)
+        _close(y, ref, 1e-2, f"fprop_many{(n, h, c, k)}")
+        yf = y.float()
+        _close(ssum, yf.sum(dim=(0, 1, 2)), 2e-3, f"stats_sum_many{(n, h, c, k)}")
+        _close(ssq, (yf * yf).sum(dim=(0, 1, 2)), 2e-3, f"stats_sq_many{(n, h, c, k)}")
+
+
 @pytest.mark.parametrize("case", CONV_CASES)
 def test_wgrad(case):
     from deeplearning_mpi_b200.ops import conv as C
