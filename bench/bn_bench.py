@@ -31,4 +31,4 @@ for (M, C) in [(802816, 64), (802816, 256), (200704, 128), (200704, 512), (50176
     def gbs(passes, t): return passes * nb / t / 1e9
     print(f"M={M:7d} C={C:5d}: fwd {gbs(2,t_f):5.0f} GB/s ({gbs(2,t_f)/peak:.2f})  fwd+res {gbs(3,t_fr):5.0f} ({gbs(3,t_fr)/peak:.2f})  "
           f"bwd(act) {gbs(7,t_b):5.0f} ({gbs(7,t_b)/peak:.2f})  bwd(from_y) {gbs(5,t_by):5.0f} ({gbs(5,t_by)/peak:.2f}) [{t_by*1e6:.0f}us vs {t_b*1e6:.0f}us]  "
-          f"bwd+dres {gbs(8,t_br):5.0f} ({gbs(8,t_br)/peak:.2f})", flush=True)
+          f"bwd+dres {gbs(7,t_br):5.0f} ({gbs(7,t_br)/peak:.2f}) [{t_br*1e6:.0f}us]", flush=True)

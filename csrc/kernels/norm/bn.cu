@@ -138,6 +138,8 @@ struct BnBwdArgs {
 };
 
 // Pass 1: per-channel reductions.  Thread (tx, ty): tx owns 8 consecutive channels, ty strides rows.
+// kFromY selects the ReLU-mask source at compile time (the two variants need different per-channel registers).
+template <bool kFromY>
 __global__ void __launch_bounds__(kBnThreads, 4) bn_bwd_reduce_kernel(const BnBwdArgs a) {
   const int vecC = a.C >> 3;
   const int tx = threadIdx.x % vecC;  // host guarantees vecC divides or is <= blockDim
@@ -151,7 +153,7 @@ __global__ void __launch_bounds__(kBnThreads, 4) bn_bwd_reduce_kernel(const BnBw
     s1[j] = s2[j] = 0.f;
     mean[j] = a.mean[c0 + j];
     sc[j] = sh[j] = 0.f;
-    if (a.relu_from_y) {
+    if (kFromY) {
       const float g = a.gamma ? a.gamma[c0 + j] : 1.f;
       const float b = a.beta ? a.beta[c0 + j] : 0.f;
       const float istd = a.invstd[c0 + j];
@@ -168,11 +170,11 @@ __global__ void __launch_bounds__(kBnThreads, 4) bn_bwd_reduce_kernel(const BnBw
       av[0] = av[1] = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);
       g[0] = *reinterpret_cast<const uint4*>(a.dout + row * a.ld_dout + c0);
       yv[0] = *reinterpret_cast<const uint4*>(a.y + row * a.ldy + c0);
-      if (a.act) av[0] = *reinterpret_cast<const uint4*>(a.act + row * a.ld_act + c0);
+      if (!kFromY && a.act) av[0] = *reinterpret_cast<const uint4*>(a.act + row * a.ld_act + c0);
       if (has2) {
         g[1] = *reinterpret_cast<const uint4*>(a.dout + row2 * a.ld_dout + c0);
         yv[1] = *reinterpret_cast<const uint4*>(a.y + row2 * a.ldy + c0);
-        if (a.act) av[1] = *reinterpret_cast<const uint4*>(a.act + row2 * a.ld_act + c0);
+        if (!kFromY && a.act) av[1] = *reinterpret_cast<const uint4*>(a.act + row2 * a.ld_act + c0);
       }
 #pragma unroll
       for (int u = 0; u < 2; ++u) {
@@ -180,16 +182,23 @@ __global__ void __launch_bounds__(kBnThreads, 4) bn_bwd_reduce_kernel(const BnBw
         const uint32_t gi[4] = {g[u].x, g[u].y, g[u].z, g[u].w}, yi[4] = {yv[u].x, yv[u].y, yv[u].z, yv[u].w},
                        ai[4] = {av[u].x, av[u].y, av[u].z, av[u].w};
 #pragma unroll
+        uint32_t ri[4];
+#pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const bool m0 = a.relu_from_y ? fmaf(bf16lo(yi[j]), sc[2 * j], sh[2 * j]) > 0.f : bf16lo(ai[j]) > 0.f;
-          const bool m1 = a.relu_from_y ? fmaf(bf16hi(yi[j]), sc[2 * j + 1], sh[2 * j + 1]) > 0.f : bf16hi(ai[j]) > 0.f;
+          const bool m0 = kFromY ? fmaf(bf16lo(yi[j]), sc[2 * j], sh[2 * j]) > 0.f : bf16lo(ai[j]) > 0.f;
+          const bool m1 = kFromY ? fmaf(bf16hi(yi[j]), sc[2 * j + 1], sh[2 * j + 1]) > 0.f : bf16hi(ai[j]) > 0.f;
           const float d0 = m0 ? bf16lo(gi[j]) : 0.f;
           const float d1 = m1 ? bf16hi(gi[j]) : 0.f;
           s1[2 * j] += d0;
           s1[2 * j + 1] += d1;
           s2[2 * j] = fmaf(d0, bf16lo(yi[j]) - mean[2 * j], s2[2 * j]);
           s2[2 * j + 1] = fmaf(d1, bf16hi(yi[j]) - mean[2 * j + 1], s2[2 * j + 1]);
+          ri[j] = (m0 ? (gi[j] & 0x0000FFFFu) : 0u) | (m1 ? (gi[j] & 0xFFFF0000u) : 0u);
         }
+        // The masked gradient is the residual branch's gradient; writing it here lets the apply pass read it back
+        // instead of dout + act (one tensor read less).
+        if (!kFromY && a.dres && a.act)
+          *reinterpret_cast<uint4*>(a.dres + (u == 0 ? row : row2) * a.ld_dres + c0) = make_uint4(ri[0], ri[1], ri[2], ri[3]);
       }
     }
   }
@@ -251,14 +260,18 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_kernel(const BnBwdArg
     const long long row2 = row + stride;
     const bool has2 = row2 < a.M;
     uint4 g[2], yv[2], av[2];
-    g[0] = *reinterpret_cast<const uint4*>(a.dout + row * a.ld_dout + c0);
+    // with a residual branch the reduce pass already stored the masked gradient in dres: read that back
+    const bool masked = a.dres != nullptr && a.act != nullptr;
+    const __nv_bfloat16* gsrc = masked ? a.dres : a.dout;
+    const long long ldg = masked ? a.ld_dres : a.ld_dout;
+    g[0] = *reinterpret_cast<const uint4*>(gsrc + row * ldg + c0);
     yv[0] = *reinterpret_cast<const uint4*>(a.y + row * a.ldy + c0);
     av[0] = av[1] = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);
-    if (a.act) av[0] = *reinterpret_cast<const uint4*>(a.act + row * a.ld_act + c0);
+    if (a.act && !masked) av[0] = *reinterpret_cast<const uint4*>(a.act + row * a.ld_act + c0);
     if (has2) {
-      g[1] = *reinterpret_cast<const uint4*>(a.dout + row2 * a.ld_dout + c0);
+      g[1] = *reinterpret_cast<const uint4*>(gsrc + row2 * ldg + c0);
       yv[1] = *reinterpret_cast<const uint4*>(a.y + row2 * a.ldy + c0);
-      if (a.act) av[1] = *reinterpret_cast<const uint4*>(a.act + row2 * a.ld_act + c0);
+      if (a.act && !masked) av[1] = *reinterpret_cast<const uint4*>(a.act + row2 * a.ld_act + c0);
     }
 #pragma unroll
     for (int u = 0; u < 2; ++u) {
@@ -278,7 +291,7 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_kernel(const BnBwdArg
         ri[j] = pack_bf16x2(d0, d1);
       }
       *reinterpret_cast<uint4*>(a.dy + r * a.ld_dy + c0) = make_uint4(oi[0], oi[1], oi[2], oi[3]);
-      if (a.dres) *reinterpret_cast<uint4*>(a.dres + r * a.ld_dres + c0) = make_uint4(ri[0], ri[1], ri[2], ri[3]);
+      if (a.dres && !masked) *reinterpret_cast<uint4*>(a.dres + r * a.ld_dres + c0) = make_uint4(ri[0], ri[1], ri[2], ri[3]);
     }
   }
 }
@@ -440,7 +453,8 @@ extern "C" int dmpi_bn_backward_ex(const void* dout, const void* y, const void* 
   long long blocks = (M + rows_per_block * 8 - 1) / (rows_per_block * 8);
   if (blocks > 148 * 8) blocks = 148 * 8;
   if (blocks < 1) blocks = 1;
-  bn_bwd_reduce_kernel<<<static_cast<int>(blocks), threads, threads * 16 * sizeof(float), s>>>(a);
+  if (a.relu_from_y) bn_bwd_reduce_kernel<true><<<static_cast<int>(blocks), threads, threads * 16 * sizeof(float), s>>>(a);
+  else bn_bwd_reduce_kernel<false><<<static_cast<int>(blocks), threads, threads * 16 * sizeof(float), s>>>(a);
   bn_bwd_apply_kernel<<<stream_grid(M, rows_per_block), threads, 0, s>>>(a);
   return cudaGetLastError() == cudaSuccess ? 0 : -2;
 }

@@ -19,9 +19,17 @@ from ..ops import functional as FN
 from ..utils.arena import ensure_arena
 
 
-def _cba(x, conv, bn, arena, relu=True, residual=None, out_holder=None, stem_hw=None):
+def _cba(x, conv, bn, arena, relu=True, residual=None, out_holder=None, stem_hw=None, link=None, link_role=None):
     return FN.ConvBnAct.apply(x, conv.weight, conv.bias, bn.weight, bn.bias, residual, conv, bn, arena, relu,
-                              out_holder, stem_hw)
+                              out_holder, stem_hw, link, link_role)
+
+
+def _fork_link(x, first_conv):
+    """A GradLink for the fork at a block input, or None when the sum has to stay with autograd (x needs no gradient,
+    or the main branch starts with a strided convolution whose dgrad is parity-decomposed)."""
+    if not (torch.is_grad_enabled() and x.requires_grad) or first_conv.stride[0] != 1:
+        return None
+    return FN.GradLink()
 
 
 class BasicBlock(nn.Module):
@@ -46,11 +54,16 @@ class BasicBlock(nn.Module):
         return self.relu(out + identity)
 
     def forward_sm100(self, x, arena):
-        identity = x
-        out = _cba(x, self.conv1, self.bn1, arena, relu=True)
+        # the identity-branch gradient is added inside conv1's dgrad epilogue (GradLink) instead of by autograd
+        link = _fork_link(x, self.conv1)
+        take = "take" if link is not None else None
+        out = _cba(x, self.conv1, self.bn1, arena, relu=True, link=link, link_role=take)
         if self.downsample is not None:
-            identity = _cba(x, self.downsample[0], self.downsample[1], arena, relu=False)
-        return _cba(out, self.conv2, self.bn2, arena, relu=True, residual=identity)
+            identity = _cba(x, self.downsample[0], self.downsample[1], arena, relu=False, link=link,
+                            link_role="give_dx" if link is not None else None)
+            return _cba(out, self.conv2, self.bn2, arena, relu=True, residual=identity)
+        return _cba(out, self.conv2, self.bn2, arena, relu=True, residual=x, link=link,
+                    link_role="give_dres" if link is not None else None)
 
 
 class Bottleneck(nn.Module):
@@ -78,12 +91,16 @@ class Bottleneck(nn.Module):
         return self.relu(out + identity)
 
     def forward_sm100(self, x, arena):
-        identity = x
-        out = _cba(x, self.conv1, self.bn1, arena, relu=True)
+        link = _fork_link(x, self.conv1)
+        take = "take" if link is not None else None
+        out = _cba(x, self.conv1, self.bn1, arena, relu=True, link=link, link_role=take)
         out = _cba(out, self.conv2, self.bn2, arena, relu=True)
         if self.downsample is not None:
-            identity = _cba(x, self.downsample[0], self.downsample[1], arena, relu=False)
-        return _cba(out, self.conv3, self.bn3, arena, relu=True, residual=identity)
+            identity = _cba(x, self.downsample[0], self.downsample[1], arena, relu=False, link=link,
+                            link_role="give_dx" if link is not None else None)
+            return _cba(out, self.conv3, self.bn3, arena, relu=True, residual=identity)
+        return _cba(out, self.conv3, self.bn3, arena, relu=True, residual=x, link=link,
+                    link_role="give_dres" if link is not None else None)
 
 
 class ResNet(nn.Module):

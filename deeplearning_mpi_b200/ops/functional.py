@@ -21,6 +21,34 @@ def _nb(t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
     return t if t is None else t.detach()
 
 
+class GradLink:
+    """Side channel between the two branches of a residual fork.
+
+    Where a tensor feeds both the main branch (conv1 ...) and the identity branch of a block, autograd would sum the two
+    branch gradients with a separate elementwise kernel (3 tensor passes).  Instead the branch that finishes first in
+    the backward pass (the ``give_*`` role) parks its gradient here and returns None to autograd, and the dgrad of the
+    main branch's first convolution (the ``take`` role) adds it inside its epilogue.  The giver always runs first:
+    it is reachable from the block output without passing through the taker, and it was created later in the forward
+    pass, so the autograd engine schedules it earlier."""
+
+    __slots__ = ("grad",)
+
+    def __init__(self):
+        self.grad = None
+
+    def give(self, g: torch.Tensor) -> None:
+        if self.grad is not None:
+            raise RuntimeError("GradLink: a parked gradient was never consumed")
+        self.grad = g
+
+    def take(self) -> torch.Tensor:
+        g = self.grad
+        if g is None:
+            raise RuntimeError("GradLink: the residual-branch gradient was not produced before the main branch's dgrad")
+        self.grad = None
+        return g
+
+
 class ConvBnAct(torch.autograd.Function):
     """y = Conv2d(x) [+bias];  out = ReLU?(BatchNorm(y) [+ residual]).
 
@@ -30,7 +58,9 @@ class ConvBnAct(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, weight, bias, gamma, beta, residual, conv: nn.Conv2d, bn: nn.BatchNorm2d, arena, relu: bool,
-                out_holder, stem_in_hw):
+                out_holder, stem_in_hw, link=None, link_role=None):
+        # link / link_role: see GradLink.  "take": this conv's dgrad adds link.grad;  "give_dx": dx goes to the link
+        # instead of to autograd;  "give_dres": the residual input's gradient goes to the link.
         # out_holder: None or a 1-element list holding a pre-allocated NHWC view (e.g. a channel slice of a UNet
         # concat buffer).  It is wrapped in a list so that autograd does not treat it as a differentiable input.
         out = out_holder[0] if out_holder else None
@@ -56,6 +86,7 @@ class ConvBnAct(torch.autograd.Function):
                      bn.num_batches_tracked if (track and training) else None, bn.eps, momentum, training, relu)
         ctx.conv, ctx.bn, ctx.arena, ctx.relu, ctx.is_stem = conv, bn, arena, relu, is_stem
         ctx.has_res = residual is not None
+        ctx.link, ctx.link_role = link, link_role
         ctx.params = (weight, bias, gamma, beta)
         ctx.in_hw = (x.shape[1], x.shape[2]) if not is_stem else stem_in_hw
         ctx.save_for_backward(x, y, out, mean, invstd)
@@ -93,9 +124,16 @@ class ConvBnAct(torch.autograd.Function):
         else:
             CV.conv2d_wgrad(dy, x, arena.grad_physical(weight), R, S, stride, pad)
             if ctx.needs_input_grad[0]:
-                dx = CV.conv2d_dgrad(dy, arena.w_transposed(weight), R, S, stride, pad, ctx.in_hw)
+                addend = ctx.link.take() if ctx.link_role == "take" else None
+                dx = CV.conv2d_dgrad(dy, arena.w_transposed(weight), R, S, stride, pad, ctx.in_hw, addend=addend)
         arena.grad_ready(weight)
-        return dx, None, None, None, None, dres, None, None, None, None, None, None
+        if ctx.link_role == "give_dx" and dx is not None:
+            ctx.link.give(dx)
+            dx = None
+        elif ctx.link_role == "give_dres" and dres is not None:
+            ctx.link.give(dres)
+            dres = None
+        return dx, None, None, None, None, dres, None, None, None, None, None, None, None, None
 
 
 class ConvTranspose2x2(torch.autograd.Function):
