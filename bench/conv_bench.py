@@ -45,6 +45,9 @@ for (h, c, k, R, st, pad) in shapes:
     res["fprop"] = timeit(lambda: C.conv2d_fprop(x, w2d, R, R, st, pad, stats=(ssum, ssq)))
     res["dgrad"] = timeit(lambda: C.conv2d_dgrad(dy, wt2d, R, R, st, pad, (h, h)))
     res["wgrad"] = timeit(lambda: C.conv2d_wgrad(dy, x, dw, R, R, st, pad))
+    if st == 1:
+        add = torch.randn_like(x)
+        res["dgrad_add"] = timeit(lambda: C.conv2d_dgrad(dy, wt2d, R, R, st, pad, (h, h), addend=add))
     if not skip_ref:
       res["cudnn_f"] = timeit(lambda: F.conv2d(xc, wc, stride=st, padding=pad))
       res["cudnn_d"] = timeit(lambda: torch.ops.aten.convolution_backward(dyc, xc, wc, None, (st, st), (pad, pad), (1, 1), False, (0, 0), 1, (True, False, False)))

@@ -34,9 +34,10 @@ struct alignas(64) ConvKernelParams {
   float* dw;
   long long w_ld;
   int k_out, c_total, splits, num_k_tiles, num_c_tiles;
-  // igemm: optional tensor added to the result in the epilogue (bf16, same pixel grid as the output, element strides)
-  const void* addend;
-  long long add_sn, add_sh, add_sw;
+  // igemm: optional tensor added to the result in the epilogue (bf16, same pixel grid and box as the output view);
+  // its sub-tiles are TMA-prefetched into the staging buffers two sub-tiles ahead of the converters
+  CUtensorMap add_map;
+  int has_add;
   int dbg;  // DMPI_IGEMM_DBG experiment bits (bench only): 1 no TMA store, 2 no statistics
 };
 
@@ -48,6 +49,7 @@ struct dmpi_conv_plan {
   const void* cached_a;
   const void* cached_b;
   const void* cached_o;
+  const void* cached_add;
   bool maps_valid;
   int num_sms;
 };

@@ -124,7 +124,8 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
   uint64_t* tempty = bars + 2 * S + 2;
   uint64_t* ofull = bars + 2 * S + 4;   // converters -> store/stat warps: sub-tile staged
   uint64_t* ofree = bars + 2 * S + 6;   // store/stat warps -> converters: buffer may be overwritten
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * S + 8);
+  uint64_t* aload = bars + 2 * S + 8;   // addend sub-tile landed in the staging buffer (replaces ofree when used)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * S + 10);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -133,6 +134,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
     for (int i = 0; i < DMPI_MAX_MAPS; ++i) tma_prefetch_desc(&p.a_map[i]);
     tma_prefetch_desc(&p.b_map);
     tma_prefetch_desc(&p.o_map[0]);
+    if (p.has_add) tma_prefetch_desc(&p.add_map);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < S; ++i) {
@@ -144,6 +146,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
       mbar_init(&tempty[i], kCvtWarps);
       mbar_init(&ofull[i], kCvtWarps);
       mbar_init(&ofree[i], kStatWarps);
+      mbar_init(&aload[i], 1);
     }
     fence_mbar_init();
   }
@@ -229,7 +232,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
     const int hi = (row / p.box_w) % p.box_h;
     const int ni = row / (p.box_w * p.box_h);
     const uint32_t obase = smem_u32(smem_o);
-    const __nv_bfloat16* addend = static_cast<const __nv_bfloat16*>(p.addend);
+    const bool has_add = p.has_add != 0;
     int acc = 0;
     uint32_t acc_phase = 0;
     uint32_t u = 0;  // staged sub-tile counter: buffer u & 1, barrier phase (u >> 1) & 1
@@ -237,9 +240,6 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
     for (tk.init(p); tk.remaining > 0; tk.next(p)) {
       const int w0 = tk.tw * p.box_w, h0 = tk.th * p.box_h, n0 = tk.tn * p.box_n;
       const bool valid = row < p.rows && (w0 + wi) < p.grid_w && (h0 + hi) < p.grid_h && (n0 + ni) < p.grid_n;
-      const __nv_bfloat16* arow = nullptr;
-      if (addend != nullptr && valid)
-        arow = addend + (n0 + ni) * p.add_sn + (h0 + hi) * p.add_sh + (w0 + wi) * p.add_sw;
 
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after_sync();
@@ -247,7 +247,11 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
 #pragma unroll
       for (int sub = 0; sub < kSubs; ++sub) {
         const uint32_t b = u & 1u;
-        if (p.out_mode == 0) mbar_wait(&ofree[b], ((u >> 1) & 1u) ^ 1u);
+        if (p.out_mode == 0) {
+          // the buffer is free (and, with a residual addend, already holds the addend sub-tile)
+          if (has_add) mbar_wait(&aload[b], (u >> 1) & 1u);
+          else mbar_wait(&ofree[b], ((u >> 1) & 1u) ^ 1u);
+        }
         const uint32_t obuf = obase + b * Cfg::kOutBytes;
 #pragma unroll
         for (int ci = 0; ci < CHs; ++ci) {
@@ -256,11 +260,12 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
           const int col0 = tk.n_blk * BN + col_t;   // global output column
           uint32_t v[32];
           tmem_ld_32x32(t_addr + col_t, v);
+          const uint32_t half_base = obuf + (cs >> 1) * (kTileM * 128) + row * 128;
+          const int c16_0 = (cs & 1) * 4;
           uint4 ad[4];
-          if (arow != nullptr) {
+          if (has_add) {
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
-              ad[i] = (col0 + i * 8 < p.n_out) ? ldg_nc128(arow + col0 + i * 8) : make_uint4(0, 0, 0, 0);
+            for (int i = 0; i < 4; ++i) ad[i] = lds128(half_base + (((c16_0 + i) ^ (row & 7)) * 16));
           }
           tmem_ld_wait();
           float f[32];
@@ -273,7 +278,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
               if (col0 + j < p.n_out) f[j] += __ldg(p.bias + ((b0 + j) < p.bias_mod ? (b0 + j) : (b0 + j - p.bias_mod)));
             }
           }
-          if (arow != nullptr) {
+          if (has_add) {
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
               const uint32_t w[4] = {ad[i].x, ad[i].y, ad[i].z, ad[i].w};
@@ -290,8 +295,6 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
           }
           if (p.out_mode == 0) {
             // 128-byte swizzle: 16-byte chunk index XOR (row & 7) inside each 64-channel half.
-            const uint32_t half_base = obuf + (cs >> 1) * (kTileM * 128) + row * 128;
-            const int c16_0 = (cs & 1) * 4;
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
               uint32_t pk[4];
@@ -344,6 +347,35 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
     const uint32_t obase = smem_u32(smem_o);
     if (p.out_mode == 0) {
       uint32_t u = 0;
+      // Residual addend: thread 0 walks a second cursor two sub-tiles ahead and TMA-loads the addend sub-tile into
+      // the staging buffer as soon as that buffer has been stored and read for the statistics.
+      const bool has_add = p.has_add != 0;
+      TileWalk ahead;
+      uint32_t ua = 0;
+      auto prefetch_addend = [&]() {  // loads sub-tile `ua` (if any) into buffer ua & 1
+        if (ahead.remaining <= 0) return;
+        const int sub = static_cast<int>(ua % kSubs);
+        const uint32_t b = ua & 1u;
+        const int aw0 = ahead.tw * p.box_w, ah0 = ahead.th * p.box_h, an0 = ahead.tn * p.box_n;
+        const int ch0 = ahead.n_blk * BN + sub * SN;
+        int halves = 0;
+#pragma unroll
+        for (int h = 0; h < SN / 64; ++h) halves += (ch0 + h * 64 < p.n_out) ? 1 : 0;
+        mbar_arrive_expect_tx(&aload[b], static_cast<uint32_t>(halves * p.rows) * 128u);
+#pragma unroll
+        for (int h = 0; h < SN / 64; ++h) {
+          if (ch0 + h * 64 < p.n_out)
+            tma_load_4d(smem_o + b * Cfg::kOutBytes + h * (kTileM * 128), &p.add_map, &aload[b], ch0 + h * 64, aw0, ah0,
+                        an0);
+        }
+        ++ua;
+        if (ua % kSubs == 0) ahead.next(p);
+      };
+      if (has_add && st == 0) {
+        ahead.init(p);
+        prefetch_addend();
+        prefetch_addend();
+      }
       TileWalk tk;
       for (tk.init(p); tk.remaining > 0; tk.next(p)) {
         const int w0 = tk.tw * p.box_w, h0 = tk.th * p.box_h, n0 = tk.tn * p.box_n;
@@ -399,8 +431,14 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
             }
           }
           if (st == 0) tma_store_wait_read0();  // the store has finished reading the buffer
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&ofree[b]);
+          if (has_add) {
+            // nobody may still be reading the buffer when the next addend sub-tile lands in it
+            if (do_stats) named_bar_sync(2, kStatThreads);
+            if (st == 0) prefetch_addend();
+          } else {
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&ofree[b]);
+          }
           ++u;
         }
       }
@@ -504,7 +542,7 @@ extern "C" dmpi_conv_plan* dmpi_conv_plan_create(const dmpi_conv_desc* desc) {
   if (!plan) return nullptr;
   memset(&plan->params, 0, sizeof(plan->params));
   plan->desc = *desc;
-  plan->cached_a = plan->cached_b = plan->cached_o = nullptr;
+  plan->cached_a = plan->cached_b = plan->cached_o = plan->cached_add = nullptr;
   plan->maps_valid = false;
   plan->num_sms = 0;
   ConvKernelParams& kp = plan->params;
@@ -608,15 +646,26 @@ extern "C" int dmpi_igemm_run_add(dmpi_conv_plan* plan, const void* a, const voi
   }
   static const int dbg = getenv("DMPI_IGEMM_DBG") ? atoi(getenv("DMPI_IGEMM_DBG")) : 0;
   kp.dbg = dbg;
-  if (addend != nullptr && (d.out_mode != 0 || (reinterpret_cast<uintptr_t>(addend) & 15) != 0 || add_sn % 8 != 0 ||
-                            add_sh % 8 != 0 || add_sw % 8 != 0)) {
-    set_err("igemm: the residual addend needs the bf16 output mode and 16-byte aligned rows");
-    return -9;
+  kp.has_add = 0;
+  if (addend != nullptr) {
+    if (d.out_mode != 0 || d.o_nviews != 1) {
+      set_err("igemm: the residual addend needs the bf16 output mode and a single output view");
+      return -9;
+    }
+    if (plan->cached_add != addend) {
+      dmpi_tensor4 av = d.o_view[0];  // same pixel grid and channel count as the output, its own strides
+      av.offset = 0;
+      av.strides[0] = add_sw;
+      av.strides[1] = add_sh;
+      av.strides[2] = add_sn;
+      if (encode_view(&kp.add_map, addend, av, 64, d.box_w, d.box_h, d.box_n)) {
+        set_err("igemm: addend tensor map encode failed");
+        return -9;
+      }
+      plan->cached_add = addend;
+    }
+    kp.has_add = 1;
   }
-  kp.addend = addend;
-  kp.add_sn = add_sn;
-  kp.add_sh = add_sh;
-  kp.add_sw = add_sw;
   kp.bias = bias;
   kp.stat_sum = stat_sum;
   kp.stat_sq = stat_sqsum;

@@ -257,7 +257,8 @@ def conv2d_dgrad(dy: torch.Tensor, wt2d: torch.Tensor, R: int, S: int, stride: i
             assert (an, ah, aw, ac) == (n, ih, iw, c), (addend.shape, (n, ih, iw, c))
             if flat:
                 assert _is_flat(n, ih, iw, asn, ash, asw)
-                strides = (0, 0, asw)
+                m = n * ih * iw
+                strides = (m * asw, m * asw, asw)  # same (c, m, 1, 1) view convention as the flat output
             else:
                 strides = (asn, ash, asw)
             _run_igemm(_get_plan(key, build), dy, wt2d, out, None, None, addend, strides)
