@@ -15,6 +15,7 @@ This module only builds descriptors and caches plans; all math runs in the nativ
 from __future__ import annotations
 
 import ctypes as C
+import os
 import functools
 from typing import Optional, Sequence, Tuple
 
@@ -87,10 +88,16 @@ def _is_flat(n, h, w, sn, sh, sw) -> bool:
     return sh == w * sw and (n == 1 or sn == h * sh)
 
 
-def _pick_bn(n_out: int) -> int:
+_BN256_MIN_K = int(os.environ.get("DMPI_BN256_MIN_K", "256"))
+
+
+def _pick_bn(n_out: int, ktot: int = 1 << 30) -> int:
+    """N tile of the implicit GEMM.  256-wide tiles halve the A-operand traffic per FLOP (the 3x3 and deep 1x1 layers
+    are bound by L2 -> SM operand bandwidth: 83 -> 56 us on 14x14x256 3x3), but with a short reduction (K <= 128) the
+    tile is epilogue-paced and two 128-wide tiles pipeline better (58 vs 73 us on 28x28 128 -> 512)."""
     if n_out <= 64:
         return 64
-    if n_out % 256 == 0 and n_out >= 512:
+    if n_out % 256 == 0 and ktot >= _BN256_MIN_K:
         return 256
     return 128
 
@@ -149,7 +156,7 @@ def conv2d_fprop(x: torch.Tensor, w2d: torch.Tensor, R: int, S: int, stride: int
     assert (on, ohh, oww, oc) == (n, oh, ow, kout)
     flat = (R == 1 and S == 1 and stride == 1 and pad == 0 and _is_flat(n, h, w, sn, sh, sw)
             and _is_flat(n, oh, ow, osn, osh, osw))
-    bn = _pick_bn(kout)
+    bn = _pick_bn(kout, R * S * c)
     key = ("fprop", n, h, w, c, sn, sh, sw, kout, R, S, stride, pad, osn, osh, osw, bias is not None,
            stats is not None, relu, bn)
 
@@ -219,7 +226,7 @@ def conv2d_dgrad(dy: torch.Tensor, wt2d: torch.Tensor, R: int, S: int, stride: i
         out = (torch.zeros if (stride == 2 and R == 1) else torch.empty)(
             (n, ih, iw, c), dtype=torch.bfloat16, device=dy.device)
     _, _, _, _, osn, osh, osw = _nhwc_meta(out)
-    bn = _pick_bn(c)
+    bn = _pick_bn(c, (R * S if stride == 1 else max(1, (R * S) // 4)) * k)
     if stride == 1:
         flat = R == 1 and S == 1 and pad == 0 and _is_flat(n, oh, ow, sn, sh, sw) and _is_flat(n, ih, iw, osn, osh, osw)
         key = ("dgrad1", n, oh, ow, k, sn, sh, sw, c, R, S, pad, osn, osh, osw, bn)
@@ -471,7 +478,7 @@ def convt2x2_dgrad(dout: torch.Tensor, wt: torch.Tensor, out: Optional[torch.Ten
     if out is None:
         out = torch.empty((n, h, w, c), dtype=torch.bfloat16, device=dout.device)
     _, _, _, _, osn, osh, osw = _nhwc_meta(out)
-    bn = _pick_bn(c)
+    bn = _pick_bn(c, 4 * k)
     key = ("convt_dgrad", n, oh, ow, k, sn, sh, sw, c, osn, osh, osw, bn)
 
     def build():
