@@ -38,7 +38,7 @@ struct alignas(64) ConvKernelParams {
   // its sub-tiles are TMA-prefetched into the staging buffers two sub-tiles ahead of the converters
   CUtensorMap add_map;
   int has_add;
-  int dbg;  // DMPI_IGEMM_DBG experiment bits (bench only): 1 no TMA store, 2 no statistics
+  int dbg;  // DMPI_IGEMM_DBG experiment bits (bench only): 1 no TMA store, 2 no statistics, 4 no loads, 8 no MMAs
 };
 
 }  // namespace dmpi

@@ -44,12 +44,17 @@ constexpr int kTileM = 128;
 constexpr int kBlockK = 64;  // bf16 elements = one 128-byte swizzle row
 constexpr int kABytes = kTileM * kBlockK * 2;
 
-template <int BN>
+// CG = 1: one CTA per tile.  CG = 2: a CTA pair (cluster of two SMs of one TPC) works on a 256-row tile with
+// tcgen05.mma.cta_group::2 — each CTA loads its own 128 A rows and only HALF of the B tile (the tensor cores of both
+// SMs read both halves), which cuts the L2 -> SM operand traffic per FLOP by a third (BN=256) that bounds the
+// deep layers (~6300 B/clk chip-wide).
+template <int BN, int CG>
 struct IgemmCfg {
   // Pipeline depth is what hides the ~1000-cycle L2/HBM latency of the TMA loads: one stage is only 128 (BN=64),
   // 256 (BN=128) or 512 (BN=256) tensor-core cycles of work, so the narrow tiles need the most stages.
-  static constexpr int kStages = BN == 256 ? 3 : (BN == 128 ? 5 : 8);
-  static constexpr int kBBytes = BN * kBlockK * 2;
+  static constexpr int kStages = CG == 2 ? (BN == 256 ? 5 : 6) : (BN == 256 ? 3 : (BN == 128 ? 5 : 8));
+  static constexpr int kBRows = BN / CG;              // B rows (filters) this CTA loads per K block
+  static constexpr int kBBytes = kBRows * kBlockK * 2;
   static constexpr int kSubN = BN < 128 ? BN : 128;   // columns per staged sub-tile
   static constexpr int kSubs = BN / kSubN;            // sub-tiles per tile: 1, 1, 2
   static constexpr int kOutBytes = kTileM * kSubN * 2;
@@ -57,26 +62,32 @@ struct IgemmCfg {
   static constexpr int kSmemBytes =
       kStages * (kABytes + kBBytes) + kOutBufs * kOutBytes + 1024 /*align slack*/ + 256 /*barriers*/;
   static constexpr int kTmemCols = 2 * BN;
+  static_assert(CG == 1 || BN >= 128, "CTA pairs are used for the wide tiles only");
 };
 
-// Walks the persistent tile sequence tile = blockIdx.x + i * gridDim.x without a division per tile: the grid step is
-// decomposed once into (n_blk, tile_w, tile_h, tile_n) digits and added with carries.
+// Walks the persistent tile sequence without a division per tile: the grid step is decomposed once into
+// (n_blk, tile_w, tile_h, tile_n) digits and added with carries.  With CTA pairs the sequence runs over pair tiles
+// (n_blk, m_pair) per cluster and the CTA of rank r owns M tile 2 * m_pair + r (possibly one past the end: such a
+// tile only loads zero fill and stores nothing).
 struct TileWalk {
   int n_blk, tw, th, tn;
   int s_nb, s_tw, s_th, s_tn;
   int remaining;
-  __device__ __forceinline__ void init(const ConvKernelParams& p) {
-    const int total = p.num_m_tiles * p.num_n_tiles;
-    const int first = blockIdx.x, step = gridDim.x;
+  int cg;
+  __device__ __forceinline__ void init(const ConvKernelParams& p, int cg_, int rank) {
+    cg = cg_;
+    const int m_units = (p.num_m_tiles + cg - 1) / cg;  // M tiles or M-tile pairs
+    const int total = m_units * p.num_n_tiles;
+    const int first = blockIdx.x / cg, step = gridDim.x / cg;
     remaining = first < total ? (total - first + step - 1) / step : 0;
     n_blk = first % p.num_n_tiles;
-    int m = first / p.num_n_tiles;
+    int m = (first / p.num_n_tiles) * cg + rank;
     tw = m % p.tiles_w;
     m /= p.tiles_w;
     th = m % p.tiles_h;
     tn = m / p.tiles_h;
     s_nb = step % p.num_n_tiles;
-    int sm = step / p.num_n_tiles;
+    int sm = (step / p.num_n_tiles) * cg;
     s_tw = sm % p.tiles_w;
     sm /= p.tiles_w;
     s_th = sm % p.tiles_h;
@@ -85,30 +96,27 @@ struct TileWalk {
   __device__ __forceinline__ void next(const ConvKernelParams& p) {
     --remaining;
     n_blk += s_nb;
-    int c = 0;
+    tw += s_tw;
     if (n_blk >= p.num_n_tiles) {
       n_blk -= p.num_n_tiles;
-      c = 1;
+      tw += cg;
     }
-    tw += s_tw + c;
-    c = 0;
-    if (tw >= p.tiles_w) {
+    th += s_th;
+    tn += s_tn;
+    while (tw >= p.tiles_w) {
       tw -= p.tiles_w;
-      c = 1;
+      ++th;
     }
-    th += s_th + c;
-    c = 0;
-    if (th >= p.tiles_h) {
+    while (th >= p.tiles_h) {
       th -= p.tiles_h;
-      c = 1;
+      ++tn;
     }
-    tn += s_tn + c;
   }
 };
 
-template <int BN>
+template <int BN, int CG>
 __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constant__ ConvKernelParams p) {
-  using Cfg = IgemmCfg<BN>;
+  using Cfg = IgemmCfg<BN, CG>;
   constexpr int S = Cfg::kStages;
   constexpr int SN = Cfg::kSubN;
   constexpr int kSubs = Cfg::kSubs;
@@ -129,6 +137,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const int rank = CG == 2 ? static_cast<int>(cluster_ctarank()) : 0;  // rank 0 of a pair is the MMA leader
 
   if (warp == 0 && lane == 0) {
     for (int i = 0; i < DMPI_MAX_MAPS; ++i) tma_prefetch_desc(&p.a_map[i]);
@@ -138,21 +147,25 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < S; ++i) {
-      mbar_init(&full[i], 1);
+      mbar_init(&full[i], CG);  // pair: the leader's expect_tx arrival + the peer's plain arrival
       mbar_init(&empty[i], 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);
-      mbar_init(&tempty[i], kCvtWarps);
+      mbar_init(&tempty[i], CG * kCvtWarps);  // pair: the converters of both CTAs release the leader's barrier
       mbar_init(&ofull[i], kCvtWarps);
       mbar_init(&ofree[i], kStatWarps);
       mbar_init(&aload[i], 1);
     }
     fence_mbar_init();
   }
-  if (warp == 2) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  if (warp == 2) {
+    if (CG == 2) tmem_alloc_pair<Cfg::kTmemCols>(tmem_slot);
+    else tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  }
   tc_fence_before_sync();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all();  // the peer's barriers must be initialised before anything signals them
+  else __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -165,16 +178,29 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
       uint32_t phase = 0;
       const uint32_t tx_bytes = static_cast<uint32_t>(p.rows) * 128u + Cfg::kBBytes;
       TileWalk tk;
-      for (tk.init(p); tk.remaining > 0; tk.next(p)) {
+      for (tk.init(p, CG, rank); tk.remaining > 0; tk.next(p)) {
         const int w0 = tk.tw * p.box_w, h0 = tk.th * p.box_h, n0 = tk.tn * p.box_n;
         for (int t = 0; t < p.ntaps; ++t) {
           const CUtensorMap* amap = &p.a_map[p.tap_view[t]];
           const int cw = w0 + p.tap_dw[t], ch = h0 + p.tap_dh[t], koff = p.tap_koff[t];
           for (int cb = 0; cb < p.cblocks; ++cb) {
-            mbar_wait(&empty[stage], phase ^ 1u);
-            mbar_arrive_expect_tx(&full[stage], tx_bytes);
-            tma_load_4d(smem_a + stage * kABytes, amap, &full[stage], cb * kBlockK, cw, ch, n0);
-            tma_load_2d(smem_b + stage * Cfg::kBBytes, &p.b_map, &full[stage], koff + cb * kBlockK, tk.n_blk * BN);
+            mbar_wait_spin(&empty[stage], phase ^ 1u);
+            if (p.dbg & 4) {  // experiment: no loads, barriers only (MMA runs on stale shared memory)
+              if (CG == 1 || rank == 0) mbar_arrive(&full[stage]);
+              else mbar_arrive_cluster(mapa_u32(smem_u32(&full[stage]), 0));
+            } else if (CG == 1) {
+              mbar_arrive_expect_tx(&full[stage], tx_bytes);
+              tma_load_4d(smem_a + stage * kABytes, amap, &full[stage], cb * kBlockK, cw, ch, n0);
+              tma_load_2d(smem_b + stage * Cfg::kBBytes, &p.b_map, &full[stage], koff + cb * kBlockK, tk.n_blk * BN);
+            } else {
+              // both CTAs report to the leader's barrier; the leader registers the bytes of the pair
+              const uint32_t lead_full = mapa_u32(smem_u32(&full[stage]), 0);
+              if (rank == 0) mbar_arrive_expect_tx(&full[stage], 2 * tx_bytes);
+              else mbar_arrive_cluster(lead_full);
+              tma_load_4d_pair(smem_a + stage * kABytes, amap, lead_full, cb * kBlockK, cw, ch, n0);
+              tma_load_2d_pair(smem_b + stage * Cfg::kBBytes, &p.b_map, lead_full, koff + cb * kBlockK,
+                               tk.n_blk * BN + rank * Cfg::kBRows);
+            }
             if (++stage == S) {
               stage = 0;
               phase ^= 1u;
@@ -186,35 +212,40 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
     __syncwarp();
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(kTileM, BN, 0, 0);
+    if (lane == 0 && rank == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(kTileM * CG, BN, 0, 0);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      const int total_tiles = p.num_m_tiles * p.num_n_tiles;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        mbar_wait(&tempty[acc], acc_phase ^ 1u);
+      TileWalk tk;
+      for (tk.init(p, CG, rank); tk.remaining > 0; --tk.remaining) {  // only the count matters here
+        mbar_wait_spin(&tempty[acc], acc_phase ^ 1u);
         tc_fence_after_sync();
         const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
         for (int kb = 0; kb < num_kb; ++kb) {
-          mbar_wait(&full[stage], phase);
+          mbar_wait_spin(&full[stage], phase);
           tc_fence_after_sync();
           const uint32_t a_addr = smem_u32(smem_a + stage * kABytes);
           const uint32_t b_addr = smem_u32(smem_b + stage * Cfg::kBBytes);
 #pragma unroll
           for (int k = 0; k < kBlockK / 16; ++k) {
+            if (p.dbg & 8) break;  // experiment: no MMAs, commits only (load pipeline alone)
             const uint64_t adesc = umma_smem_desc(a_addr + k * 32, 0, 1024);
             const uint64_t bdesc = umma_smem_desc(b_addr + k * 32, 0, 1024);
-            umma_bf16(d_tmem, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+            if (CG == 2) umma_bf16_pair(d_tmem, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+            else umma_bf16(d_tmem, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
           }
-          umma_commit(&empty[stage]);
+          // frees the stage in both CTAs of a pair (each producer waits on its own barrier)
+          if (CG == 2) umma_commit_pair(&empty[stage], 0b11);
+          else umma_commit(&empty[stage]);
           if (++stage == S) {
             stage = 0;
             phase ^= 1u;
           }
         }
-        umma_commit(&tfull[acc]);
+        if (CG == 2) umma_commit_pair(&tfull[acc], 0b11);
+        else umma_commit(&tfull[acc]);
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1u;
       }
@@ -236,8 +267,9 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
     int acc = 0;
     uint32_t acc_phase = 0;
     uint32_t u = 0;  // staged sub-tile counter: buffer u & 1, barrier phase (u >> 1) & 1
+    const uint32_t lead_tempty = CG == 2 ? mapa_u32(smem_u32(&tempty[0]), 0) : 0u;
     TileWalk tk;
-    for (tk.init(p); tk.remaining > 0; tk.next(p)) {
+    for (tk.init(p, CG, rank); tk.remaining > 0; tk.next(p)) {
       const int w0 = tk.tw * p.box_w, h0 = tk.th * p.box_h, n0 = tk.tn * p.box_n;
       const bool valid = row < p.rows && (w0 + wi) < p.grid_w && (h0 + hi) < p.grid_h && (n0 + ni) < p.grid_n;
 
@@ -315,7 +347,10 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
           // every TMEM read of this accumulator has completed: hand it back to the MMA issuer
           tc_fence_before_sync();
           __syncwarp();
-          if (lane == 0) mbar_arrive(&tempty[acc]);
+          if (lane == 0) {
+            if (CG == 2) mbar_arrive_cluster(lead_tempty + acc * 8);
+            else mbar_arrive(&tempty[acc]);
+          }
         }
         if (p.out_mode == 0) {
           fence_proxy_async_smem();
@@ -372,12 +407,12 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
         if (ua % kSubs == 0) ahead.next(p);
       };
       if (has_add && st == 0) {
-        ahead.init(p);
+        ahead.init(p, CG, rank);
         prefetch_addend();
         prefetch_addend();
       }
       TileWalk tk;
-      for (tk.init(p); tk.remaining > 0; tk.next(p)) {
+      for (tk.init(p, CG, rank); tk.remaining > 0; tk.next(p)) {
         const int w0 = tk.tw * p.box_w, h0 = tk.th * p.box_h, n0 = tk.tn * p.box_n;
         if (do_stats && tk.n_blk != st_nblk) {
           // the CTA moves to another N tile (rare: the grid is a multiple of the N-tile count): flush directly
@@ -474,8 +509,13 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
   }
 
   tc_fence_before_sync();
-  __syncthreads();
-  if (warp == 2) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+  if (CG == 2) {
+    cluster_sync_all();  // the leader's MMAs read the peer's shared memory and write its TMEM until the last commit
+    if (warp == 2) tmem_dealloc_pair<Cfg::kTmemCols>(tmem_base);
+  } else {
+    __syncthreads();
+    if (warp == 2) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+  }
 }
 
 // ------------------------------------------------------------------------------------------ host
@@ -500,27 +540,70 @@ static int encode_view(CUtensorMap* map, const void* base, const dmpi_tensor4& v
   return encode_bf16_map(map, ptr, 4, v.dims, v.strides, box);
 }
 
-template <int BN>
+template <int BN, int CG>
 static int launch_igemm(const ConvKernelParams& kp, int num_sms, cudaStream_t stream) {
+  using Cfg = IgemmCfg<BN, CG>;
   static bool attr_set = false;
+  static int max_clusters = 0;
   if (!attr_set) {
     cudaError_t e =
-        cudaFuncSetAttribute(igemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, IgemmCfg<BN>::kSmemBytes);
+        cudaFuncSetAttribute(igemm_kernel<BN, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
     if (getenv("DMPI_TRACE")) fprintf(stderr, "[dmpi] cudaFuncSetAttribute: %s\n", cudaGetErrorString(e));
     if (e != cudaSuccess) {
       set_err(cudaGetErrorString(e));
       return -10;
     }
+    if (CG == 2) {
+      // how many CTA pairs the device can hold at once (a pair occupies the two SMs of one TPC)
+      cudaLaunchConfig_t qc = {};
+      qc.gridDim = dim3(num_sms, 1, 1);
+      qc.blockDim = dim3(kThreads, 1, 1);
+      qc.dynamicSmemBytes = Cfg::kSmemBytes;
+      cudaLaunchAttribute qa[1];
+      qa[0].id = cudaLaunchAttributeClusterDimension;
+      qa[0].val.clusterDim.x = 2;
+      qa[0].val.clusterDim.y = 1;
+      qa[0].val.clusterDim.z = 1;
+      qc.attrs = qa;
+      qc.numAttrs = 1;
+      int n = 0;
+      e = cudaOccupancyMaxActiveClusters(&n, igemm_kernel<BN, CG>, &qc);
+      if (e != cudaSuccess || n <= 0) {
+        cudaGetLastError();
+        n = num_sms / 2;
+      }
+      max_clusters = n < num_sms / 2 ? n : num_sms / 2;
+      if (getenv("DMPI_TRACE")) fprintf(stderr, "[dmpi] max active CTA pairs: %d\n", max_clusters);
+    }
     attr_set = true;
   }
-  const int total = kp.num_m_tiles * kp.num_n_tiles;
-  int grid = total < num_sms ? total : num_sms;
+  const int units = (CG == 2 ? (kp.num_m_tiles + 1) / 2 : kp.num_m_tiles) * kp.num_n_tiles;  // tiles or pair tiles
+  const int slots = CG == 2 ? max_clusters : num_sms;
+  int grid = units < slots ? units : slots;
   // A grid that is a multiple of the N-tile count keeps n_blk fixed per CTA, so the BatchNorm partial sums stay
-  // in registers for the whole kernel (one atomic flush per CTA).
-  if (grid == num_sms && kp.num_n_tiles > 1 && kp.num_n_tiles <= num_sms) grid = (num_sms / kp.num_n_tiles) * kp.num_n_tiles;
-  if (getenv("DMPI_TRACE")) fprintf(stderr, "[dmpi] launch grid=%d smem=%d params=%zu bytes\n", grid, IgemmCfg<BN>::kSmemBytes, sizeof(kp));
-  igemm_kernel<BN><<<grid, kThreads, IgemmCfg<BN>::kSmemBytes, stream>>>(kp);
-  cudaError_t e = cudaGetLastError();
+  // in registers for the whole kernel (one flush per CTA).
+  if (grid == slots && kp.num_n_tiles > 1 && kp.num_n_tiles <= slots) grid = (slots / kp.num_n_tiles) * kp.num_n_tiles;
+  grid *= CG;
+  if (getenv("DMPI_TRACE")) fprintf(stderr, "[dmpi] launch grid=%d smem=%d params=%zu bytes\n", grid, Cfg::kSmemBytes, sizeof(kp));
+  cudaError_t e;
+  if (CG == 2) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid, 1, 1);
+    cfg.blockDim = dim3(kThreads, 1, 1);
+    cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    e = cudaLaunchKernelEx(&cfg, igemm_kernel<BN, CG>, kp);
+  } else {
+    igemm_kernel<BN, CG><<<grid, kThreads, Cfg::kSmemBytes, stream>>>(kp);
+    e = cudaGetLastError();
+  }
   if (getenv("DMPI_TRACE")) {
     fprintf(stderr, "[dmpi] launched: %s\n", cudaGetErrorString(e));
     cudaError_t se = cudaDeviceSynchronize();
@@ -623,7 +706,7 @@ extern "C" int dmpi_igemm_run_add(dmpi_conv_plan* plan, const void* a, const voi
     {
       int64_t dims[2] = {d.b_k, d.b_rows};
       int64_t strides[1] = {d.b_k};
-      int box[2] = {kBlockK, d.bn};
+      int box[2] = {kBlockK, d.cta_group == 2 ? d.bn / 2 : d.bn};  // a CTA of a pair loads half of the B tile
       if (encode_bf16_map(&kp.b_map, b, 2, dims, strides, box)) {
         set_err("igemm: B tensor map encode failed");
         return -5;
@@ -682,9 +765,15 @@ extern "C" int dmpi_igemm_run_add(dmpi_conv_plan* plan, const void* a, const voi
   if (plan->num_sms == 0) plan->num_sms = device_sm_count();
   if (trace) fprintf(stderr, "[dmpi] sms=%d launching\n", plan->num_sms);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (d.cta_group == 2) {
+    if (d.bn == 128) return launch_igemm<128, 2>(kp, plan->num_sms, s);
+    if (d.bn == 256) return launch_igemm<256, 2>(kp, plan->num_sms, s);
+    set_err("igemm: CTA pairs need bn 128 or 256");
+    return -2;
+  }
   switch (d.bn) {
-    case 64: return launch_igemm<64>(kp, plan->num_sms, s);
-    case 128: return launch_igemm<128>(kp, plan->num_sms, s);
-    default: return launch_igemm<256>(kp, plan->num_sms, s);
+    case 64: return launch_igemm<64, 1>(kp, plan->num_sms, s);
+    case 128: return launch_igemm<128, 1>(kp, plan->num_sms, s);
+    default: return launch_igemm<256, 1>(kp, plan->num_sms, s);
   }
 }

@@ -45,6 +45,7 @@ class ConvDesc(C.Structure):
         ("w_ld", C.c_int64),
         ("tap_woff", C.c_int * MAX_TAPS),
         ("splits", C.c_int),
+        ("cta_group", C.c_int),
     ]
 
 
@@ -138,6 +139,7 @@ def _bind_cuda(lib) -> None:
     _sig(lib, "dmpi_igemm_run", I, [VP, VP, VP, VP, VP, VP, VP, VP])
     _sig(lib, "dmpi_igemm_run_add", I, [VP, VP, VP, VP, VP, VP, VP, VP, I64, I64, I64, VP])
     _sig(lib, "dmpi_wgrad_run", I, [VP, VP, VP, VP, VP])
+    _sig(lib, "dmpi_umma_probe", I, [VP, VP, VP, I, I, I, VP])
     _sig(lib, "dmpi_conv_last_error", I, [C.c_char_p, I])
     # norm
     _sig(lib, "dmpi_bn_forward", I, [VP, VP, VP, I64, I, I64, I64, I64, VP, VP, VP, VP, VP, VP, VP, VP, VP, F, F, I, I, VP])

@@ -139,6 +139,20 @@ def _run_igemm(plan, a, b, out, bias, stats, addend=None, add_strides=(0, 0, 0))
     _check(rc, "dmpi_igemm_run")
 
 
+_CTA_GROUP = int(os.environ.get("DMPI_CTA_GROUP", "0"))  # 0: automatic, 1 / 2: forced (where legal)
+_CG2_MIN_K = int(os.environ.get("DMPI_CG2_MIN_K", "256"))
+
+
+def _pick_cg(bn: int, ktot: int) -> int:
+    """CTA pairs (tcgen05.mma.cta_group::2): each CTA loads half of the weight tile, so the operand traffic per FLOP
+    drops by 1/4 (BN=128) to 1/3 (BN=256).  Worth it where the main loop, not the epilogue, paces the kernel."""
+    if bn < 128 or _CTA_GROUP == 1:
+        return 1
+    if _CTA_GROUP == 2:
+        return 2
+    return 2 if ktot >= _CG2_MIN_K else 1
+
+
 # --------------------------------------------------------------------------------------- fprop
 def conv2d_fprop(x: torch.Tensor, w2d: torch.Tensor, R: int, S: int, stride: int = 1, pad: int = 0,
                  out: Optional[torch.Tensor] = None, bias: Optional[torch.Tensor] = None,
@@ -157,8 +171,9 @@ def conv2d_fprop(x: torch.Tensor, w2d: torch.Tensor, R: int, S: int, stride: int
     flat = (R == 1 and S == 1 and stride == 1 and pad == 0 and _is_flat(n, h, w, sn, sh, sw)
             and _is_flat(n, oh, ow, osn, osh, osw))
     bn = _pick_bn(kout, R * S * c)
+    cg = _pick_cg(bn, R * S * c)
     key = ("fprop", n, h, w, c, sn, sh, sw, kout, R, S, stride, pad, osn, osh, osw, bias is not None,
-           stats is not None, relu, bn)
+           stats is not None, relu, bn, cg)
 
     def build():
         d = N.ConvDesc()
@@ -199,6 +214,7 @@ def conv2d_fprop(x: torch.Tensor, w2d: torch.Tensor, R: int, S: int, stride: int
         d.b_rows, d.b_k = kout, R * S * c
         d.nblk_per_oview = 0
         d.n_out, d.bn = kout, bn
+        d.cta_group = cg
         d.bias_mod = kout if bias is not None else 0
         d.stat_mod = kout if stats is not None else 0
         d.relu = int(relu)
@@ -226,10 +242,12 @@ def conv2d_dgrad(dy: torch.Tensor, wt2d: torch.Tensor, R: int, S: int, stride: i
         out = (torch.zeros if (stride == 2 and R == 1) else torch.empty)(
             (n, ih, iw, c), dtype=torch.bfloat16, device=dy.device)
     _, _, _, _, osn, osh, osw = _nhwc_meta(out)
-    bn = _pick_bn(c, (R * S if stride == 1 else max(1, (R * S) // 4)) * k)
+    ktot = (R * S if stride == 1 else max(1, (R * S) // 4)) * k
+    bn = _pick_bn(c, ktot)
+    cg = _pick_cg(bn, ktot)
     if stride == 1:
         flat = R == 1 and S == 1 and pad == 0 and _is_flat(n, oh, ow, sn, sh, sw) and _is_flat(n, ih, iw, osn, osh, osw)
-        key = ("dgrad1", n, oh, ow, k, sn, sh, sw, c, R, S, pad, osn, osh, osw, bn)
+        key = ("dgrad1", n, oh, ow, k, sn, sh, sw, c, R, S, pad, osn, osh, osw, bn, cg)
 
         def build():
             d = N.ConvDesc()
@@ -257,6 +275,7 @@ def conv2d_dgrad(dy: torch.Tensor, wt2d: torch.Tensor, R: int, S: int, stride: i
             d.cblocks = k // 64
             d.b_rows, d.b_k = c, R * S * k
             d.n_out, d.bn = c, bn
+            d.cta_group = cg
             return d
 
         if addend is not None:
@@ -287,7 +306,7 @@ def conv2d_dgrad(dy: torch.Tensor, wt2d: torch.Tensor, R: int, S: int, stride: i
                 if not (R == 1):
                     out[:, a::2, b::2, :].zero_()
                 continue
-            key = ("dgrad2", a, b, n, oh, ow, k, sn, sh, sw, c, R, S, pad, ih, iw, osn, osh, osw, bn)
+            key = ("dgrad2", a, b, n, oh, ow, k, sn, sh, sw, c, R, S, pad, ih, iw, osn, osh, osw, bn, cg)
 
             def build(a=a, b=b, rs=rs, ss=ss, sub_h=sub_h, sub_w=sub_w):
                 d = N.ConvDesc()
@@ -310,6 +329,7 @@ def conv2d_dgrad(dy: torch.Tensor, wt2d: torch.Tensor, R: int, S: int, stride: i
                 d.cblocks = k // 64
                 d.b_rows, d.b_k = c, R * S * k
                 d.n_out, d.bn = c, bn
+                d.cta_group = cg
                 return d
 
             _run_igemm(_get_plan(key, build), dy, wt2d, out, None, None)

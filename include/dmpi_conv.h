@@ -64,6 +64,7 @@ typedef struct {
   int64_t w_ld;
   int tap_woff[DMPI_MAX_TAPS];
   int splits; /* wgrad split-K factor over pixel tiles (0: auto) */
+  int cta_group; /* igemm: 2 = CTA pairs (tcgen05.mma.cta_group::2, 256-row tiles; bn must be 128 or 256), else 1 */
 } dmpi_conv_desc;
 
 typedef struct dmpi_conv_plan dmpi_conv_plan;
