@@ -38,6 +38,9 @@ struct alignas(64) ConvKernelParams {
   // its sub-tiles are TMA-prefetched into the staging buffers two sub-tiles ahead of the converters
   CUtensorMap add_map;
   int has_add;
+  // igemm patch mode (see dmpi_conv_desc.patch): patch width in pixels, bytes per patch TMA box, shared-memory stride of
+  // one patch stage, ring depths, and whether the whole filter stays resident in the B ring
+  int patch, halo, pw, pa_bytes, pa_stride, pa_stages, pb_stages, b_resident;
   int dbg;  // DMPI_IGEMM_DBG experiment bits (bench only): 1 no TMA store, 2 no statistics, 4 no loads, 8 no MMAs
 };
 

@@ -60,7 +60,8 @@ struct IgemmCfg {
   static constexpr int kOutBytes = kTileM * kSubN * 2;
   static constexpr int kOutBufs = 2;
   static constexpr int kSmemBytes =
-      kStages * (kABytes + kBBytes) + kOutBufs * kOutBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+      kStages * (kABytes + kBBytes) + kOutBufs * kOutBytes + 1024 /*align slack*/ + 512 /*barriers*/ + 128 /*tap table*/;
+  static constexpr int kRingBytes = kStages * (kABytes + kBBytes);  // patch mode re-carves this region (2 rings)
   static constexpr int kTmemCols = 2 * BN;
   static_assert(CG == 1 || BN >= 128, "CTA pairs are used for the wide tiles only");
 };
@@ -133,7 +134,14 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
   uint64_t* ofull = bars + 2 * S + 4;   // converters -> store/stat warps: sub-tile staged
   uint64_t* ofree = bars + 2 * S + 6;   // store/stat warps -> converters: buffer may be overwritten
   uint64_t* aload = bars + 2 * S + 8;   // addend sub-tile landed in the staging buffer (replaces ofree when used)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * S + 10);
+  // patch mode: separate rings for input patches (<= kMaxPA stages) and filter-tap tiles (<= kMaxPB stages)
+  constexpr int kMaxPA = 4, kMaxPB = 12;
+  uint64_t* pa_full = bars + 2 * S + 10;
+  uint64_t* pa_empty = pa_full + kMaxPA;
+  uint64_t* pb_full = pa_empty + kMaxPA;
+  uint64_t* pb_empty = pb_full + kMaxPB;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pb_empty + kMaxPB);
+  static_assert((2 * S + 10 + 2 * kMaxPA + 2 * kMaxPB) * 8 + 8 <= 512, "barrier region too small");
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -157,6 +165,16 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
       mbar_init(&ofree[i], kStatWarps);
       mbar_init(&aload[i], 1);
     }
+    if (p.patch) {
+      for (int i = 0; i < kMaxPA; ++i) {
+        mbar_init(&pa_full[i], 1);
+        mbar_init(&pa_empty[i], 1);
+      }
+      for (int i = 0; i < kMaxPB; ++i) {
+        mbar_init(&pb_full[i], 1);
+        mbar_init(&pb_empty[i], 1);
+      }
+    }
     fence_mbar_init();
   }
   if (warp == 2) {
@@ -173,7 +191,41 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
-    if (lane == 0) {
+    if (lane == 0 && p.patch) {
+      // Patch mode: one input patch per (tile, channel block) into the A ring, one filter tile per tap into the B ring
+      // (loaded once and kept when the whole filter fits: b_resident).
+      uint8_t* ring_a = smem;
+      uint8_t* ring_b = smem + p.pa_stages * p.pa_stride;
+      int sa = 0, sb = 0;
+      uint32_t pha = 0, phb = 0;
+      bool first = true;
+      TileWalk tk;
+      for (tk.init(p, 1, 0); tk.remaining > 0; tk.next(p)) {
+        const int w0 = tk.tw * p.box_w, h0 = tk.th * p.box_h, n0 = tk.tn * p.box_n;
+        for (int cb = 0; cb < p.cblocks; ++cb) {
+          mbar_wait_spin(&pa_empty[sa], pha ^ 1u);
+          mbar_arrive_expect_tx(&pa_full[sa], static_cast<uint32_t>(p.pa_bytes));
+          tma_load_4d(ring_a + sa * p.pa_stride, &p.a_map[0], &pa_full[sa], cb * kBlockK, w0 - p.halo, h0 - p.halo, n0);
+          if (++sa == p.pa_stages) {
+            sa = 0;
+            pha ^= 1u;
+          }
+          if (p.b_resident && !first) continue;
+          for (int t = 0; t < p.ntaps; ++t) {
+            const int slot = p.b_resident ? cb * p.ntaps + t : sb;
+            if (!p.b_resident) mbar_wait_spin(&pb_empty[sb], phb ^ 1u);
+            mbar_arrive_expect_tx(&pb_full[slot], Cfg::kBBytes);
+            tma_load_2d(ring_b + slot * Cfg::kBBytes, &p.b_map, &pb_full[slot], p.tap_koff[t] + cb * kBlockK,
+                        tk.n_blk * BN);
+            if (!p.b_resident && ++sb == p.pb_stages) {
+              sb = 0;
+              phb ^= 1u;
+            }
+          }
+        }
+        first = false;
+      }
+    } else if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
       const uint32_t tx_bytes = static_cast<uint32_t>(p.rows) * 128u + Cfg::kBBytes;
@@ -212,8 +264,121 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
     __syncwarp();
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0 && rank == 0) {
+    // The whole warp runs the loops (warp-uniform control flow, every lane polls the barriers); one elected lane
+    // issues the tcgen05 instructions.  Descriptors are split into a constant high word and a low word that advances
+    // by (bytes >> 4), so a K step or a tap shift is one 32-bit add.
+    const bool leader = elect_one();
+    const uint32_t hi = umma_desc_hi(1024);
+    if (p.patch) {
+      constexpr uint32_t idesc = umma_idesc_bf16(kTileM, BN, 0, 0);
+      const uint32_t ring_a = smem_u32(smem);
+      const uint32_t ring_b = ring_a + p.pa_stages * p.pa_stride;
+      const uint32_t a_lo_ring = umma_desc_lo(ring_a, 0);
+      const uint32_t b_lo0 = umma_desc_lo(ring_b, 0);
+      const uint32_t pa_step = static_cast<uint32_t>(p.pa_stride) >> 4;
+      constexpr uint32_t pb_step = static_cast<uint32_t>(Cfg::kBBytes) >> 4;
+      // per-tap row shift inside the patch, in descriptor units (128 B >> 4 = 8 per pixel row)
+      uint32_t* tap_shift = reinterpret_cast<uint32_t*>(smem_o + Cfg::kOutBufs * Cfg::kOutBytes + 512);  // 32 words
+      if (lane < p.ntaps)
+        tap_shift[lane] = static_cast<uint32_t>((p.tap_dh[lane] + p.halo) * p.pw + p.tap_dw[lane] + p.halo) * 8u;
+      __syncwarp();
+      const int ntaps = p.ntaps, cblocks = p.cblocks, pb_stages = p.pb_stages, pa_stages = p.pa_stages;
+      const bool resident = p.b_resident != 0;
+      // 3x3 filters (every caller today): tap shifts live in registers and the tap loop is fully unrolled, so the
+      // steady state is ~3 instructions per MMA
+      uint32_t ts[9];
+#pragma unroll
+      for (int t = 0; t < 9; ++t) ts[t] = t < ntaps ? tap_shift[t] : 0u;
+      int sa = 0, sb = 0;
+      uint32_t pha = 0, phb = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      bool first = true;
+      TileWalk tk;
+      for (tk.init(p, 1, 0); tk.remaining > 0; --tk.remaining) {
+        mbar_wait_spin(&tempty[acc], acc_phase ^ 1u);
+        tc_fence_after_sync();
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
+        uint32_t accum = 0;
+        for (int cb = 0; cb < cblocks; ++cb) {
+          mbar_wait_spin(&pa_full[sa], pha);
+          tc_fence_after_sync();
+          const uint32_t a_lo0 = a_lo_ring + static_cast<uint32_t>(sa) * pa_step;
+          if (ntaps == 9 && resident && !first) {
+            // whole filter resident: no barrier traffic inside the tile
+            const uint32_t b_cb = b_lo0 + static_cast<uint32_t>(cb * 9) * pb_step;
+            if (leader) {
+#pragma unroll
+              for (int t = 0; t < 9; ++t) {
+                const uint32_t a_lo = a_lo0 + ts[t];
+                const uint32_t b_lo = b_cb + static_cast<uint32_t>(t) * pb_step;
+                umma_bf16_lohi(d_tmem, a_lo, hi, b_lo, hi, idesc, t == 0 ? accum : 1u);
+                umma_bf16_lohi(d_tmem, a_lo + 2, hi, b_lo + 2, hi, idesc, 1u);
+                umma_bf16_lohi(d_tmem, a_lo + 4, hi, b_lo + 4, hi, idesc, 1u);
+                umma_bf16_lohi(d_tmem, a_lo + 6, hi, b_lo + 6, hi, idesc, 1u);
+              }
+            }
+            accum = 1u;
+          } else if (ntaps == 9 && !resident) {
+#pragma unroll
+            for (int t = 0; t < 9; ++t) {
+              mbar_wait_spin(&pb_full[sb], phb);
+              tc_fence_after_sync();
+              if (leader) {
+                const uint32_t a_lo = a_lo0 + ts[t];
+                const uint32_t b_lo = b_lo0 + static_cast<uint32_t>(sb) * pb_step;
+                umma_bf16_lohi(d_tmem, a_lo, hi, b_lo, hi, idesc, accum);
+                umma_bf16_lohi(d_tmem, a_lo + 2, hi, b_lo + 2, hi, idesc, 1u);
+                umma_bf16_lohi(d_tmem, a_lo + 4, hi, b_lo + 4, hi, idesc, 1u);
+                umma_bf16_lohi(d_tmem, a_lo + 6, hi, b_lo + 6, hi, idesc, 1u);
+                umma_commit(&pb_empty[sb]);
+              }
+              accum = 1u;
+              if (++sb == pb_stages) {
+                sb = 0;
+                phb ^= 1u;
+              }
+            }
+          } else {
+            // generic path: any tap count, first tile of the resident mode
+#pragma unroll 1
+            for (int t = 0; t < ntaps; ++t) {
+              const int slot = resident ? cb * ntaps + t : sb;
+              if (!resident || first) {
+                mbar_wait_spin(&pb_full[slot], resident ? 0u : phb);
+                tc_fence_after_sync();
+              }
+              const uint32_t a_lo = a_lo0 + tap_shift[t];
+              const uint32_t b_lo = b_lo0 + static_cast<uint32_t>(slot) * pb_step;
+              if (leader) {
+                umma_bf16_lohi(d_tmem, a_lo, hi, b_lo, hi, idesc, accum);
+                umma_bf16_lohi(d_tmem, a_lo + 2, hi, b_lo + 2, hi, idesc, 1u);
+                umma_bf16_lohi(d_tmem, a_lo + 4, hi, b_lo + 4, hi, idesc, 1u);
+                umma_bf16_lohi(d_tmem, a_lo + 6, hi, b_lo + 6, hi, idesc, 1u);
+                if (!resident) umma_commit(&pb_empty[sb]);
+              }
+              accum = 1u;
+              if (!resident && ++sb == pb_stages) {
+                sb = 0;
+                phb ^= 1u;
+              }
+            }
+          }
+          if (leader) umma_commit(&pa_empty[sa]);
+          if (++sa == pa_stages) {
+            sa = 0;
+            pha ^= 1u;
+          }
+        }
+        first = false;
+        if (leader) umma_commit(&tfull[acc]);
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1u;
+      }
+    } else if (rank == 0) {
       constexpr uint32_t idesc = umma_idesc_bf16(kTileM * CG, BN, 0, 0);
+      const uint32_t a_lo_ring = umma_desc_lo(smem_u32(smem_a), 0);
+      const uint32_t b_lo_ring = umma_desc_lo(smem_u32(smem_b), 0);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -223,29 +388,34 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
         mbar_wait_spin(&tempty[acc], acc_phase ^ 1u);
         tc_fence_after_sync();
         const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
+        uint32_t accum = 0;
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait_spin(&full[stage], phase);
           tc_fence_after_sync();
-          const uint32_t a_addr = smem_u32(smem_a + stage * kABytes);
-          const uint32_t b_addr = smem_u32(smem_b + stage * Cfg::kBBytes);
+          const uint32_t a_lo = a_lo_ring + static_cast<uint32_t>(stage) * (kABytes >> 4);
+          const uint32_t b_lo = b_lo_ring + static_cast<uint32_t>(stage) * (Cfg::kBBytes >> 4);
+          if (leader) {
+            if (!(p.dbg & 8)) {  // (experiment bit 8: no MMAs, commits only)
 #pragma unroll
-          for (int k = 0; k < kBlockK / 16; ++k) {
-            if (p.dbg & 8) break;  // experiment: no MMAs, commits only (load pipeline alone)
-            const uint64_t adesc = umma_smem_desc(a_addr + k * 32, 0, 1024);
-            const uint64_t bdesc = umma_smem_desc(b_addr + k * 32, 0, 1024);
-            if (CG == 2) umma_bf16_pair(d_tmem, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
-            else umma_bf16(d_tmem, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+              for (int k = 0; k < kBlockK / 16; ++k) {
+                if (CG == 2) umma_bf16_pair_lohi(d_tmem, a_lo + 2 * k, hi, b_lo + 2 * k, hi, idesc, k == 0 ? accum : 1u);
+                else umma_bf16_lohi(d_tmem, a_lo + 2 * k, hi, b_lo + 2 * k, hi, idesc, k == 0 ? accum : 1u);
+              }
+            }
+            // frees the stage in both CTAs of a pair (each producer waits on its own barrier)
+            if (CG == 2) umma_commit_pair(&empty[stage], 0b11);
+            else umma_commit(&empty[stage]);
           }
-          // frees the stage in both CTAs of a pair (each producer waits on its own barrier)
-          if (CG == 2) umma_commit_pair(&empty[stage], 0b11);
-          else umma_commit(&empty[stage]);
+          accum = 1u;
           if (++stage == S) {
             stage = 0;
             phase ^= 1u;
           }
         }
-        if (CG == 2) umma_commit_pair(&tfull[acc], 0b11);
-        else umma_commit(&tfull[acc]);
+        if (leader) {
+          if (CG == 2) umma_commit_pair(&tfull[acc], 0b11);
+          else umma_commit(&tfull[acc]);
+        }
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1u;
       }
@@ -258,10 +428,26 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
     constexpr int CHs = SN / 64;  // 32-column chunks per warp and sub-tile: 1 (BN=64) or 2
     const int q = warp & 3;
     const int hf = (warp - 4) >> 2;
-    const int row = q * 32 + lane;
-    const int wi = row % p.box_w;
-    const int hi = (row / p.box_w) % p.box_h;
-    const int ni = row / (p.box_w * p.box_h);
+    const int row = q * 32 + lane;  // accumulator row (TMEM lane)
+    // (wi, hi, ni): pixel of this row inside the tile;  srow: its row in the dense staged tile
+    int wi, hi, ni, srow;
+    bool row_ok;
+    if (p.patch) {
+      // accumulator rows run over the padded patch width: row = hi * pw + wi; columns >= box_w and rows >= box_h are
+      // halo positions whose results are discarded (they take the unused tail rows of the staged tile, zeroed)
+      wi = row % p.pw;
+      hi = row / p.pw;
+      ni = 0;
+      row_ok = wi < p.box_w && hi < p.box_h;
+      const int below = (hi < p.box_h ? hi : p.box_h) * p.box_w + (hi < p.box_h ? (wi < p.box_w ? wi : p.box_w) : 0);
+      srow = row_ok ? hi * p.box_w + wi : p.box_w * p.box_h + (row - below);
+    } else {
+      wi = row % p.box_w;
+      hi = (row / p.box_w) % p.box_h;
+      ni = row / (p.box_w * p.box_h);
+      row_ok = row < p.rows;
+      srow = row;
+    }
     const uint32_t obase = smem_u32(smem_o);
     const bool has_add = p.has_add != 0;
     int acc = 0;
@@ -271,7 +457,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
     TileWalk tk;
     for (tk.init(p, CG, rank); tk.remaining > 0; tk.next(p)) {
       const int w0 = tk.tw * p.box_w, h0 = tk.th * p.box_h, n0 = tk.tn * p.box_n;
-      const bool valid = row < p.rows && (w0 + wi) < p.grid_w && (h0 + hi) < p.grid_h && (n0 + ni) < p.grid_n;
+      const bool valid = row_ok && (w0 + wi) < p.grid_w && (h0 + hi) < p.grid_h && (n0 + ni) < p.grid_n;
 
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after_sync();
@@ -292,12 +478,12 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
           const int col0 = tk.n_blk * BN + col_t;   // global output column
           uint32_t v[32];
           tmem_ld_32x32(t_addr + col_t, v);
-          const uint32_t half_base = obuf + (cs >> 1) * (kTileM * 128) + row * 128;
+          const uint32_t half_base = obuf + (cs >> 1) * (kTileM * 128) + srow * 128;
           const int c16_0 = (cs & 1) * 4;
           uint4 ad[4];
           if (has_add) {
 #pragma unroll
-            for (int i = 0; i < 4; ++i) ad[i] = lds128(half_base + (((c16_0 + i) ^ (row & 7)) * 16));
+            for (int i = 0; i < 4; ++i) ad[i] = lds128(half_base + (((c16_0 + i) ^ (srow & 7)) * 16));
           }
           tmem_ld_wait();
           float f[32];
@@ -333,7 +519,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
 #pragma unroll
               for (int j = 0; j < 4; ++j)
                 pk[j] = valid ? pack_bf16x2(f[i * 8 + 2 * j], f[i * 8 + 2 * j + 1]) : 0u;
-              const int c16 = (c16_0 + i) ^ (row & 7);
+              const int c16 = (c16_0 + i) ^ (srow & 7);
               sts128(half_base + c16 * 16, pk[0], pk[1], pk[2], pk[3]);
             }
           } else if (valid) {
@@ -662,6 +848,9 @@ extern "C" dmpi_conv_plan* dmpi_conv_plan_create(const dmpi_conv_desc* desc) {
   kp.c_total = d.c_total;
   kp.w_ld = d.w_ld;
   kp.splits = d.splits;
+  kp.patch = d.patch;
+  kp.halo = d.halo;
+  kp.pw = d.box_w + 2 * d.halo;
   return plan;
 }
 
@@ -696,13 +885,46 @@ extern "C" int dmpi_igemm_run_add(dmpi_conv_plan* plan, const void* a, const voi
     set_err("igemm: fp32 direct output needs the flat (GEMM) pixel layout");
     return -3;
   }
+  if (d.patch) {
+    // ring geometry: as many filter-tap stages as fit next to 2-3 patch stages; the whole filter stays resident when
+    // it fits and every tile of the launch uses the same N tile
+    const int ph = d.box_h + 2 * d.halo;
+    if (d.box_n != 1 || d.a_nviews != 1 || d.cta_group == 2 || (d.box_h - 1) * kp.pw + d.box_w > kTileM) {
+      set_err("igemm: illegal patch-mode geometry");
+      return -12;
+    }
+    const int read_rows = kTileM + 2 * d.halo * kp.pw + 2 * d.halo;  // furthest row a (discarded) accumulator row reads
+    const int rows_alloc = read_rows > kp.pw * ph ? read_rows : kp.pw * ph;
+    kp.pa_bytes = kp.pw * ph * 128;
+    kp.pa_stride = ((rows_alloc * 128 + 1023) / 1024) * 1024;
+    const int ring = d.bn == 64 ? IgemmCfg<64, 1>::kRingBytes : (d.bn == 128 ? IgemmCfg<128, 1>::kRingBytes : IgemmCfg<256, 1>::kRingBytes);
+    const int bbytes = d.bn * kBlockK * 2;
+    const int taps_total = d.ntaps * d.cblocks;
+    int pa = 3;
+    if (ring - pa * kp.pa_stride < 4 * bbytes) pa = 2;
+    int pb = (ring - pa * kp.pa_stride) / bbytes;
+    if (pb > 12) pb = 12;
+    if (pb < 2) {
+      set_err("igemm: patch does not fit in shared memory");
+      return -12;
+    }
+    kp.pa_stages = pa;
+    kp.pb_stages = pb;
+    kp.b_resident = (kp.num_n_tiles == 1 && taps_total <= pb) ? 1 : 0;
+  }
   if (!plan->maps_valid || plan->cached_a != a || plan->cached_b != b || plan->cached_o != out) {
+    if (d.patch) {
+      if (encode_view(&kp.a_map[0], a, d.a_view[0], kBlockK, kp.pw, d.box_h + 2 * d.halo, 1)) {
+        set_err("igemm: patch tensor map encode failed");
+        return -4;
+      }
+    } else
     for (int i = 0; i < d.a_nviews; ++i)
       if (encode_view(&kp.a_map[i], a, d.a_view[i], kBlockK, d.box_w, d.box_h, d.box_n)) {
         set_err("igemm: A tensor map encode failed");
         return -4;
       }
-    for (int i = d.a_nviews; i < DMPI_MAX_MAPS; ++i) kp.a_map[i] = kp.a_map[0];
+    for (int i = d.patch ? 1 : d.a_nviews; i < DMPI_MAX_MAPS; ++i) kp.a_map[i] = kp.a_map[0];
     {
       int64_t dims[2] = {d.b_k, d.b_rows};
       int64_t strides[1] = {d.b_k};

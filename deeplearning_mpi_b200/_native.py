@@ -46,6 +46,7 @@ class ConvDesc(C.Structure):
         ("tap_woff", C.c_int * MAX_TAPS),
         ("splits", C.c_int),
         ("cta_group", C.c_int),
+        ("patch", C.c_int), ("halo", C.c_int),
     ]
 
 

@@ -153,6 +153,43 @@ def _pick_cg(bn: int, ktot: int) -> int:
     return 2 if ktot >= _CG2_MIN_K else 1
 
 
+_PATCH = int(os.environ.get("DMPI_PATCH", "1"))
+_PATCH_MIN_EFF = float(os.environ.get("DMPI_PATCH_MIN_EFF", "0.85"))
+
+
+def choose_patch_tile(ow: int, oh: int, halo: int = 1) -> Optional[Tuple[int, int, float]]:
+    """Tile (columns, rows) of the patch-mode implicit GEMM for a stride-1 R x S convolution, or None.
+
+    The accumulator rows run over the padded tile width pw = tw + 2*halo, so tw output columns x th output rows fit when
+    (th-1)*pw + tw <= 128; the efficiency is the fraction of accumulator rows that are real output pixels."""
+    best = None
+    for tw in sorted({min(ow, 128)} | {-(-ow // k) for k in range(1, 9)}):
+        if tw < 8 or tw > 128:
+            continue
+        pw = tw + 2 * halo
+        th = min(oh, (128 - tw) // pw + 1)
+        if (th - 1) * pw + tw > 128:
+            continue
+        tiles = -(-ow // tw) * -(-oh // th)
+        eff = ow * oh / (tiles * 128.0)
+        if best is None or eff > best[2] + 1e-9:
+            best = (tw, th, eff)
+    return best
+
+
+def _patch_ok(R, S, stride, pad, c_in, ow, oh, n_out=64):
+    """Patch mode pays where the whole filter stays resident in shared memory (C_in = 64, N <= 64: 88 vs 136 us on
+    56x56x64 3x3); with streamed filter taps the weight traffic dominates and it only ties (DMPI_PATCH=2 forces it)."""
+    if not _PATCH or R != S or R != 3 or stride != 1 or pad != 1 or c_in % 64 != 0:
+        return None
+    if _PATCH != 2 and not (c_in == 64 and n_out <= 64):
+        return None
+    t = choose_patch_tile(ow, oh, pad)
+    if t is None or t[2] < _PATCH_MIN_EFF:
+        return None
+    return t
+
+
 # --------------------------------------------------------------------------------------- fprop
 def conv2d_fprop(x: torch.Tensor, w2d: torch.Tensor, R: int, S: int, stride: int = 1, pad: int = 0,
                  out: Optional[torch.Tensor] = None, bias: Optional[torch.Tensor] = None,
@@ -172,8 +209,11 @@ def conv2d_fprop(x: torch.Tensor, w2d: torch.Tensor, R: int, S: int, stride: int
             and _is_flat(n, oh, ow, osn, osh, osw))
     bn = _pick_bn(kout, R * S * c)
     cg = _pick_cg(bn, R * S * c)
+    ptile = _patch_ok(R, S, stride, pad, c, ow, oh, kout)
+    if ptile is not None:
+        cg = 1
     key = ("fprop", n, h, w, c, sn, sh, sw, kout, R, S, stride, pad, osn, osh, osw, bias is not None,
-           stats is not None, relu, bn, cg)
+           stats is not None, relu, bn, cg, ptile)
 
     def build():
         d = N.ConvDesc()
@@ -192,7 +232,11 @@ def conv2d_fprop(x: torch.Tensor, w2d: torch.Tensor, R: int, S: int, stride: int
             d.a_nviews = len(views)
             for i, v in enumerate(views):
                 d.a_view[i] = v
-            bw, bh, bnn = choose_box(ow, oh, n)
+            if ptile is not None:
+                bw, bh, bnn = ptile[0], ptile[1], 1
+                d.patch, d.halo = 1, pad
+            else:
+                bw, bh, bnn = choose_box(ow, oh, n)
             d.box_w, d.box_h, d.box_n = bw, bh, bnn
             d.grid_w, d.grid_h, d.grid_n = ow, oh, n
             d.ntaps = R * S
@@ -247,7 +291,10 @@ def conv2d_dgrad(dy: torch.Tensor, wt2d: torch.Tensor, R: int, S: int, stride: i
     cg = _pick_cg(bn, ktot)
     if stride == 1:
         flat = R == 1 and S == 1 and pad == 0 and _is_flat(n, oh, ow, sn, sh, sw) and _is_flat(n, ih, iw, osn, osh, osw)
-        key = ("dgrad1", n, oh, ow, k, sn, sh, sw, c, R, S, pad, osn, osh, osw, bn, cg)
+        ptile = _patch_ok(R, S, 1, pad, k, iw, ih, c)
+        if ptile is not None:
+            cg = 1
+        key = ("dgrad1", n, oh, ow, k, sn, sh, sw, c, R, S, pad, osn, osh, osw, bn, cg, ptile)
 
         def build():
             d = N.ConvDesc()
@@ -261,7 +308,11 @@ def conv2d_dgrad(dy: torch.Tensor, wt2d: torch.Tensor, R: int, S: int, stride: i
                 d.o_view[0] = _t4((c, m, 1, 1), (osw, m * osw, m * osw))
             else:
                 d.a_view[0] = _t4((k, ow, oh, n), (sw, sh, sn))
-                bw, bh, bnn = choose_box(iw, ih, n)
+                if ptile is not None:
+                    bw, bh, bnn = ptile[0], ptile[1], 1
+                    d.patch, d.halo = 1, pad
+                else:
+                    bw, bh, bnn = choose_box(iw, ih, n)
                 d.box_w, d.box_h, d.box_n = bw, bh, bnn
                 d.grid_w, d.grid_h, d.grid_n = iw, ih, n
                 d.ntaps = R * S

@@ -65,6 +65,11 @@ typedef struct {
   int tap_woff[DMPI_MAX_TAPS];
   int splits; /* wgrad split-K factor over pixel tiles (0: auto) */
   int cta_group; /* igemm: 2 = CTA pairs (tcgen05.mma.cta_group::2, 256-row tiles; bn must be 128 or 256), else 1 */
+  /* igemm patch mode (stride-1 R x S convolutions, halo = pad): the M tile is box_h output rows x box_w output columns;
+   * ONE shared-memory patch of (box_h + 2*halo) x (box_w + 2*halo) input pixels per 64-channel block serves every
+   * filter tap through row-shifted tcgen05 descriptors (tap (dh, dw) = shift of ((dh+halo)*(box_w+2*halo) + dw+halo)
+   * pixel rows).  Needs (box_h-1)*(box_w+2*halo) + box_w <= 128, box_n == 1, one A view, cta_group 1. */
+  int patch, halo;
 } dmpi_conv_desc;
 
 typedef struct dmpi_conv_plan dmpi_conv_plan;

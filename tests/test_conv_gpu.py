@@ -1,5 +1,9 @@
 """Numerics of the tcgen05 implicit-GEMM / wgrad kernels against plain PyTorch fp32 references
 (same bf16-rounded inputs, fp32 math)."""
+import os
+
+os.environ.setdefault("DMPI_PATCH", "2")  # exercise the patch-mode kernel on every eligible 3x3 case, not only C = 64
+
 import pytest
 import torch
 import torch.nn.functional as F
@@ -41,6 +45,10 @@ def _wt2d(w):  # [K, C, R, S] -> [C, R*S*K]
 
 CONV_CASES = [
     # n, h, w, c, k, R, stride, pad
+    (3, 28, 28, 128, 128, 3, 1, 1),   # patch mode, streamed filter taps, 2 channel blocks
+    (1, 128, 128, 64, 64, 3, 1, 1),   # patch mode, row-segment tiles (128 x 1), resident filter
+    (1, 56, 40, 64, 256, 3, 1, 1),    # patch mode, non-square image, two N tiles
+    (2, 224, 224, 64, 64, 3, 1, 1),   # patch mode, many tiles per CTA
     (4, 14, 14, 256, 512, 1, 1, 0),
     (2, 56, 56, 64, 64, 3, 1, 1),
     (3, 28, 28, 128, 128, 3, 2, 1),
@@ -93,7 +101,8 @@ def test_dgrad(case):
     _torch_setup()
     n, h, w, c, k, R, stride, pad = case
     oh = (h + 2 * pad - R) // stride + 1
-    dy = _rand(n, oh, oh, k)
+    ow = (w + 2 * pad - R) // stride + 1
+    dy = _rand(n, oh, ow, k)
     wt = _rand(k, c, R, R, scale=(k * R * R) ** -0.5)
     dx = C.conv2d_dgrad(dy, _wt2d(wt), R, R, stride, pad, (h, w))
     ref = torch.nn.grad.conv2d_input((n, c, h, w), wt.float(), dy.float().permute(0, 3, 1, 2), stride=stride,
@@ -144,8 +153,9 @@ def test_wgrad(case):
     _torch_setup()
     n, h, w, c, k, R, stride, pad = case
     oh = (h + 2 * pad - R) // stride + 1
+    ow = (w + 2 * pad - R) // stride + 1
     x = _rand(n, h, w, c)
-    dy = _rand(n, oh, oh, k)
+    dy = _rand(n, oh, ow, k)
     dw = torch.zeros(k, R, R, c, device=_dev())
     C.conv2d_wgrad(dy, x, dw, R, R, stride, pad)
     ref = torch.nn.grad.conv2d_weight(x.float().permute(0, 3, 1, 2), (k, c, R, R), dy.float().permute(0, 3, 1, 2),
