@@ -123,36 +123,42 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
       }
       __syncwarp();
     } else if (warp == 1) {
-      if (lane == 0) {
-        constexpr uint32_t idesc = umma_idesc_bf16(128, BN, 1, 1);
-        int stage = 0;
-        uint32_t phase = 0;
-        for (int it = 0; it < num_it; ++it) {
-          mbar_wait(&full[stage], phase);
-          tc_fence_after_sync();
-          const uint32_t a_addr = smem_u32(smem + stage * Cfg::kStageBytes);
-          const uint32_t b_addr = a_addr + kWABytes;
+      // warp-uniform loop, one elected lane issues (see elect_one() in ptx.cuh); split descriptors: one add per MMA
+      const bool leader = elect_one();
+      constexpr uint32_t idesc = umma_idesc_bf16(128, BN, 1, 1);
+      const uint32_t hi = umma_desc_hi(1024);
+      // MN-major, 128B swizzle: LBO = stride between 64-channel atoms, SBO = stride between 8-pixel groups;
+      // one MMA consumes 16 pixels = 2048 bytes (128 descriptor units) of every atom.
+      const uint32_t a_lo_ring = umma_desc_lo(smem_u32(smem), kAtomBytes);
+      constexpr uint32_t stage_step = static_cast<uint32_t>(Cfg::kStageBytes) >> 4;
+      constexpr uint32_t b_off = static_cast<uint32_t>(kWABytes) >> 4;
+      constexpr uint32_t tap_step = static_cast<uint32_t>(Cfg::kBTapBytes) >> 4;
+      int stage = 0;
+      uint32_t phase = 0;
+      uint32_t accum = 0;
+      for (int it = 0; it < num_it; ++it) {
+        mbar_wait_spin(&full[stage], phase);
+        tc_fence_after_sync();
+        const uint32_t a_lo = a_lo_ring + static_cast<uint32_t>(stage) * stage_step;
+        if (leader) {
 #pragma unroll
           for (int g = 0; g < G; ++g) {
             if (g < ntap) {
 #pragma unroll
-              for (int k = 0; k < kPix / 16; ++k) {
-                // MN-major, 128B swizzle: LBO = stride between 64-channel atoms, SBO = stride between
-                // 8-pixel groups; one MMA consumes 16 pixels = 2048 bytes of every atom.
-                const uint64_t adesc = umma_smem_desc(a_addr + k * 2048, kAtomBytes, 1024);
-                const uint64_t bdesc = umma_smem_desc(b_addr + g * Cfg::kBTapBytes + k * 2048, kAtomBytes, 1024);
-                umma_bf16(tmem_base + g * BN, adesc, bdesc, idesc, (it | k) != 0 ? 1u : 0u);
-              }
+              for (int k = 0; k < kPix / 16; ++k)
+                umma_bf16_lohi(tmem_base + g * BN, a_lo + k * 128, hi, a_lo + b_off + g * tap_step + k * 128, hi, idesc,
+                               k == 0 ? accum : 1u);
             }
           }
           umma_commit(&empty[stage]);
-          if (++stage == S) {
-            stage = 0;
-            phase ^= 1u;
-          }
         }
-        umma_commit(tfull);
+        accum = 1u;
+        if (++stage == S) {
+          stage = 0;
+          phase ^= 1u;
+        }
       }
+      if (leader) umma_commit(tfull);
       __syncwarp();
     } else if (warp >= 4) {
       const int q = warp - 4;
@@ -243,7 +249,9 @@ extern "C" int dmpi_wgrad_run(dmpi_conv_plan* plan, const void* dy, const void* 
   int splits = d.splits;
   if (splits <= 0) {
     const int tiles = groups * kp.num_k_tiles * kp.num_c_tiles;
-    splits = (2 * plan->num_sms + tiles - 1) / tiles;
+    // as many CTAs as fit in two full waves, never a few more (a third wave with a handful of CTAs costs a whole
+    // wave of time: 3 tiles x 99 splits = 297 CTAs on 148 SMs)
+    splits = (2 * plan->num_sms) / tiles;
     const int max_splits = kp.num_m_tiles / 4 > 0 ? kp.num_m_tiles / 4 : 1;
     if (splits > max_splits) splits = max_splits;
     if (splits < 1) splits = 1;
