@@ -345,7 +345,9 @@ __global__ void __launch_bounds__(kBnThreads) bn_stats_kernel(const __nv_bfloat1
 // Row-streaming kernels: each block handles rows_per_block rows per step and two steps per loop iteration; enough
 // blocks to fill the machine (8 resident 256-thread blocks on each of the 148 SMs) but no more than there is work.
 static int stream_grid(long long rows, int rows_per_block) {
-  long long blocks = (rows + 2LL * rows_per_block - 1) / (2LL * rows_per_block);
+  // at least 8 rows per thread: the per-thread prologue (per-channel constants from ~5 small arrays) costs as much
+  // as streaming several rows, which made the small late-layer launches latency-bound (22 us for 75 MB of traffic)
+  long long blocks = (rows + 8LL * rows_per_block - 1) / (8LL * rows_per_block);
   const long long cap = 148LL * 8;
   if (blocks > cap) blocks = cap;
   return blocks < 1 ? 1 : static_cast<int>(blocks);

@@ -253,3 +253,26 @@ def test_smallc(cfg):
                                          padding=pad)
     got = dww.view(k, R, 8, 8)[:, :, :R, :3].permute(0, 3, 1, 2)
     _close(got, ref_dw, 1e-2, f"smallc_wgrad{cfg}")
+
+
+def test_umma_row_shifted_descriptors():
+    """Hardware contract the patch-mode kernel relies on: a tcgen05 shared-memory descriptor whose start address is
+    shifted by whole 128-byte rows inside a 1024-byte swizzle atom (base-offset field 0) addresses exactly the rows a
+    TMA load with 128B swizzle put there, for K-major and MN-major operands."""
+    from deeplearning_mpi_b200 import _native as N
+
+    _torch_setup()
+    rows = 192
+    x = _rand(rows, 64)
+    w = _rand(64, 64)
+    y = _rand(64, 128)
+    lib = N.cuda()
+    for mode in (0, 2):
+        for shift in (0, 1, 3, 7, 8, 9, 17, 58, 59, 60):
+            out = torch.zeros(128, 64, device=_dev())
+            src = y if mode else w
+            rc = lib.dmpi_umma_probe(x.data_ptr(), src.data_ptr(), out.data_ptr(), rows, shift, mode, N.stream_ptr())
+            assert rc == 0
+            torch.cuda.synchronize()
+            ref = (y.float().t() @ x[shift:shift + 64].float()) if mode else (x[shift:shift + 128].float() @ w.float().t())
+            _close(out, ref, 1e-2, f"umma_shift mode={mode} shift={shift}")
