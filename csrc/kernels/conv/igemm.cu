@@ -900,7 +900,11 @@ extern "C" int dmpi_igemm_run_add(dmpi_conv_plan* plan, const void* a, const voi
     const int ring = d.bn == 64 ? IgemmCfg<64, 1>::kRingBytes : (d.bn == 128 ? IgemmCfg<128, 1>::kRingBytes : IgemmCfg<256, 1>::kRingBytes);
     const int bbytes = d.bn * kBlockK * 2;
     const int taps_total = d.ntaps * d.cblocks;
+    // prefer a configuration in which the whole filter stays resident (then only patches stream); 3 patch stages
+    // if they fit beside it, else 2
     int pa = 3;
+    const bool can_reside = kp.num_n_tiles == 1 && taps_total <= 12;
+    if (can_reside && ring - 3 * kp.pa_stride < taps_total * bbytes && ring - 2 * kp.pa_stride >= taps_total * bbytes) pa = 2;
     if (ring - pa * kp.pa_stride < 4 * bbytes) pa = 2;
     int pb = (ring - pa * kp.pa_stride) / bbytes;
     if (pb > 12) pb = 12;

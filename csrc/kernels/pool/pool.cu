@@ -17,16 +17,11 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const __nv_bfloat16* _
                                                           int N, int H, int W, int C, int OH, int OW, int k, int s,
                                                           int p, long long xsn, long long xsh, long long xsw,
                                                           long long ysn, long long ysh, long long ysw) {
+  // grid: x covers (ow, channel vector) of one output row, y = n * OH + oh  (32-bit index math only)
   const int vecC = C >> 3;
-  const long long total = static_cast<long long>(N) * OH * OW * vecC;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int cv = static_cast<int>(i % vecC);
-    long long t = i / vecC;
-    const int ow = static_cast<int>(t % OW);
-    t /= OW;
-    const int oh = static_cast<int>(t % OH);
-    const int n = static_cast<int>(t / OH);
+  const int n = blockIdx.y / OH, oh = blockIdx.y - n * OH;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < OW * vecC; i += gridDim.x * blockDim.x) {
+    const int ow = i / vecC, cv = i - ow * vecC;
     float best[8];
     int bidx[8];
 #pragma unroll
@@ -77,17 +72,14 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const __nv_bfloat16* _
                                                           __nv_bfloat16* __restrict__ dx, int N, int H, int W, int C,
                                                           int OH, int OW, int k, int s, int p, long long dsn,
                                                           long long dsh, long long dsw, long long xsn, long long xsh,
-                                                          long long xsw) {
+                                                          long long xsw, const __nv_bfloat16* __restrict__ addend,
+                                                          long long asn, long long ash, long long asw) {
+  // `addend` (optional): a second gradient of the pooled tensor (the UNet skip connection) added in the same pass
+  // grid: x covers (iw, channel vector) of one input row, y = n * H + ih  (32-bit index math only)
   const int vecC = C >> 3;
-  const long long total = static_cast<long long>(N) * H * W * vecC;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int cv = static_cast<int>(i % vecC);
-    long long t = i / vecC;
-    const int iw = static_cast<int>(t % W);
-    t /= W;
-    const int ih = static_cast<int>(t % H);
-    const int n = static_cast<int>(t / H);
+  const int n = blockIdx.y / H, ih = blockIdx.y - n * H;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < W * vecC; i += gridDim.x * blockDim.x) {
+    const int iw = i / vecC, cv = i - iw * vecC;
     float g[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) g[j] = 0.f;
@@ -109,6 +101,15 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const __nv_bfloat16* _
           const int tj = ((j < 4 ? id.x : id.y) >> ((j & 3) * 8)) & 0xFF;
           if (tj == tap) g[j] += (j & 1) ? bf16hi(di[j >> 1]) : bf16lo(di[j >> 1]);
         }
+      }
+    }
+    if (addend != nullptr) {
+      const uint4 a = *reinterpret_cast<const uint4*>(addend + n * asn + ih * ash + iw * asw + cv * 8);
+      const uint32_t ai[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        g[2 * j] += bf16lo(ai[j]);
+        g[2 * j + 1] += bf16hi(ai[j]);
       }
     }
     uint4 o;
@@ -181,22 +182,31 @@ extern "C" int dmpi_maxpool_forward(const void* x, void* y, void* idx, int N, in
                                     int k, int s, int p, long long xsn, long long xsh, long long xsw, long long ysn,
                                     long long ysh, long long ysw, void* stream) {
   if (C % 8 || k * k > 255) return -1;
-  const long long items = static_cast<long long>(N) * OH * OW * (C / 8);
-  maxpool_fwd_kernel<<<ew_grid(items), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  const dim3 grid((OW * (C / 8) + 255) / 256, N * OH);
+  maxpool_fwd_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), static_cast<uint8_t*>(idx), N, H, W, C, OH,
       OW, k, s, p, xsn, xsh, xsw, ysn, ysh, ysw);
+  return cudaGetLastError() == cudaSuccess ? 0 : -2;
+}
+
+extern "C" int dmpi_maxpool_backward_add(const void* dy, const void* idx, void* dx, int N, int H, int W, int C, int OH,
+                                         int OW, int k, int s, int p, long long dsn, long long dsh, long long dsw,
+                                         long long xsn, long long xsh, long long xsw, const void* addend,
+                                         long long asn, long long ash, long long asw, void* stream) {
+  if (C % 8) return -1;
+  if (addend != nullptr && ((reinterpret_cast<uintptr_t>(addend) & 15) || asn % 8 || ash % 8 || asw % 8)) return -3;
+  const dim3 grid((W * (C / 8) + 255) / 256, N * H);
+  maxpool_bwd_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(dy), static_cast<const uint8_t*>(idx), static_cast<__nv_bfloat16*>(dx), N, H,
+      W, C, OH, OW, k, s, p, dsn, dsh, dsw, xsn, xsh, xsw, static_cast<const __nv_bfloat16*>(addend), asn, ash, asw);
   return cudaGetLastError() == cudaSuccess ? 0 : -2;
 }
 
 extern "C" int dmpi_maxpool_backward(const void* dy, const void* idx, void* dx, int N, int H, int W, int C, int OH,
                                      int OW, int k, int s, int p, long long dsn, long long dsh, long long dsw,
                                      long long xsn, long long xsh, long long xsw, void* stream) {
-  if (C % 8) return -1;
-  const long long items = static_cast<long long>(N) * H * W * (C / 8);
-  maxpool_bwd_kernel<<<ew_grid(items), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(dy), static_cast<const uint8_t*>(idx), static_cast<__nv_bfloat16*>(dx), N, H,
-      W, C, OH, OW, k, s, p, dsn, dsh, dsw, xsn, xsh, xsw);
-  return cudaGetLastError() == cudaSuccess ? 0 : -2;
+  return dmpi_maxpool_backward_add(dy, idx, dx, N, H, W, C, OH, OW, k, s, p, dsn, dsh, dsw, xsn, xsh, xsw, nullptr, 0,
+                                   0, 0, stream);
 }
 
 extern "C" int dmpi_avgpool_forward(const void* x, void* y, int N, int HW, int C, void* stream) {

@@ -150,6 +150,8 @@ def _bind_cuda(lib) -> None:
     # pool
     _sig(lib, "dmpi_maxpool_forward", I, [VP, VP, VP, I, I, I, I, I, I, I, I, I, I64, I64, I64, I64, I64, I64, VP])
     _sig(lib, "dmpi_maxpool_backward", I, [VP, VP, VP, I, I, I, I, I, I, I, I, I, I64, I64, I64, I64, I64, I64, VP])
+    _sig(lib, "dmpi_maxpool_backward_add", I, [VP, VP, VP, I, I, I, I, I, I, I, I, I, I64, I64, I64, I64, I64, I64, VP,
+                                               I64, I64, I64, VP])
     _sig(lib, "dmpi_avgpool_forward", I, [VP, VP, I, I, I, VP])
     _sig(lib, "dmpi_avgpool_backward", I, [VP, VP, I, I, I, VP])
     # loss / head

@@ -57,7 +57,10 @@ class DownBlock(nn.Module):
 
     def forward_sm100(self, x, arena, skip_holder, stem_hw=None):
         skip = self.double_conv.forward_sm100(x, arena, out_holder=skip_holder, stem_hw=stem_hw)
-        return FN.MaxPool.apply(skip, 2, 2, 0), skip
+        # the skip tensor has two consumers (pool, decoder concat): the concat's gradient slice is added inside the
+        # pooling backward kernel (GradLink) instead of by autograd
+        link = FN.GradLink() if (torch.is_grad_enabled() and skip.requires_grad) else None
+        return FN.MaxPool.apply(skip, 2, 2, 0, link), skip, link
 
 
 class UpBlock(nn.Module):
@@ -77,7 +80,7 @@ class UpBlock(nn.Module):
         x = torch.cat([x, skip_input], dim=1)
         return self.double_conv(x)
 
-    def forward_sm100(self, down, skip, cat_buf, arena):
+    def forward_sm100(self, down, skip, cat_buf, arena, link=None):
         c_up = down.shape[-1]
         if isinstance(self.up_sample, nn.ConvTranspose2d):
             up = FN.ConvTranspose2x2.apply(down, self.up_sample.weight, self.up_sample.bias, [cat_buf[..., :c_up]], arena)
@@ -85,7 +88,7 @@ class UpBlock(nn.Module):
             up_nchw = F.interpolate(down.permute(0, 3, 1, 2).float(), scale_factor=2, mode="bilinear", align_corners=True)
             up = up_nchw.permute(0, 2, 3, 1).to(torch.bfloat16)
             cat_buf[..., :c_up].copy_(up.detach())
-        x = FN.ConcatView.apply(up, skip, [cat_buf])
+        x = FN.ConcatView.apply(up, skip, [cat_buf], link)
         return self.double_conv.forward_sm100(x, arena)
 
 
@@ -133,13 +136,13 @@ class UNet(nn.Module):
         cat2 = torch.empty((n, h // 2, w // 2, 256 + 128), dtype=torch.bfloat16, device=dev)
         cat3 = torch.empty((n, h // 4, w // 4, 512 + 256), dtype=torch.bfloat16, device=dev)
         cat4 = torch.empty((n, h // 8, w // 8, 1024 + 512), dtype=torch.bfloat16, device=dev)
-        a, s1 = self.down_conv1.forward_sm100(xp, arena, [cat1[..., 128:]], stem_hw=(h, w))
-        a, s2 = self.down_conv2.forward_sm100(a, arena, [cat2[..., 256:]])
-        a, s3 = self.down_conv3.forward_sm100(a, arena, [cat3[..., 512:]])
-        a, s4 = self.down_conv4.forward_sm100(a, arena, [cat4[..., 1024:]])
+        a, s1, l1 = self.down_conv1.forward_sm100(xp, arena, [cat1[..., 128:]], stem_hw=(h, w))
+        a, s2, l2 = self.down_conv2.forward_sm100(a, arena, [cat2[..., 256:]])
+        a, s3, l3 = self.down_conv3.forward_sm100(a, arena, [cat3[..., 512:]])
+        a, s4, l4 = self.down_conv4.forward_sm100(a, arena, [cat4[..., 1024:]])
         a = self.double_conv.forward_sm100(a, arena)
-        a = self.up_conv4.forward_sm100(a, s4, cat4, arena)
-        a = self.up_conv3.forward_sm100(a, s3, cat3, arena)
-        a = self.up_conv2.forward_sm100(a, s2, cat2, arena)
-        a = self.up_conv1.forward_sm100(a, s1, cat1, arena)
+        a = self.up_conv4.forward_sm100(a, s4, cat4, arena, l4)
+        a = self.up_conv3.forward_sm100(a, s3, cat3, arena, l3)
+        a = self.up_conv2.forward_sm100(a, s2, cat2, arena, l2)
+        a = self.up_conv1.forward_sm100(a, s1, cat1, arena, l1)
         return FN.Head1x1.apply(a, self.conv_last.weight, self.conv_last.bias, arena)

@@ -174,20 +174,28 @@ class ConcatView(torch.autograd.Function):
     this node only ties them into the autograd graph and splits the incoming gradient into two slice views."""
 
     @staticmethod
-    def forward(ctx, up, skip, buf_holder):
+    def forward(ctx, up, skip, buf_holder, link=None):
+        # link (GradLink, optional): the skip tensor also feeds a MaxPool; its gradient slice is parked in the link
+        # and added inside the pooling backward kernel instead of by an autograd add over a strided view
         ctx.c_up = up.shape[-1]
+        ctx.link = link
         return buf_holder[0].view(buf_holder[0].shape)
 
     @staticmethod
     def backward(ctx, g):
-        return g[..., : ctx.c_up], g[..., ctx.c_up:], None
+        g_skip = g[..., ctx.c_up:]
+        if ctx.link is not None:
+            ctx.link.give(g_skip)
+            g_skip = None
+        return g[..., : ctx.c_up], g_skip, None, None
 
 
 class MaxPool(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, k, s, p):
+    def forward(ctx, x, k, s, p, link=None):
         y, idx = K.maxpool_forward(x, k, s, p, want_idx=ctx.needs_input_grad[0])
         ctx.cfg = (tuple(x.shape), k, s, p)
+        ctx.link = link
         ctx.save_for_backward(idx)
         return y
 
@@ -197,7 +205,10 @@ class MaxPool(torch.autograd.Function):
         shape, k, s, p = ctx.cfg
         if dy.stride(-1) != 1:
             dy = dy.contiguous()
-        return K.maxpool_backward(dy, idx, shape, k, s, p), None, None, None
+        addend = ctx.link.take() if ctx.link is not None else None
+        if addend is not None and addend.dtype != torch.bfloat16:
+            addend = addend.to(torch.bfloat16)
+        return K.maxpool_backward(dy, idx, shape, k, s, p, addend=addend), None, None, None, None
 
 
 class GlobalAvgPool(torch.autograd.Function):

@@ -82,13 +82,22 @@ def maxpool_forward(x, k: int, s: int, p: int, want_idx: bool):
     return y, idx
 
 
-def maxpool_backward(dy, idx, in_shape, k: int, s: int, p: int):
+def maxpool_backward(dy, idx, in_shape, k: int, s: int, p: int, addend=None):
+    """dx of MaxPool2d; ``addend`` (bf16 NHWC, any n/h/w strides) is a second gradient of the same tensor that is added
+    in the same pass (the UNet skip connection)."""
     n, h, w, c = in_shape
     _, oh, ow, _ = dy.shape
     dx = torch.empty((n, h, w, c), dtype=torch.bfloat16, device=dy.device)
-    rc = N.cuda().dmpi_maxpool_backward(_p(dy), _p(idx), _p(dx), n, h, w, c, oh, ow, k, s, p, dy.stride(0),
-                                        dy.stride(1), dy.stride(2), dx.stride(0), dx.stride(1), dx.stride(2),
-                                        N.stream_ptr())
+    if addend is None:
+        rc = N.cuda().dmpi_maxpool_backward(_p(dy), _p(idx), _p(dx), n, h, w, c, oh, ow, k, s, p, dy.stride(0),
+                                            dy.stride(1), dy.stride(2), dx.stride(0), dx.stride(1), dx.stride(2),
+                                            N.stream_ptr())
+    else:
+        assert tuple(addend.shape) == (n, h, w, c) and addend.dtype == torch.bfloat16 and addend.stride(3) == 1
+        rc = N.cuda().dmpi_maxpool_backward_add(_p(dy), _p(idx), _p(dx), n, h, w, c, oh, ow, k, s, p, dy.stride(0),
+                                                dy.stride(1), dy.stride(2), dx.stride(0), dx.stride(1), dx.stride(2),
+                                                _p(addend), addend.stride(0), addend.stride(1), addend.stride(2),
+                                                N.stream_ptr())
     N.count_launch()
     _chk(rc, "dmpi_maxpool_backward")
     return dx

@@ -57,6 +57,12 @@ int dmpi_maxpool_forward(const void* x, void* y, void* idx /* uint8 arg-max tap 
 int dmpi_maxpool_backward(const void* dy, const void* idx, void* dx, int N, int H, int W, int C, int OH, int OW, int k,
                           int s, int p, long long dsn, long long dsh, long long dsw, long long xsn, long long xsh,
                           long long xsw, void* stream);
+/* Same, plus an optional second gradient of the pooled tensor (bf16, element strides of n / h / w, channel stride 1)
+ * added in the same pass: the UNet skip-connection gradient, so no separate add kernel runs. */
+int dmpi_maxpool_backward_add(const void* dy, const void* idx, void* dx, int N, int H, int W, int C, int OH, int OW,
+                              int k, int s, int p, long long dsn, long long dsh, long long dsw, long long xsn,
+                              long long xsh, long long xsw, const void* addend, long long asn, long long ash,
+                              long long asw, void* stream);
 int dmpi_avgpool_forward(const void* x, void* y, int N, int HW, int C, void* stream);
 int dmpi_avgpool_backward(const void* dy, void* dx, int N, int HW, int C, void* stream);
 
