@@ -140,6 +140,7 @@ def _bind_cuda(lib) -> None:
     _sig(lib, "dmpi_igemm_run", I, [VP, VP, VP, VP, VP, VP, VP, VP])
     _sig(lib, "dmpi_igemm_run_add", I, [VP, VP, VP, VP, VP, VP, VP, VP, I64, I64, I64, VP])
     _sig(lib, "dmpi_wgrad_run", I, [VP, VP, VP, VP, VP])
+    _sig(lib, "dmpi_wgrad_patch_run", I, [VP, VP, VP, VP, VP])
     _sig(lib, "dmpi_umma_probe", I, [VP, VP, VP, I, I, I, VP])
     _sig(lib, "dmpi_conv_last_error", I, [C.c_char_p, I])
     # norm

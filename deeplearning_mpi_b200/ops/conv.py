@@ -402,6 +402,9 @@ def conv2d_wgrad(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, R: int, S:
     xn, h, w, c, xsn, xsh, xsw = _nhwc_meta(x)
     assert xn == n and c % 64 == 0 and dw.dtype == torch.float32
     bn = _wgrad_bn(c)
+    if (_WGRAD_PATCH and R == 3 and S == 3 and stride == 1 and pad == 1 and k % 64 == 0
+            and (_WGRAD_PATCH == 2 or (c <= _WGRAD_PATCH_MAXC and k <= _WGRAD_PATCH_MAXC))):
+        return _conv2d_wgrad_patch(dy, x, dw, pad)
     key = ("wgrad", n, oh, ow, k, sn, sh, sw, h, w, c, xsn, xsh, xsw, R, S, stride, pad, bn)
 
     def build():
@@ -435,6 +438,48 @@ def conv2d_wgrad(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, R: int, S:
     rc = N.cuda().dmpi_wgrad_run(_get_plan(key, build), dy.data_ptr(), x.data_ptr(), dw.data_ptr(), N.stream_ptr())
     N.count_launch()
     _check(rc, "dmpi_wgrad_run")
+
+
+_WGRAD_PATCH = int(os.environ.get("DMPI_WGRAD_PATCH", "1"))  # 0 off, 1 automatic, 2 every eligible 3x3
+_WGRAD_PATCH_MAXC = int(os.environ.get("DMPI_WGRAD_PATCH_MAXC", "64"))
+
+
+def _conv2d_wgrad_patch(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, pad: int) -> None:
+    """3x3 stride-1 weight gradient from one shared-memory input patch per pixel tile (csrc/kernels/conv/wgrad_patch.cu):
+    full-width tiles of a few rows for narrow images, 128-pixel row segments for wide ones."""
+    n, oh, ow, k, sn, sh, sw = _nhwc_meta(dy)
+    _, h, w, c, xsn, xsh, xsw = _nhwc_meta(x)
+    if ow <= 127:
+        bw = ow
+        bh = max(1, min(oh, 128 // (ow + 2 * pad)))
+    else:
+        bw, bh = 128, 1
+    key = ("wgrad_patch", n, oh, ow, k, sn, sh, sw, h, w, c, xsn, xsh, xsw, pad, bw, bh)
+
+    def build():
+        d = N.ConvDesc()
+        d.a_nviews = 1
+        d.a_view[0] = _t4((c, w, h, n), (xsw, xsh, xsn))
+        d.box_w, d.box_h, d.box_n = bw, bh, 1
+        d.grid_w, d.grid_h, d.grid_n = ow, oh, n
+        d.patch, d.halo = 1, pad
+        d.ntaps = 9
+        t = 0
+        for r in range(3):
+            for s_ in range(3):
+                d.tap_view[t], d.tap_dh[t], d.tap_dw[t] = 0, r - pad, s_ - pad
+                d.tap_woff[t] = t * c
+                t += 1
+        d.o_nviews = 1
+        d.o_view[0] = _t4((k, ow, oh, n), (sw, sh, sn))
+        d.k_out, d.c_total, d.w_ld = k, c, 9 * c
+        d.splits = int(os.environ.get("DMPI_WGRAD_PATCH_SPLITS", "0"))
+        return d
+
+    rc = N.cuda().dmpi_wgrad_patch_run(_get_plan(key, build), dy.data_ptr(), x.data_ptr(), dw.data_ptr(),
+                                       N.stream_ptr())
+    N.count_launch()
+    _check(rc, "dmpi_wgrad_patch_run")
 
 
 # --------------------------------------------------------------------------------------- linear

@@ -91,6 +91,10 @@ int dmpi_igemm_run_add(dmpi_conv_plan* plan, const void* a, const void* b, void*
 /* dW += dY^T (*) X.  `dw` must already hold the value to accumulate onto (zero for a fresh gradient). */
 int dmpi_wgrad_run(dmpi_conv_plan* plan, const void* dy, const void* x, float* dw, void* stream);
 
+/* dW += ... for 3x3 stride-1 convolutions from one shared-memory input patch per pixel tile (taps = row-shifted
+ * descriptors, two taps per M = 128 operand); desc as for dmpi_wgrad_run plus patch-mode box_w / box_h / halo. */
+int dmpi_wgrad_patch_run(dmpi_conv_plan* plan, const void* dy, const void* x, float* dw, void* stream);
+
 /* number of kernels the last call launched (for launch accounting) */
 int dmpi_conv_last_error(char* buf, int buflen);
 

@@ -3,6 +3,7 @@
 import os
 
 os.environ.setdefault("DMPI_PATCH", "2")  # exercise the patch-mode kernel on every eligible 3x3 case, not only C = 64
+os.environ.setdefault("DMPI_WGRAD_PATCH", "2")
 
 import pytest
 import torch
