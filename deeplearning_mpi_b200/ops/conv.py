@@ -403,7 +403,9 @@ def conv2d_wgrad(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, R: int, S:
     assert xn == n and c % 64 == 0 and dw.dtype == torch.float32
     bn = _wgrad_bn(c)
     if (_WGRAD_PATCH and R == 3 and S == 3 and stride == 1 and pad == 1 and k % 64 == 0
-            and (_WGRAD_PATCH == 2 or (c <= _WGRAD_PATCH_MAXC and k <= _WGRAD_PATCH_MAXC))):
+            and (_WGRAD_PATCH == 2 or k <= _WGRAD_PATCH_MAXK)):
+        # k <= 64 is where the tap-group kernel wastes half of every M = 128 MMA (bench/wgrad_ab.py: 512x512 192->64
+        # 1772 -> 858 us, 128->64 811 -> 575 us; at k = 128 the two kernels tie or the tap-group one wins)
         return _conv2d_wgrad_patch(dy, x, dw, pad)
     key = ("wgrad", n, oh, ow, k, sn, sh, sw, h, w, c, xsn, xsh, xsw, R, S, stride, pad, bn)
 
@@ -441,7 +443,7 @@ def conv2d_wgrad(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, R: int, S:
 
 
 _WGRAD_PATCH = int(os.environ.get("DMPI_WGRAD_PATCH", "1"))  # 0 off, 1 automatic, 2 every eligible 3x3
-_WGRAD_PATCH_MAXC = int(os.environ.get("DMPI_WGRAD_PATCH_MAXC", "64"))
+_WGRAD_PATCH_MAXK = int(os.environ.get("DMPI_WGRAD_PATCH_MAXK", "64"))
 
 
 def _conv2d_wgrad_patch(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, pad: int) -> None:
