@@ -182,10 +182,18 @@ def _patch_ok(R, S, stride, pad, c_in, ow, oh, n_out=64):
     56x56x64 3x3); with streamed filter taps the weight traffic dominates and it only ties (DMPI_PATCH=2 forces it)."""
     if not _PATCH or R != S or R != 3 or stride != 1 or pad != 1 or c_in % 64 != 0:
         return None
-    if _PATCH != 2 and not (c_in == 64 and n_out <= 64):
+    if _PATCH != 2 and n_out > 64:  # bench/igemm_patch_ab.py: 64->64 1.5-1.9x, 128/192->64 +5-12 %, N >= 128 ties
         return None
     t = choose_patch_tile(ow, oh, pad)
     if t is None or t[2] < _PATCH_MIN_EFF:
+        return None
+    # two patch stages plus at least two filter-tap tiles must fit in the kernel's operand ring (igemm.cu: kRingBytes)
+    bn = _pick_bn(n_out, 9 * c_in)
+    ring = {64: 192, 128: 160, 256: 144}[bn] * 1024
+    pw = t[0] + 2 * pad
+    rows = max(128 + 2 * pad * pw + 2 * pad, pw * (t[1] + 2 * pad))
+    stride = -(-rows * 128 // 1024) * 1024
+    if ring - 2 * stride < 2 * bn * 128:
         return None
     return t
 
