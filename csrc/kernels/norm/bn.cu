@@ -36,6 +36,8 @@ struct BnFwdArgs {
   long long* num_batches_tracked;
   float eps, momentum;
   int training, relu;
+  uint8_t* relu_mask;  // optional [M, C/8]: bit j of byte (row, c/8) = (out[row, c + j] > 0); lets the backward pass
+                       // read 1/16 of the bytes of `out` for the ReLU gate of a residual block
 };
 
 __global__ void __launch_bounds__(kBnThreads) bn_fwd_kernel(const BnFwdArgs a) {
@@ -102,6 +104,7 @@ __global__ void __launch_bounds__(kBnThreads) bn_fwd_kernel(const BnFwdArgs a) {
       const uint32_t vi[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
       const uint32_t ri[4] = {r[u].x, r[u].y, r[u].z, r[u].w};
       uint32_t oi[4];
+      uint32_t bits = 0;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         float lo = fmaf(bf16lo(vi[j]), sc[2 * j], sh[2 * j]) + bf16lo(ri[j]);
@@ -111,10 +114,25 @@ __global__ void __launch_bounds__(kBnThreads) bn_fwd_kernel(const BnFwdArgs a) {
           hi = fmaxf(hi, 0.f);
         }
         oi[j] = pack_bf16x2(lo, hi);
+        // the gate the backward pass uses is (stored bf16 value > 0)
+        bits |= ((oi[j] & 0x7FFFu) != 0u && !(oi[j] & 0x8000u) ? 1u : 0u) << (2 * j);
+        bits |= ((oi[j] & 0x7FFF0000u) != 0u && !(oi[j] & 0x80000000u) ? 1u : 0u) << (2 * j + 1);
       }
       *reinterpret_cast<uint4*>(a.out + (u == 0 ? row : row2) * a.ldo + c0) = make_uint4(oi[0], oi[1], oi[2], oi[3]);
+      if (a.relu_mask) a.relu_mask[(u == 0 ? row : row2) * vecC + tx] = static_cast<uint8_t>(bits);
     }
   }
+}
+
+// Expands the 8 gate bits of one (row, 8-channel group) into the bf16x2 layout of an activation vector (1.0 / 0.0),
+// so that the gate tests below work unchanged on either source.
+__device__ __forceinline__ uint4 expand_relu_bits(uint32_t b) {
+  uint4 v;
+  v.x = ((b & 1u) ? 0x3f80u : 0u) | ((b & 2u) ? 0x3f800000u : 0u);
+  v.y = ((b & 4u) ? 0x3f80u : 0u) | ((b & 8u) ? 0x3f800000u : 0u);
+  v.z = ((b & 16u) ? 0x3f80u : 0u) | ((b & 32u) ? 0x3f800000u : 0u);
+  v.w = ((b & 64u) ? 0x3f80u : 0u) | ((b & 128u) ? 0x3f800000u : 0u);
+  return v;
 }
 
 struct BnBwdArgs {
@@ -133,6 +151,7 @@ struct BnBwdArgs {
   float* dgamma;  // parameter gradients, accumulated (+=) by the apply pass
   float* dbeta;
   const float* beta;  // only for relu_from_y
+  const uint8_t* relu_mask;  // bit mask written by the forward pass (replaces `act` as the gate source when set)
   int relu_from_y;    // ReLU mask recomputed as (y*scale + shift > 0) instead of being read from `act`: exact for a
                       // BatchNorm+ReLU without residual (same fp32 fma as the forward) and saves one tensor read per pass
 };
@@ -170,11 +189,13 @@ __global__ void __launch_bounds__(kBnThreads, 4) bn_bwd_reduce_kernel(const BnBw
       av[0] = av[1] = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);
       g[0] = *reinterpret_cast<const uint4*>(a.dout + row * a.ld_dout + c0);
       yv[0] = *reinterpret_cast<const uint4*>(a.y + row * a.ldy + c0);
-      if (!kFromY && a.act) av[0] = *reinterpret_cast<const uint4*>(a.act + row * a.ld_act + c0);
+      if (!kFromY && a.relu_mask) av[0] = expand_relu_bits(a.relu_mask[row * vecC + tx]);
+      else if (!kFromY && a.act) av[0] = *reinterpret_cast<const uint4*>(a.act + row * a.ld_act + c0);
       if (has2) {
         g[1] = *reinterpret_cast<const uint4*>(a.dout + row2 * a.ld_dout + c0);
         yv[1] = *reinterpret_cast<const uint4*>(a.y + row2 * a.ldy + c0);
-        if (!kFromY && a.act) av[1] = *reinterpret_cast<const uint4*>(a.act + row2 * a.ld_act + c0);
+        if (!kFromY && a.relu_mask) av[1] = expand_relu_bits(a.relu_mask[row2 * vecC + tx]);
+        else if (!kFromY && a.act) av[1] = *reinterpret_cast<const uint4*>(a.act + row2 * a.ld_act + c0);
       }
 #pragma unroll
       for (int u = 0; u < 2; ++u) {
@@ -197,7 +218,7 @@ __global__ void __launch_bounds__(kBnThreads, 4) bn_bwd_reduce_kernel(const BnBw
         }
         // The masked gradient is the residual branch's gradient; writing it here lets the apply pass read it back
         // instead of dout + act (one tensor read less).
-        if (!kFromY && a.dres && a.act)
+        if (!kFromY && a.dres && (a.act || a.relu_mask))
           *reinterpret_cast<uint4*>(a.dres + (u == 0 ? row : row2) * a.ld_dres + c0) = make_uint4(ri[0], ri[1], ri[2], ri[3]);
       }
     }
@@ -261,17 +282,20 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_kernel(const BnBwdArg
     const bool has2 = row2 < a.M;
     uint4 g[2], yv[2], av[2];
     // with a residual branch the reduce pass already stored the masked gradient in dres: read that back
-    const bool masked = a.dres != nullptr && a.act != nullptr;
+    const bool has_gate = a.act != nullptr || a.relu_mask != nullptr;
+    const bool masked = a.dres != nullptr && has_gate;
     const __nv_bfloat16* gsrc = masked ? a.dres : a.dout;
     const long long ldg = masked ? a.ld_dres : a.ld_dout;
     g[0] = *reinterpret_cast<const uint4*>(gsrc + row * ldg + c0);
     yv[0] = *reinterpret_cast<const uint4*>(a.y + row * a.ldy + c0);
     av[0] = av[1] = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);
-    if (a.act && !masked) av[0] = *reinterpret_cast<const uint4*>(a.act + row * a.ld_act + c0);
+    if (a.relu_mask && !masked) av[0] = expand_relu_bits(a.relu_mask[row * vecC + tx]);
+    else if (a.act && !masked) av[0] = *reinterpret_cast<const uint4*>(a.act + row * a.ld_act + c0);
     if (has2) {
       g[1] = *reinterpret_cast<const uint4*>(gsrc + row2 * ldg + c0);
       yv[1] = *reinterpret_cast<const uint4*>(a.y + row2 * a.ldy + c0);
-      if (a.act && !masked) av[1] = *reinterpret_cast<const uint4*>(a.act + row2 * a.ld_act + c0);
+      if (a.relu_mask && !masked) av[1] = expand_relu_bits(a.relu_mask[row2 * vecC + tx]);
+      else if (a.act && !masked) av[1] = *reinterpret_cast<const uint4*>(a.act + row2 * a.ld_act + c0);
     }
 #pragma unroll
     for (int u = 0; u < 2; ++u) {
@@ -365,13 +389,31 @@ static int grid_for(long long work_items, int threads) {
 
 using namespace dmpi;
 
+extern "C" int dmpi_bn_forward_mask(const void* y, const void* res, void* out, long long M, int C, long long ldy,
+                                    long long ldr, long long ldo, const float* sum, const float* sqsum,
+                                    const float* gamma, const float* beta, float* save_mean, float* save_invstd,
+                                    float* running_mean, float* running_var, long long* num_batches_tracked, float eps,
+                                    float momentum, int training, int relu, void* relu_mask, void* stream);
+
 extern "C" int dmpi_bn_forward(const void* y, const void* res, void* out, long long M, int C, long long ldy,
                                long long ldr, long long ldo, const float* sum, const float* sqsum, const float* gamma,
                                const float* beta, float* save_mean, float* save_invstd, float* running_mean,
                                float* running_var, long long* num_batches_tracked, float eps, float momentum,
                                int training, int relu, void* stream) {
+  return dmpi_bn_forward_mask(y, res, out, M, C, ldy, ldr, ldo, sum, sqsum, gamma, beta, save_mean, save_invstd,
+                              running_mean, running_var, num_batches_tracked, eps, momentum, training, relu, nullptr,
+                              stream);
+}
+
+// `relu_mask` (optional, [M, C/8] bytes): receives one bit per output element, set where the stored value is > 0.
+extern "C" int dmpi_bn_forward_mask(const void* y, const void* res, void* out, long long M, int C, long long ldy,
+                                    long long ldr, long long ldo, const float* sum, const float* sqsum,
+                                    const float* gamma, const float* beta, float* save_mean, float* save_invstd,
+                                    float* running_mean, float* running_var, long long* num_batches_tracked, float eps,
+                                    float momentum, int training, int relu, void* relu_mask, void* stream) {
   if (C % 8 != 0 || C > kMaxC) return -1;
   BnFwdArgs a;
+  a.relu_mask = static_cast<uint8_t*>(relu_mask);
   a.y = static_cast<const __nv_bfloat16*>(y);
   a.res = static_cast<const __nv_bfloat16*>(res);
   a.out = static_cast<__nv_bfloat16*>(out);
@@ -418,11 +460,27 @@ extern "C" int dmpi_bn_backward(const void* dout, const void* y, const void* act
                              nullptr, 0, acc, dgamma, dbeta, stream);
 }
 
+extern "C" int dmpi_bn_backward_mask(const void* dout, const void* y, const void* act, void* dy, void* dres, long long M,
+                                     int C, long long ld_dout, long long ldy, long long ld_act, long long ld_dy,
+                                     long long ld_dres, const float* mean, const float* invstd, const float* gamma,
+                                     const float* beta, int relu_from_y, const void* relu_mask, float* acc,
+                                     float* dgamma, float* dbeta, void* stream);
+
 extern "C" int dmpi_bn_backward_ex(const void* dout, const void* y, const void* act, void* dy, void* dres, long long M,
                                    int C, long long ld_dout, long long ldy, long long ld_act, long long ld_dy,
                                    long long ld_dres, const float* mean, const float* invstd, const float* gamma,
                                    const float* beta, int relu_from_y, float* acc, float* dgamma, float* dbeta,
                                    void* stream) {
+  return dmpi_bn_backward_mask(dout, y, act, dy, dres, M, C, ld_dout, ldy, ld_act, ld_dy, ld_dres, mean, invstd, gamma,
+                               beta, relu_from_y, nullptr, acc, dgamma, dbeta, stream);
+}
+
+// `relu_mask` (optional): the bit mask dmpi_bn_forward_mask wrote; used as the ReLU gate instead of `act`.
+extern "C" int dmpi_bn_backward_mask(const void* dout, const void* y, const void* act, void* dy, void* dres, long long M,
+                                     int C, long long ld_dout, long long ldy, long long ld_act, long long ld_dy,
+                                     long long ld_dres, const float* mean, const float* invstd, const float* gamma,
+                                     const float* beta, int relu_from_y, const void* relu_mask, float* acc,
+                                     float* dgamma, float* dbeta, void* stream) {
   if (C % 8 != 0) return -1;
   const int vecC = C / 8;
   BnBwdArgs a;
@@ -445,7 +503,9 @@ extern "C" int dmpi_bn_backward_ex(const void* dout, const void* y, const void* 
   a.dgamma = dgamma;
   a.dbeta = dbeta;
   a.beta = beta;
-  a.relu_from_y = (relu_from_y && act == nullptr) ? 1 : 0;
+  a.relu_mask = static_cast<const uint8_t*>(relu_mask);
+  if (a.relu_mask) a.act = nullptr;
+  a.relu_from_y = (relu_from_y && act == nullptr && relu_mask == nullptr) ? 1 : 0;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   // reduce: block = vecC * rows_per_block threads (vecC <= 256 for C <= 2048)
   int threads = kBnThreads;

@@ -8,6 +8,7 @@ autograd knows the function needs a backward pass.
 """
 from __future__ import annotations
 
+import os
 from typing import Optional
 
 import torch
@@ -15,6 +16,9 @@ import torch.nn as nn
 
 from . import conv as CV
 from . import kernels as K
+
+
+_RELU_MASK = os.environ.get("DMPI_NOMASK", "0") != "1"  # A/B switch for the ReLU bit mask of residual blocks
 
 
 def _nb(t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
@@ -81,9 +85,16 @@ class ConvBnAct(torch.autograd.Function):
         invstd = torch.empty(c, dtype=torch.float32, device=y.device) if training else None
         track = bn.track_running_stats and bn.running_mean is not None
         momentum = bn.momentum if bn.momentum is not None else 0.1
+        # residual + ReLU: the backward gate cannot be recomputed from y alone; one bit per element is 1/16 of the
+        # bytes of re-reading `out`
+        mask = None
+        if training and relu and residual is not None and torch.is_grad_enabled() and _RELU_MASK:
+            mask = torch.empty((y.numel() // 8,), dtype=torch.uint8, device=y.device)
         K.bn_forward(y, residual, out, stats[0] if training else None, stats[1] if training else None, _nb(gamma),
                      _nb(beta), mean, invstd, bn.running_mean if track else None, bn.running_var if track else None,
-                     bn.num_batches_tracked if (track and training) else None, bn.eps, momentum, training, relu)
+                     bn.num_batches_tracked if (track and training) else None, bn.eps, momentum, training, relu,
+                     relu_mask=mask)
+        ctx.relu_mask = mask
         ctx.conv, ctx.bn, ctx.arena, ctx.relu, ctx.is_stem = conv, bn, arena, relu, is_stem
         ctx.has_res = residual is not None
         ctx.link, ctx.link_role = link, link_role
@@ -105,9 +116,10 @@ class ConvBnAct(torch.autograd.Function):
         dres = torch.empty_like(y) if ctx.has_res else None
         # Without a residual the ReLU gate is a function of y alone: recompute it instead of reading `out` again.
         from_y = ctx.relu and not ctx.has_res
-        K.bn_backward(dout, y, out if (ctx.relu and not from_y) else None, dy, dres, mean, invstd, gamma.detach(),
-                      arena.bn_acc(bn), arena.grad_physical(gamma), arena.grad_physical(beta), beta=beta.detach(),
-                      relu_from_y=from_y)
+        mask = ctx.relu_mask
+        K.bn_backward(dout, y, out if (ctx.relu and not from_y and mask is None) else None, dy, dres, mean, invstd,
+                      gamma.detach(), arena.bn_acc(bn), arena.grad_physical(gamma), arena.grad_physical(beta),
+                      beta=beta.detach(), relu_from_y=from_y, relu_mask=mask)
         arena.grad_ready(gamma)
         arena.grad_ready(beta)
         if bias is not None:

@@ -34,29 +34,33 @@ def _rows_ld(x: torch.Tensor) -> Tuple[int, int]:
 
 # ------------------------------------------------------------------------------------------ BatchNorm
 def bn_forward(y, res, out, ssum, ssq, gamma, beta, save_mean, save_invstd, running_mean, running_var, nbt,
-               eps: float, momentum: float, training: bool, relu: bool) -> None:
+               eps: float, momentum: float, training: bool, relu: bool, relu_mask=None) -> None:
+    """``relu_mask`` (uint8 [M, C/8], optional) receives one bit per output element (value > 0) for the backward pass."""
     M, ldy = _rows_ld(y)
     _, ldo = _rows_ld(out)
     ldr = _rows_ld(res)[1] if res is not None else 0
     C = y.shape[-1]
-    rc = N.cuda().dmpi_bn_forward(_p(y), _p(res), _p(out), M, C, ldy, ldr, ldo, _p(ssum), _p(ssq), _p(gamma), _p(beta),
-                                  _p(save_mean), _p(save_invstd), _p(running_mean), _p(running_var), _p(nbt),
-                                  float(eps), float(momentum), int(training), int(relu), N.stream_ptr())
+    rc = N.cuda().dmpi_bn_forward_mask(_p(y), _p(res), _p(out), M, C, ldy, ldr, ldo, _p(ssum), _p(ssq), _p(gamma),
+                                       _p(beta), _p(save_mean), _p(save_invstd), _p(running_mean), _p(running_var),
+                                       _p(nbt), float(eps), float(momentum), int(training), int(relu), _p(relu_mask),
+                                       N.stream_ptr())
     N.count_launch()
     _chk(rc, "dmpi_bn_forward")
 
 
-def bn_backward(dout, y, act, dy, dres, mean, invstd, gamma, acc, dgamma, dbeta, beta=None, relu_from_y=False) -> None:
-    """``relu_from_y`` (with ``act=None``): the ReLU mask is recomputed from y instead of read from the forward output."""
+def bn_backward(dout, y, act, dy, dres, mean, invstd, gamma, acc, dgamma, dbeta, beta=None, relu_from_y=False,
+                relu_mask=None) -> None:
+    """ReLU gate source, in order of preference: ``relu_mask`` (bits written by bn_forward), ``relu_from_y`` (recomputed
+    from y, exact without a residual), ``act`` (the forward output)."""
     M, ld_dout = _rows_ld(dout)
     _, ldy = _rows_ld(y)
     ld_act = _rows_ld(act)[1] if act is not None else 0
     _, ld_dy = _rows_ld(dy)
     ld_dres = _rows_ld(dres)[1] if dres is not None else 0
     C = y.shape[-1]
-    rc = N.cuda().dmpi_bn_backward_ex(_p(dout), _p(y), _p(act), _p(dy), _p(dres), M, C, ld_dout, ldy, ld_act, ld_dy,
-                                      ld_dres, _p(mean), _p(invstd), _p(gamma), _p(beta), int(relu_from_y), _p(acc),
-                                      _p(dgamma), _p(dbeta), N.stream_ptr())
+    rc = N.cuda().dmpi_bn_backward_mask(_p(dout), _p(y), _p(act), _p(dy), _p(dres), M, C, ld_dout, ldy, ld_act, ld_dy,
+                                        ld_dres, _p(mean), _p(invstd), _p(gamma), _p(beta), int(relu_from_y),
+                                        _p(relu_mask), _p(acc), _p(dgamma), _p(dbeta), N.stream_ptr())
     N.count_launch(2)
     _chk(rc, "dmpi_bn_backward")
 

@@ -33,6 +33,18 @@ int dmpi_bn_backward_ex(const void* dout, const void* y, const void* act, void* 
                         long long ld_dout, long long ldy, long long ld_act, long long ld_dy, long long ld_dres,
                         const float* mean, const float* invstd, const float* gamma, const float* beta, int relu_from_y,
                         float* acc, float* dgamma, float* dbeta, void* stream);
+/* ReLU bit mask variants: the forward pass also writes one bit per output element (set where the stored value is > 0,
+ * [M, C/8] bytes) and the backward pass takes its ReLU gate from those bits instead of re-reading the activation. */
+int dmpi_bn_forward_mask(const void* y, const void* res, void* out, long long M, int C, long long ldy, long long ldr,
+                         long long ldo, const float* sum, const float* sqsum, const float* gamma, const float* beta,
+                         float* save_mean, float* save_invstd, float* running_mean, float* running_var,
+                         long long* num_batches_tracked, float eps, float momentum, int training, int relu,
+                         void* relu_mask, void* stream);
+int dmpi_bn_backward_mask(const void* dout, const void* y, const void* act, void* dy, void* dres, long long M, int C,
+                          long long ld_dout, long long ldy, long long ld_act, long long ld_dy, long long ld_dres,
+                          const float* mean, const float* invstd, const float* gamma, const float* beta,
+                          int relu_from_y, const void* relu_mask, float* acc, float* dgamma, float* dbeta,
+                          void* stream);
 /* Same computation for callers that cannot allocate the scratch (GPU memory fully owned by the host application's
  * pool, latency-critical paths where cudaMalloc/cudaFree would stall the device, plug-ins barred from any allocator).
  * This entry point has no counterpart in the reference; it exists for such embedders only.

@@ -71,6 +71,25 @@ def test_bn_forward_backward(shape, res, relu):
     _close(dbeta, b_ref.grad, 1e-2, "bn_dbeta")
     if res:
         _close(dres, rr.grad.permute(0, 2, 3, 1), 1e-2, "bn_dres")
+    if relu:
+        # the bit mask written by the forward pass must reproduce the gate read from the forward output
+        mask = torch.zeros(y.numel() // 8, dtype=torch.uint8, device=DEV)
+        out_m = torch.empty_like(y)
+        rm_m, rv_m = torch.zeros(c, device=DEV), torch.ones(c, device=DEV)
+        K.bn_forward(y, r, out_m, ssum, ssq, gamma, beta, mean, invstd, rm_m, rv_m, None, 1e-5, 0.1, True, relu,
+                     relu_mask=mask)
+        assert torch.equal(out_m, out)
+        bits = (out.view(-1, 8) > 0).to(torch.int32) * (1 << torch.arange(8, device=DEV, dtype=torch.int32))
+        assert torch.equal(mask.to(torch.int32), bits.sum(1)), "ReLU bit mask differs from (out > 0)"
+        dy3 = torch.empty_like(y)
+        dres3 = torch.empty_like(y) if res else None
+        acc3 = torch.zeros(2 * c, device=DEV)
+        dg3, db3 = torch.zeros(c, device=DEV), torch.zeros(c, device=DEV)
+        K.bn_backward(dout, y, None, dy3, dres3, mean, invstd, gamma, acc3, dg3, db3, relu_mask=mask)
+        _close(dy3, dy, 1e-2, "bn_dy_mask")
+        _close(dg3, dgamma, 1e-5, "bn_dgamma_mask")
+        if res:
+            assert torch.equal(dres3, dres), "masked residual gradient differs"
     if relu and not res:
         # the gate recomputed from y must reproduce the gate read from the forward output exactly
         dy2 = torch.empty_like(y)
