@@ -12,6 +12,7 @@
 //
 // Replaces cuDNN wgrad / cuBLAS dW GEMMs.
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "../../common/ptx.cuh"
 #include "../../common/tensormap.h"
@@ -26,24 +27,28 @@ constexpr int kWABytes = 2 * kAtomBytes;    // M = 128
 
 constexpr int pow2_cols(int c) { return c <= 32 ? 32 : c <= 64 ? 64 : c <= 128 ? 128 : c <= 256 ? 256 : 512; }
 
-template <int BN, int G>
+// CG = 2: a CTA pair (tcgen05.mma.cta_group::2) covers TWO 128-filter tiles of the same (tap group, channel tile,
+// pixel slice); each CTA loads its own dY tile and only half of the X tile, which both tensor cores share.
+template <int BN, int G, int CG = 1>
 struct WgradCfg {
-  static constexpr int kBTapBytes = (BN / 64) * kAtomBytes;
+  static constexpr int kBAtoms = BN / CG / 64;  // 64-channel X atoms this CTA loads per tap
+  static constexpr int kBTapBytes = kBAtoms * kAtomBytes;
   static constexpr int kStageBytes = kWABytes + G * kBTapBytes;
   static constexpr int kStages = (220 * 1024) / kStageBytes > 8 ? 8 : (220 * 1024) / kStageBytes;
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256;
   static constexpr int kTmemCols = pow2_cols(G * BN);
   static_assert(G * BN <= 512, "accumulators exceed TMEM");
   static_assert(kStages >= 2, "pipeline too shallow");
+  static_assert(CG == 1 || (G == 1 && BN >= 128), "CTA pairs: single-tap wide tiles only");
 };
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
-template <int BN, int G>
+template <int BN, int G, int CG>
 __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_constant__ ConvKernelParams p) {
-  using Cfg = WgradCfg<BN, G>;
+  using Cfg = WgradCfg<BN, G, CG>;
   constexpr int S = Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -56,9 +61,11 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
-  // tile decode: blockIdx.x = ((tap_group * num_k_tiles + k_blk) * num_c_tiles + c_blk), blockIdx.y = split
-  const int c_blk = blockIdx.x % p.num_c_tiles;
-  const int k_blk = (blockIdx.x / p.num_c_tiles) % p.num_k_tiles;
+  // tile decode: blockIdx.x = ((tap_group * num_k_tiles + k_blk) * num_c_tiles + c_blk), blockIdx.y = split;
+  // with CTA pairs k_blk is the fastest index so that the two CTAs of a cluster own filter tiles 2j and 2j+1
+  const int rank = CG == 2 ? static_cast<int>(cluster_ctarank()) : 0;
+  const int c_blk = CG == 2 ? (blockIdx.x / p.num_k_tiles) % p.num_c_tiles : blockIdx.x % p.num_c_tiles;
+  const int k_blk = CG == 2 ? blockIdx.x % p.num_k_tiles : (blockIdx.x / p.num_c_tiles) % p.num_k_tiles;
   const int tap0 = (blockIdx.x / (p.num_c_tiles * p.num_k_tiles)) * G;
   const int ntap = (p.ntaps - tap0) < G ? (p.ntaps - tap0) : G;
   const int split = blockIdx.y;
@@ -73,15 +80,19 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < S; ++i) {
-      mbar_init(&full[i], 1);
+      mbar_init(&full[i], CG);
       mbar_init(&empty[i], 1);
     }
     mbar_init(tfull, 1);
     fence_mbar_init();
   }
-  if (warp == 2) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  if (warp == 2) {
+    if (CG == 2) tmem_alloc_pair<Cfg::kTmemCols>(tmem_slot);
+    else tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  }
   tc_fence_before_sync();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all();
+  else __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -97,22 +108,37 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
           const int th = (m_blk / p.tiles_w) % p.tiles_h;
           const int tn = m_blk / (p.tiles_w * p.tiles_h);
           const int w0 = tw * p.box_w, h0 = th * p.box_h, n0 = tn * p.box_n;
-          mbar_wait(&empty[stage], phase ^ 1u);
-          mbar_arrive_expect_tx(&full[stage], tx_bytes);
+          mbar_wait_spin(&empty[stage], phase ^ 1u);
           uint8_t* sa = smem + stage * Cfg::kStageBytes;
           uint8_t* sb = sa + kWABytes;
+          if (CG == 2) {
+            // both CTAs report to the leader's barrier; the leader registers the bytes of the pair
+            const uint32_t lead_full = mapa_u32(smem_u32(&full[stage]), 0);
+            if (rank == 0) mbar_arrive_expect_tx(&full[stage], 2 * tx_bytes);
+            else mbar_arrive_cluster(lead_full);
 #pragma unroll
-          for (int j = 0; j < 2; ++j)
-            tma_load_4d(sa + j * kAtomBytes, &p.b_map, &full[stage], k_blk * 128 + j * 64, w0, h0, n0);
+            for (int j = 0; j < 2; ++j)
+              tma_load_4d_pair(sa + j * kAtomBytes, &p.b_map, lead_full, k_blk * 128 + j * 64, w0, h0, n0);
+            const CUtensorMap* xmap = &p.a_map[p.tap_view[tap0]];
 #pragma unroll
-          for (int g = 0; g < G; ++g) {
-            if (g < ntap) {
-              const int t = tap0 + g;
-              const CUtensorMap* xmap = &p.a_map[p.tap_view[t]];
+            for (int j = 0; j < Cfg::kBAtoms; ++j)
+              tma_load_4d_pair(sb + j * kAtomBytes, xmap, lead_full, c_blk * BN + (rank * Cfg::kBAtoms + j) * 64,
+                               w0 + p.tap_dw[tap0], h0 + p.tap_dh[tap0], n0);
+          } else {
+            mbar_arrive_expect_tx(&full[stage], tx_bytes);
 #pragma unroll
-              for (int j = 0; j < BN / 64; ++j)
-                tma_load_4d(sb + g * Cfg::kBTapBytes + j * kAtomBytes, xmap, &full[stage], c_blk * BN + j * 64,
-                            w0 + p.tap_dw[t], h0 + p.tap_dh[t], n0);
+            for (int j = 0; j < 2; ++j)
+              tma_load_4d(sa + j * kAtomBytes, &p.b_map, &full[stage], k_blk * 128 + j * 64, w0, h0, n0);
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+              if (g < ntap) {
+                const int t = tap0 + g;
+                const CUtensorMap* xmap = &p.a_map[p.tap_view[t]];
+#pragma unroll
+                for (int j = 0; j < BN / 64; ++j)
+                  tma_load_4d(sb + g * Cfg::kBTapBytes + j * kAtomBytes, xmap, &full[stage], c_blk * BN + j * 64,
+                              w0 + p.tap_dw[t], h0 + p.tap_dh[t], n0);
+              }
             }
           }
           if (++stage == S) {
@@ -124,8 +150,8 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
       __syncwarp();
     } else if (warp == 1) {
       // warp-uniform loop, one elected lane issues (see elect_one() in ptx.cuh); split descriptors: one add per MMA
-      const bool leader = elect_one();
-      constexpr uint32_t idesc = umma_idesc_bf16(128, BN, 1, 1);
+      const bool leader = elect_one() && rank == 0;  // of a pair only the leader CTA issues
+      constexpr uint32_t idesc = umma_idesc_bf16(128 * CG, BN, 1, 1);
       const uint32_t hi = umma_desc_hi(1024);
       // MN-major, 128B swizzle: LBO = stride between 64-channel atoms, SBO = stride between 8-pixel groups;
       // one MMA consumes 16 pixels = 2048 bytes (128 descriptor units) of every atom.
@@ -136,29 +162,40 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
       int stage = 0;
       uint32_t phase = 0;
       uint32_t accum = 0;
-      for (int it = 0; it < num_it; ++it) {
-        mbar_wait_spin(&full[stage], phase);
-        tc_fence_after_sync();
-        const uint32_t a_lo = a_lo_ring + static_cast<uint32_t>(stage) * stage_step;
-        if (leader) {
+      if (CG == 1 || rank == 0) {
+        for (int it = 0; it < num_it; ++it) {
+          mbar_wait_spin(&full[stage], phase);
+          tc_fence_after_sync();
+          const uint32_t a_lo = a_lo_ring + static_cast<uint32_t>(stage) * stage_step;
+          if (leader) {
 #pragma unroll
-          for (int g = 0; g < G; ++g) {
-            if (g < ntap) {
+            for (int g = 0; g < G; ++g) {
+              if (g < ntap) {
 #pragma unroll
-              for (int k = 0; k < kPix / 16; ++k)
-                umma_bf16_lohi(tmem_base + g * BN, a_lo + k * 128, hi, a_lo + b_off + g * tap_step + k * 128, hi, idesc,
-                               k == 0 ? accum : 1u);
+                for (int k = 0; k < kPix / 16; ++k) {
+                  if (CG == 2)
+                    umma_bf16_pair_lohi(tmem_base + g * BN, a_lo + k * 128, hi, a_lo + b_off + g * tap_step + k * 128,
+                                        hi, idesc, k == 0 ? accum : 1u);
+                  else
+                    umma_bf16_lohi(tmem_base + g * BN, a_lo + k * 128, hi, a_lo + b_off + g * tap_step + k * 128, hi,
+                                   idesc, k == 0 ? accum : 1u);
+                }
+              }
             }
+            if (CG == 2) umma_commit_pair(&empty[stage], 0b11);
+            else umma_commit(&empty[stage]);
           }
-          umma_commit(&empty[stage]);
+          accum = 1u;
+          if (++stage == S) {
+            stage = 0;
+            phase ^= 1u;
+          }
         }
-        accum = 1u;
-        if (++stage == S) {
-          stage = 0;
-          phase ^= 1u;
+        if (leader) {
+          if (CG == 2) umma_commit_pair(tfull, 0b11);
+          else umma_commit(tfull);
         }
       }
-      if (leader) umma_commit(tfull);
       __syncwarp();
     } else if (warp >= 4) {
       const int q = warp - 4;
@@ -188,22 +225,43 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
     }
   }
   tc_fence_before_sync();
-  __syncthreads();
-  if (warp == 2) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+  if (CG == 2) {
+    cluster_sync_all();
+    if (warp == 2) tmem_dealloc_pair<Cfg::kTmemCols>(tmem_base);
+  } else {
+    __syncthreads();
+    if (warp == 2) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+  }
 }
 
-template <int BN, int G>
+template <int BN, int G, int CG = 1>
 static int launch_wgrad(const ConvKernelParams& kp, cudaStream_t stream) {
+  using Cfg = WgradCfg<BN, G, CG>;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(wgrad_kernel<BN, G>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         WgradCfg<BN, G>::kSmemBytes);
+    cudaError_t e =
+        cudaFuncSetAttribute(wgrad_kernel<BN, G, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
     if (e != cudaSuccess) return -10;
     attr_set = true;
   }
   const int groups = (kp.ntaps + G - 1) / G;
   dim3 grid(groups * kp.num_k_tiles * kp.num_c_tiles, kp.splits, 1);
-  wgrad_kernel<BN, G><<<grid, kWThreads, WgradCfg<BN, G>::kSmemBytes, stream>>>(kp);
+  if (CG == 2) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;  // k_blk is the fastest index and num_k_tiles is even: clusters pair filter tiles 2j, 2j+1
+    cfg.blockDim = dim3(kWThreads, 1, 1);
+    cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, wgrad_kernel<BN, G, CG>, kp) == cudaSuccess ? 0 : -11;
+  }
+  wgrad_kernel<BN, G, CG><<<grid, kWThreads, Cfg::kSmemBytes, stream>>>(kp);
   return cudaGetLastError() == cudaSuccess ? 0 : -11;
 }
 
@@ -249,9 +307,11 @@ extern "C" int dmpi_wgrad_run(dmpi_conv_plan* plan, const void* dy, const void* 
   int splits = d.splits;
   if (splits <= 0) {
     const int tiles = groups * kp.num_k_tiles * kp.num_c_tiles;
-    // as many CTAs as fit in two full waves, never a few more (a third wave with a handful of CTAs costs a whole
-    // wave of time: 3 tiles x 99 splits = 297 CTAs on 148 SMs)
-    splits = (2 * plan->num_sms) / tiles;
+    // ONE full wave of CTAs: every CTA pays a fixed prologue (TMEM allocation, pipeline fill) and an epilogue that adds
+    // a whole 128 x BN fp32 tile into the gradient, so fewer, longer CTAs win (14x14 256->1024: 51 us at two waves,
+    // 42 us at one, 60 us at three), and never a partial extra wave.
+    static const int waves = getenv("DMPI_WGRAD_WAVES") ? atoi(getenv("DMPI_WGRAD_WAVES")) : 1;
+    splits = (waves * plan->num_sms) / tiles;
     const int max_splits = kp.num_m_tiles / 4 > 0 ? kp.num_m_tiles / 4 : 1;
     if (splits > max_splits) splits = max_splits;
     if (splits < 1) splits = 1;
@@ -264,6 +324,12 @@ extern "C" int dmpi_wgrad_run(dmpi_conv_plan* plan, const void* dy, const void* 
     if (G == 4) return launch_wgrad<64, 4>(kp, s);
     return launch_wgrad<64, 1>(kp, s);
   }
-  if (d.bn == 128) return G == 3 ? launch_wgrad<128, 3>(kp, s) : launch_wgrad<128, 1>(kp, s);
-  return launch_wgrad<256, 1>(kp, s);
+  // CTA pairs for the single-tap wide tiles when the filter tiles pair up (L2 -> SM traffic per FLOP drops by a third)
+  static const int cg_env = getenv("DMPI_WGRAD_CG") ? atoi(getenv("DMPI_WGRAD_CG")) : 2;
+  const bool pair = cg_env == 2 && G == 1 && kp.num_k_tiles % 2 == 0;
+  if (d.bn == 128) {
+    if (G == 3) return launch_wgrad<128, 3>(kp, s);
+    return pair ? launch_wgrad<128, 1, 2>(kp, s) : launch_wgrad<128, 1>(kp, s);
+  }
+  return pair ? launch_wgrad<256, 1, 2>(kp, s) : launch_wgrad<256, 1>(kp, s);
 }
