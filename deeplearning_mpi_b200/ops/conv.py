@@ -280,16 +280,19 @@ def conv2d_fprop(x: torch.Tensor, w2d: torch.Tensor, R: int, S: int, stride: int
 # --------------------------------------------------------------------------------------- dgrad
 def conv2d_dgrad(dy: torch.Tensor, wt2d: torch.Tensor, R: int, S: int, stride: int, pad: int,
                  in_hw: Tuple[int, int], out: Optional[torch.Tensor] = None,
-                 addend: Optional[torch.Tensor] = None) -> torch.Tensor:
+                 addend: Optional[torch.Tensor] = None, accumulate: bool = False) -> torch.Tensor:
     """dx[n,ih,iw,c] = sum_{r,s,k} dy[n,(ih+pad-r)/stride,(iw+pad-s)/stride,k] * wt2d[c, (r*S+s)*K + k] (+ addend).
 
     ``addend`` (stride-1 only): a bf16 NHWC tensor of dx's shape added in the kernel epilogue before rounding — the
-    gradient arriving at the same tensor through the residual branch, so no separate add kernel runs."""
+    gradient arriving at the same tensor through the residual branch, so no separate add kernel runs.
+    ``accumulate`` (stride-2 only, needs ``out``): the result is added onto what ``out`` already holds — each parity
+    class reads its own strided view of ``out`` as the addend; positions that receive no tap are left untouched."""
     n, oh, ow, k, sn, sh, sw = _nhwc_meta(dy)
     assert k % 64 == 0
     c = wt2d.shape[0]
     assert wt2d.shape[1] == R * S * k and wt2d.is_contiguous()
     ih, iw = in_hw
+    assert not accumulate or (out is not None and stride == 2)
     if out is None:
         out = (torch.zeros if (stride == 2 and R == 1) else torch.empty)(
             (n, ih, iw, c), dtype=torch.bfloat16, device=dy.device)
@@ -362,7 +365,7 @@ def conv2d_dgrad(dy: torch.Tensor, wt2d: torch.Tensor, R: int, S: int, stride: i
             if sub_h <= 0 or sub_w <= 0:
                 continue
             if not rs or not ss:
-                if not (R == 1):
+                if not (R == 1) and not accumulate:
                     out[:, a::2, b::2, :].zero_()
                 continue
             key = ("dgrad2", a, b, n, oh, ow, k, sn, sh, sw, c, R, S, pad, ih, iw, osn, osh, osw, bn, cg)
@@ -391,7 +394,12 @@ def conv2d_dgrad(dy: torch.Tensor, wt2d: torch.Tensor, R: int, S: int, stride: i
                 d.cta_group = cg
                 return d
 
-            _run_igemm(_get_plan(key, build), dy, wt2d, out, None, None)
+            if accumulate:
+                view = out[:, a::2, b::2, :]  # same pixels and strides as the output view of this parity class
+                _run_igemm(_get_plan(key, build), dy, wt2d, out, None, None, view,
+                           (view.stride(0), view.stride(1), view.stride(2)))
+            else:
+                _run_igemm(_get_plan(key, build), dy, wt2d, out, None, None)
     return out
 
 

@@ -40,12 +40,12 @@ class GradLink:
     def __init__(self):
         self.grad = None
 
-    def give(self, g: torch.Tensor) -> None:
+    def give(self, g) -> None:  # a gradient tensor, or a callable that accumulates one onto the taker's result
         if self.grad is not None:
             raise RuntimeError("GradLink: a parked gradient was never consumed")
         self.grad = g
 
-    def take(self) -> torch.Tensor:
+    def take(self):
         g = self.grad
         if g is None:
             raise RuntimeError("GradLink: the residual-branch gradient was not produced before the main branch's dgrad")
@@ -136,8 +136,19 @@ class ConvBnAct(torch.autograd.Function):
         else:
             CV.conv2d_wgrad(dy, x, arena.grad_physical(weight), R, S, stride, pad)
             if ctx.needs_input_grad[0]:
-                addend = ctx.link.take() if ctx.link_role == "take" else None
-                dx = CV.conv2d_dgrad(dy, arena.w_transposed(weight), R, S, stride, pad, ctx.in_hw, addend=addend)
+                parked = ctx.link.take() if ctx.link_role == "take" else None
+                if ctx.link_role == "give_dx" and stride == 2:
+                    # strided downsample branch: park the dgrad itself; the main branch's dgrad runs it afterwards,
+                    # accumulating onto its own (dense) result — no zero-filled sparse tensor, no add kernel
+                    wt = arena.w_transposed(weight)
+                    in_hw = ctx.in_hw
+                    ctx.link.give(lambda dx_main: CV.conv2d_dgrad(dy, wt, R, S, stride, pad, in_hw, out=dx_main,
+                                                                    accumulate=True))
+                elif callable(parked):
+                    dx = CV.conv2d_dgrad(dy, arena.w_transposed(weight), R, S, stride, pad, ctx.in_hw)
+                    dx = parked(dx)
+                else:
+                    dx = CV.conv2d_dgrad(dy, arena.w_transposed(weight), R, S, stride, pad, ctx.in_hw, addend=parked)
         arena.grad_ready(weight)
         if ctx.link_role == "give_dx" and dx is not None:
             ctx.link.give(dx)

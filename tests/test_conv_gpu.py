@@ -128,6 +128,23 @@ def test_dgrad_addend(case):
     _close(dx, ref, 1e-2, f"dgrad_addend{case}")
 
 
+def test_dgrad_stride2_accumulate():
+    """Strided 1x1 (downsample) and 3x3 dgrad accumulated onto an existing tensor through the parity views."""
+    from deeplearning_mpi_b200.ops import conv as C
+
+    _torch_setup()
+    for (n, h, c, k, R, pad) in [(2, 28, 256, 512, 1, 0), (2, 14, 128, 128, 3, 1)]:
+        oh = (h + 2 * pad - R) // 2 + 1
+        dy = _rand(n, oh, oh, k)
+        wt = _rand(k, c, R, R, scale=(k * R * R) ** -0.5)
+        base = _rand(n, h, h, c)
+        out = base.clone()
+        C.conv2d_dgrad(dy, _wt2d(wt), R, R, 2, pad, (h, h), out=out, accumulate=True)
+        ref = torch.nn.grad.conv2d_input((n, c, h, h), wt.float(), dy.float().permute(0, 3, 1, 2), stride=2,
+                                         padding=pad).permute(0, 2, 3, 1) + base.float()
+        _close(out, ref, 1e-2, f"dgrad_s2_accumulate{(n, h, c, k, R)}")
+
+
 def test_fprop_many_tiles_per_cta():
     """More tiles than SMs x pipeline depth: exercises the persistent loop, both accumulator stages, both staging
     buffers and the register-resident statistics for every tile width (BN = 64, 128, 256)."""
