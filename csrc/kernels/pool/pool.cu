@@ -121,6 +121,69 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const __nv_bfloat16* _
   }
 }
 
+// Compile-time (K, S, P) variant of the backward pass: the generic kernel above is issue-bound (~500 instructions per
+// 8-channel item: runtime divisions, per-channel byte extraction); here the candidate windows are an unrolled K x K
+// loop with constant tap ids, the "is this pixel the arg-max" test is a 4-byte SIMD compare and the masking of the
+// bf16 pairs is two byte permutes per 32-bit word.
+template <int K, int S, int P>
+__global__ void __launch_bounds__(256) maxpool_bwd_fixed_kernel(const __nv_bfloat16* __restrict__ dy,
+                                                                const uint8_t* __restrict__ idx,
+                                                                __nv_bfloat16* __restrict__ dx, int N, int H, int W,
+                                                                int C, int OH, int OW, long long dsn, long long dsh,
+                                                                long long dsw, long long xsn, long long xsh,
+                                                                long long xsw, const __nv_bfloat16* __restrict__ addend,
+                                                                long long asn, long long ash, long long asw) {
+  const int vecC = C >> 3;
+  const int n = blockIdx.y / H, ih = blockIdx.y - n * H;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < W * vecC; i += gridDim.x * blockDim.x) {
+    const int iw = i / vecC, cv = i - iw * vecC;
+    float g[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) g[j] = 0.f;
+#pragma unroll
+    for (int r = 0; r < K; ++r) {
+      const int th = ih + P - r;  // = oh * S for the window whose row r covers this pixel
+      if (th < 0 || th % S != 0 || th / S >= OH) continue;
+      const int oh = th / S;
+#pragma unroll
+      for (int q = 0; q < K; ++q) {
+        const int tw = iw + P - q;
+        if (tw < 0 || tw % S != 0 || tw / S >= OW) continue;
+        const int ow = tw / S;
+        const uint2 id = *reinterpret_cast<const uint2*>(idx + ((static_cast<long long>(n) * OH + oh) * OW + ow) * C + cv * 8);
+        const uint4 d = *reinterpret_cast<const uint4*>(dy + n * dsn + oh * dsh + ow * dsw + cv * 8);
+        const uint32_t tapv = static_cast<uint32_t>(r * K + q) * 0x01010101u;  // constant after unrolling
+        const uint32_t m0 = __vcmpeq4(id.x, tapv), m1 = __vcmpeq4(id.y, tapv);  // 0xFF per matching channel byte
+        const uint32_t w0 = d.x & __byte_perm(m0, 0, 0x1100), w1 = d.y & __byte_perm(m0, 0, 0x3322);
+        const uint32_t w2 = d.z & __byte_perm(m1, 0, 0x1100), w3 = d.w & __byte_perm(m1, 0, 0x3322);
+        g[0] += bf16lo(w0);
+        g[1] += bf16hi(w0);
+        g[2] += bf16lo(w1);
+        g[3] += bf16hi(w1);
+        g[4] += bf16lo(w2);
+        g[5] += bf16hi(w2);
+        g[6] += bf16lo(w3);
+        g[7] += bf16hi(w3);
+      }
+    }
+    if (addend != nullptr) {
+      const uint4 a = *reinterpret_cast<const uint4*>(addend + n * asn + ih * ash + iw * asw + cv * 8);
+      const uint32_t ai[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        g[2 * j] += bf16lo(ai[j]);
+        g[2 * j + 1] += bf16hi(ai[j]);
+      }
+    }
+    uint4 o;
+    o.x = pack_bf16x2(g[0], g[1]);
+    o.y = pack_bf16x2(g[2], g[3]);
+    o.z = pack_bf16x2(g[4], g[5]);
+    o.w = pack_bf16x2(g[6], g[7]);
+    *reinterpret_cast<uint4*>(dx + n * xsn + ih * xsh + iw * xsw + cv * 8) = o;
+  }
+}
+
 // [N, HW, C] -> [N, C]: block = (C/8 vector lanes) x row slabs, tree-free accumulate then smem reduce.
 __global__ void __launch_bounds__(256) avgpool_fwd_kernel(const __nv_bfloat16* __restrict__ x,
                                                           __nv_bfloat16* __restrict__ y, int HW, int C) {
@@ -196,6 +259,13 @@ extern "C" int dmpi_maxpool_backward_add(const void* dy, const void* idx, void* 
   if (C % 8) return -1;
   if (addend != nullptr && ((reinterpret_cast<uintptr_t>(addend) & 15) || asn % 8 || ash % 8 || asw % 8)) return -3;
   const dim3 grid((W * (C / 8) + 255) / 256, N * H);
+  if ((k == 3 && s == 2 && p == 1) || (k == 2 && s == 2 && p == 0)) {
+    auto kern = k == 3 ? maxpool_bwd_fixed_kernel<3, 2, 1> : maxpool_bwd_fixed_kernel<2, 2, 0>;
+    kern<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(dy), static_cast<const uint8_t*>(idx), static_cast<__nv_bfloat16*>(dx), N, H,
+        W, C, OH, OW, dsn, dsh, dsw, xsn, xsh, xsw, static_cast<const __nv_bfloat16*>(addend), asn, ash, asw);
+    return cudaGetLastError() == cudaSuccess ? 0 : -2;
+  }
   maxpool_bwd_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(dy), static_cast<const uint8_t*>(idx), static_cast<__nv_bfloat16*>(dx), N, H,
       W, C, OH, OW, k, s, p, dsn, dsh, dsw, xsn, xsh, xsw, static_cast<const __nv_bfloat16*>(addend), asn, ash, asw);

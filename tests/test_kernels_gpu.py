@@ -114,7 +114,7 @@ def test_bn_eval():
     _close(out, ref.permute(0, 2, 3, 1), 1e-2, "bn_eval")
 
 
-@pytest.mark.parametrize("k,s,p,hw", [(3, 2, 1, 16), (2, 2, 0, 16), (3, 2, 1, 15)])
+@pytest.mark.parametrize("k,s,p,hw", [(3, 2, 1, 16), (2, 2, 0, 16), (3, 2, 1, 15), (3, 1, 1, 12)])
 def test_maxpool(k, s, p, hw):
     from deeplearning_mpi_b200.ops import kernels as K
 
@@ -128,6 +128,11 @@ def test_maxpool(k, s, p, hw):
     yr.backward(dy.float().permute(0, 3, 1, 2))
     dx = K.maxpool_backward(dy, idx, tuple(x.shape), k, s, p)
     _close(dx, xr.grad.permute(0, 2, 3, 1), 1e-2, "maxpool_bwd")
+    # second gradient of the pooled tensor added in the same pass (a channel slice of a wider buffer, as in the UNet)
+    wide = torch.randn(2, hw, hw, 96, device=DEV).bfloat16()
+    add = wide[..., 32:]
+    dx2 = K.maxpool_backward(dy, idx, tuple(x.shape), k, s, p, addend=add)
+    _close(dx2, xr.grad.permute(0, 2, 3, 1) + add.float(), 1e-2, "maxpool_bwd_addend")
 
 
 def test_avgpool():
