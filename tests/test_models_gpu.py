@@ -329,3 +329,41 @@ def test_cuda_graph_training_step():
     assert ul[-1] < ul[0]
     # warm-up steps + replays advanced the device-side step count (the capture pass itself records but does not execute)
     assert float(adam.state["step_t"].item()) == 2 + 8
+
+
+@pytest.mark.parametrize("kind", ["resnet18", "resnet50", "unet"])
+def test_odd_input_shapes(kind):
+    """Non-square / odd spatial sizes: every tile planner (pixel boxes, patch tiles, parity views) has ragged edges here.
+    Eval-mode forward is compared strictly against the fp32 oracle; the training step must stay finite and agree with
+    the oracle on the loss."""
+    import deeplearning_mpi_b200.nn as dnn
+    from deeplearning_mpi_b200.models import UNet, resnet18, resnet50
+
+    torch.manual_seed(3)
+    if kind == "unet":
+        make, x = (lambda: UNet(out_classes=1)), torch.randn(3, 3, 48, 80)
+        target = (torch.rand(3, 48, 80) > 0.5).float()
+    else:
+        make = (lambda: resnet18(num_classes=10)) if kind == "resnet18" else (lambda: resnet50(num_classes=10))
+        x, target = torch.randn(5, 3, 75, 101), torch.randint(0, 10, (5,))
+    ref = make()
+    _round_weights_to_bf16(ref)
+    fast = copy.deepcopy(ref).to(DEV)
+    ref.eval()
+    fast.eval()
+    with torch.no_grad():
+        r_eval = _rel(fast(x.to(DEV)), ref(x))
+    print(f"{kind} eval rel={r_eval:.4e}")
+    assert r_eval < 3e-2
+    ref.train()
+    fast.train()
+    if kind == "unet":
+        loss_ref = F.binary_cross_entropy_with_logits(ref(x).squeeze(1), target)
+        loss = dnn.binary_cross_entropy_with_logits(fast(x.to(DEV)).squeeze(1), target.to(DEV))
+    else:
+        loss_ref = F.cross_entropy(ref(x), target)
+        loss = dnn.cross_entropy(fast(x.to(DEV)), target.to(DEV))
+    loss.backward()
+    torch.cuda.synchronize()
+    assert abs(loss.item() - loss_ref.item()) < 0.1 * abs(loss_ref.item()) + 1e-2, (loss.item(), loss_ref.item())
+    assert all(torch.isfinite(p.grad).all() for p in fast.parameters() if p.grad is not None)
