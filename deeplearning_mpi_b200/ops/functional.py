@@ -25,6 +25,35 @@ def _nb(t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
     return t if t is None else t.detach()
 
 
+# ------------------------------------------------------------------------------------------------------------------
+# Weight gradients on a side stream.  wgrad(l) only feeds the optimizer / the gradient bucket, so it does not have to
+# sit on the critical path dy(l) -> dgrad(l) -> BatchNorm backward(l-1) -> ...  It is launched on a second stream and
+# co-runs with the HBM-bound BatchNorm backward kernels of the next layer (the conv kernels are tensor / L2 bound, so
+# the two use different resources).  The parameter is reported ready (and the main stream made to wait for the side
+# stream) one layer later; the last layer of the backward pass runs in order and joins everything.
+# Measured (ResNet-50, 1 GPU, same box A/B): 12.72k / 12.89k img/s with the side stream vs 12.72k / 12.78k without —
+# the persistent conv kernels hold an SM's whole shared memory, so little actually co-runs; kept as an opt-in switch.
+_WGRAD_STREAM = os.environ.get("DMPI_WGRAD_STREAM", "0") == "1"
+_side_streams = {}
+_pending_wgrads = []  # (arena, weight, event) in launch order
+
+
+def _side_stream(device) -> "torch.cuda.Stream":
+    s = _side_streams.get(device)
+    if s is None:
+        s = torch.cuda.Stream(device=device)
+        _side_streams[device] = s
+    return s
+
+
+def _flush_pending_wgrads(keep_last: int = 0) -> None:
+    """Main stream waits for the parked weight gradients (all but the newest ``keep_last``) and reports them ready."""
+    while len(_pending_wgrads) > keep_last:
+        arena, weight, ev = _pending_wgrads.pop(0)
+        torch.cuda.current_stream().wait_event(ev)
+        arena.grad_ready(weight)
+
+
 class GradLink:
     """Side channel between the two branches of a residual fork.
 
@@ -128,13 +157,32 @@ class ConvBnAct(torch.autograd.Function):
             arena.grad_ready(bias)
         dx = None
         if ctx.is_stem:
+            _flush_pending_wgrads()
             dwin = arena.stem_dw[id(weight)]
             dwin.zero_()
             CV.smallc_wgrad(dy, x, dwin, R, stride)
             k, c = weight.shape[0], weight.shape[1]
             K.stem_unpack_grad(dwin, arena.grad_physical(weight), k, R, S, c)
         else:
-            CV.conv2d_wgrad(dy, x, arena.grad_physical(weight), R, S, stride, pad)
+            overlap = _WGRAD_STREAM and ctx.needs_input_grad[0]
+            if overlap:
+                # everything launched so far (the previous layer's wgrad included) stays ahead of this layer's dgrad
+                _flush_pending_wgrads(keep_last=0)
+                main = torch.cuda.current_stream()
+                side = _side_stream(dy.device)
+                side.wait_stream(main)
+                with torch.cuda.stream(side):
+                    CV.conv2d_wgrad(dy, x, arena.grad_physical(weight), R, S, stride, pad)
+                    ev = side.record_event()
+                dy.record_stream(side)
+                x.record_stream(side)
+                if not _pending_wgrads:
+                    # safety net for graphs whose first layer also needs an input gradient (nothing "last" to join at)
+                    torch.autograd.Variable._execution_engine.queue_callback(_flush_pending_wgrads)
+                _pending_wgrads.append((arena, weight, ev))
+            else:
+                _flush_pending_wgrads()  # last layer of the backward pass: join the side stream, then run in order
+                CV.conv2d_wgrad(dy, x, arena.grad_physical(weight), R, S, stride, pad)
             if ctx.needs_input_grad[0]:
                 parked = ctx.link.take() if ctx.link_role == "take" else None
                 if ctx.link_role == "give_dx" and stride == 2:
@@ -149,7 +197,8 @@ class ConvBnAct(torch.autograd.Function):
                     dx = parked(dx)
                 else:
                     dx = CV.conv2d_dgrad(dy, arena.w_transposed(weight), R, S, stride, pad, ctx.in_hw, addend=parked)
-        arena.grad_ready(weight)
+        if not (_WGRAD_STREAM and ctx.needs_input_grad[0] and not ctx.is_stem):
+            arena.grad_ready(weight)
         if ctx.link_role == "give_dx" and dx is not None:
             ctx.link.give(dx)
             dx = None

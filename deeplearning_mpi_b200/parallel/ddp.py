@@ -163,6 +163,10 @@ class DistributedDataParallel(nn.Module):
     # ------------------------------------------------------------------ per-iteration machinery
     def _autograd_hook(self, idx: int) -> None:
         slot = self.arena.slots[idx]
+        if getattr(slot, "fused", False):
+            # written by a fused backward kernel (possibly still running on the weight-gradient side stream): only
+            # arena.grad_ready(), called once that kernel is ordered before the compute stream, may publish it
+            return
         g = slot.param.grad
         base = self.arena.flat_g.data_ptr() + slot.offset * 4
         if g is not None and g.data_ptr() != base:

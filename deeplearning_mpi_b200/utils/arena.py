@@ -73,6 +73,7 @@ class ParamSlot:
     t_offset: int = -1   # element offset of the transposed bf16 shadow
     t_shape: Tuple[int, int] = (0, 0)
     ready_cb: Optional[Callable[[], None]] = None
+    fused: bool = False  # gradient written by a fused kernel and published through grad_ready() only
 
 
 def _physical(p: torch.Tensor, kind: str) -> torch.Tensor:
@@ -319,6 +320,7 @@ class ParamArena:
         """fp32 gradient slot in physical element order (what the wgrad kernels accumulate into)."""
         s = self.by_param[id(p)]
         self._ensure_grad(s)
+        s.fused = True  # this parameter's gradient is published by grad_ready(), never by an autograd hook
         v = self.flat_g[s.offset: s.offset + s.numel]
         if s.kind in ("conv", "stem"):
             k, c, r, q = s.shape
