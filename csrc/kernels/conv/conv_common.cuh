@@ -41,6 +41,11 @@ struct alignas(64) ConvKernelParams {
   // igemm patch mode (see dmpi_conv_desc.patch): patch width in pixels, bytes per patch TMA box, shared-memory stride of
   // one patch stage, ring depths, and whether the whole filter stays resident in the B ring
   int patch, halo, pw, pa_bytes, pa_stride, pa_stages, pb_stages, b_resident;
+  // igemm: deterministic BatchNorm statistics.  Every CTA stores its per-column partial sums in stat_scratch
+  // (a 64-float header holding the uint32 ticket, then [gridDim.x][2][BN] floats) and the last CTA to finish adds them up in CTA order, so the
+  // result does not depend on the order in which CTAs retire (fp32 atomics made whole-network gradients differ by
+  // ~20 % run to run through ReLU gate flips).  Null: atomics.
+  float* stat_scratch;
   int dbg;  // DMPI_IGEMM_DBG experiment bits (bench only): 1 no TMA store, 2 no statistics, 4 no loads, 8 no MMAs
 };
 
@@ -53,6 +58,8 @@ struct dmpi_conv_plan {
   const void* cached_b;
   const void* cached_o;
   const void* cached_add;
+  void* stat_scratch;
+  long long stat_scratch_bytes;
   bool maps_valid;
   int num_sms;
 };

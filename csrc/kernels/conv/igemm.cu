@@ -43,6 +43,7 @@ constexpr int kStatWarps = 4;
 constexpr int kTileM = 128;
 constexpr int kBlockK = 64;  // bf16 elements = one 128-byte swizzle row
 constexpr int kABytes = kTileM * kBlockK * 2;
+constexpr int kStatHdr = 64;  // floats reserved at the head of the statistics scratch (ticket counter)
 
 // CG = 1: one CTA per tile.  CG = 2: a CTA pair (cluster of two SMs of one TPC) works on a 256-row tile with
 // tcgen05.mma.cta_group::2 — each CTA loads its own 128 A rows and only HALF of the B tile (the tensor cores of both
@@ -141,6 +142,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
   uint64_t* pb_full = pa_empty + kMaxPA;
   uint64_t* pb_empty = pb_full + kMaxPB;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pb_empty + kMaxPB);
+  uint32_t* last_flag = reinterpret_cast<uint32_t*>(smem_o + Cfg::kOutBufs * Cfg::kOutBytes + 512 + 124);  // see end
   static_assert((2 * S + 10 + 2 * kMaxPA + 2 * kMaxPB) * 8 + 8 <= 512, "barrier region too small");
 
   const int warp = threadIdx.x >> 5;
@@ -148,6 +150,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
   const int rank = CG == 2 ? static_cast<int>(cluster_ctarank()) : 0;  // rank 0 of a pair is the MMA leader
 
   if (warp == 0 && lane == 0) {
+    *last_flag = 0u;
     for (int i = 0; i < DMPI_MAX_MAPS; ++i) tma_prefetch_desc(&p.a_map[i]);
     tma_prefetch_desc(&p.b_map);
     tma_prefetch_desc(&p.o_map[0]);
@@ -684,9 +687,21 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
             t2 += red[((1 * kSubs + s) * kSlabs + sl) * SN + cc];
           }
           const int gcol = st_nblk * BN + c;
-          if (gcol < p.n_out) {
+          if (p.stat_scratch != nullptr) {
+            // deterministic path: park the partial sums; the last CTA adds all of them up in CTA order (below)
+            p.stat_scratch[kStatHdr + (blockIdx.x * 2 + 0) * BN + c] = t1;
+            p.stat_scratch[kStatHdr + (blockIdx.x * 2 + 1) * BN + c] = t2;
+          } else if (gcol < p.n_out) {
             atomicAdd(p.stat_sum + (gcol % p.stat_mod), t1);
             atomicAdd(p.stat_sq + (gcol % p.stat_mod), t2);
+          }
+        }
+        if (p.stat_scratch != nullptr) {
+          __threadfence();
+          named_bar_sync(2, kStatThreads);
+          if (st == 0) {
+            uint32_t* ticket = reinterpret_cast<uint32_t*>(p.stat_scratch);  // fixed place: launches of every shape share it
+            *last_flag = (atomicAdd(ticket, 1u) == gridDim.x - 1) ? 1u : 0u;
           }
         }
       }
@@ -701,6 +716,47 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
   } else {
     __syncthreads();
     if (warp == 2) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+  }
+
+  // Deterministic BatchNorm statistics: the CTA that drew the last ticket adds the partial sums of all CTAs in CTA
+  // order.  8 lanes share a channel (each takes every 8th CTA of that channel's list, ascending) and combine with a
+  // fixed shuffle tree, so the summation order is a function of the launch geometry only.
+  if (p.stat_scratch != nullptr && *last_flag != 0u) {
+    __threadfence();
+    const int grid = static_cast<int>(gridDim.x);
+    const int nnt = p.num_n_tiles;
+    const int l = threadIdx.x & 7;
+    for (int ch0 = 0; ch0 < p.stat_mod; ch0 += kThreads / 8) {
+      const int ch = ch0 + (threadIdx.x >> 3);
+      float t1 = 0.f, t2 = 0.f;
+      if (ch < p.stat_mod) {
+        for (int gcol = ch; gcol < p.n_out; gcol += p.stat_mod) {  // column groups that share the channel (convT)
+          const int n_blk = gcol / BN, cc = gcol - n_blk * BN;
+          // CTAs that worked on this N tile: blockIdx = CG * (n_blk + j * nnt) + r
+          int idx = 0;
+          for (int u = n_blk; u * CG < grid; u += nnt) {
+#pragma unroll
+            for (int r = 0; r < CG; ++r, ++idx) {
+              const int b = u * CG + r;
+              if ((idx & 7) == l && b < grid) {
+                t1 += __ldcg(p.stat_scratch + kStatHdr + (b * 2 + 0) * BN + cc);
+                t2 += __ldcg(p.stat_scratch + kStatHdr + (b * 2 + 1) * BN + cc);
+              }
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int o = 1; o < 8; o <<= 1) {
+        t1 += __shfl_xor_sync(0xffffffffu, t1, o);
+        t2 += __shfl_xor_sync(0xffffffffu, t2, o);
+      }
+      if (l == 0 && ch < p.stat_mod) {
+        p.stat_sum[ch] += t1;
+        p.stat_sq[ch] += t2;
+      }
+    }
+    if (threadIdx.x == 0) *reinterpret_cast<uint32_t*>(p.stat_scratch) = 0u;  // ready for the next launch
   }
 }
 
@@ -727,7 +783,7 @@ static int encode_view(CUtensorMap* map, const void* base, const dmpi_tensor4& v
 }
 
 template <int BN, int CG>
-static int launch_igemm(const ConvKernelParams& kp, int num_sms, cudaStream_t stream) {
+static int launch_igemm(const ConvKernelParams& kp, int num_sms, cudaStream_t stream, long long scratch_bytes) {
   using Cfg = IgemmCfg<BN, CG>;
   static bool attr_set = false;
   static int max_clusters = 0;
@@ -769,7 +825,17 @@ static int launch_igemm(const ConvKernelParams& kp, int num_sms, cudaStream_t st
   // A grid that is a multiple of the N-tile count keeps n_blk fixed per CTA, so the BatchNorm partial sums stay
   // in registers for the whole kernel (one flush per CTA).
   if (grid == slots && kp.num_n_tiles > 1 && kp.num_n_tiles <= slots) grid = (slots / kp.num_n_tiles) * kp.num_n_tiles;
+  // deterministic statistics need every CTA to stay on one N tile and the scratch to hold one partial per CTA
+  const bool one_n_tile_per_cta = grid == units || grid % kp.num_n_tiles == 0;
   grid *= CG;
+  ConvKernelParams kp2;
+  const ConvKernelParams* kpp = &kp;
+  if (kp.stat_scratch != nullptr &&
+      (!one_n_tile_per_cta || scratch_bytes < (static_cast<long long>(grid) * 2 * BN + kStatHdr) * 4 || kp.stat_mod <= 0)) {
+    kp2 = kp;
+    kp2.stat_scratch = nullptr;  // fall back to atomics for this launch
+    kpp = &kp2;
+  }
   if (getenv("DMPI_TRACE")) fprintf(stderr, "[dmpi] launch grid=%d smem=%d params=%zu bytes\n", grid, Cfg::kSmemBytes, sizeof(kp));
   cudaError_t e;
   if (CG == 2) {
@@ -785,9 +851,9 @@ static int launch_igemm(const ConvKernelParams& kp, int num_sms, cudaStream_t st
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    e = cudaLaunchKernelEx(&cfg, igemm_kernel<BN, CG>, kp);
+    e = cudaLaunchKernelEx(&cfg, igemm_kernel<BN, CG>, *kpp);
   } else {
-    igemm_kernel<BN, CG><<<grid, kThreads, Cfg::kSmemBytes, stream>>>(kp);
+    igemm_kernel<BN, CG><<<grid, kThreads, Cfg::kSmemBytes, stream>>>(*kpp);
     e = cudaGetLastError();
   }
   if (getenv("DMPI_TRACE")) {
@@ -812,6 +878,8 @@ extern "C" dmpi_conv_plan* dmpi_conv_plan_create(const dmpi_conv_desc* desc) {
   memset(&plan->params, 0, sizeof(plan->params));
   plan->desc = *desc;
   plan->cached_a = plan->cached_b = plan->cached_o = plan->cached_add = nullptr;
+  plan->stat_scratch = nullptr;
+  plan->stat_scratch_bytes = 0;
   plan->maps_valid = false;
   plan->num_sms = 0;
   ConvKernelParams& kp = plan->params;
@@ -855,6 +923,13 @@ extern "C" dmpi_conv_plan* dmpi_conv_plan_create(const dmpi_conv_desc* desc) {
 }
 
 extern "C" void dmpi_conv_plan_destroy(dmpi_conv_plan* plan) { delete plan; }
+
+// Scratch for deterministic BatchNorm statistics (see ConvKernelParams::stat_scratch): zero-initialised device memory
+// of at least (CTAs * 2 * bn + 1) * 4 bytes that no other stream uses concurrently; null disables (atomics).
+extern "C" void dmpi_conv_plan_set_stat_scratch(dmpi_conv_plan* plan, void* scratch, long long bytes) {
+  plan->stat_scratch = scratch;
+  plan->stat_scratch_bytes = scratch ? bytes : 0;
+}
 
 extern "C" int dmpi_conv_last_error(char* buf, int buflen) {
   snprintf(buf, buflen, "%s", g_err);
@@ -975,6 +1050,7 @@ extern "C" int dmpi_igemm_run_add(dmpi_conv_plan* plan, const void* a, const voi
     }
     kp.has_add = 1;
   }
+  kp.stat_scratch = (d.stat_mod > 0 && stat_sum != nullptr) ? static_cast<float*>(plan->stat_scratch) : nullptr;
   kp.bias = bias;
   kp.stat_sum = stat_sum;
   kp.stat_sq = stat_sqsum;
@@ -992,14 +1068,14 @@ extern "C" int dmpi_igemm_run_add(dmpi_conv_plan* plan, const void* a, const voi
   if (trace) fprintf(stderr, "[dmpi] sms=%d launching\n", plan->num_sms);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (d.cta_group == 2) {
-    if (d.bn == 128) return launch_igemm<128, 2>(kp, plan->num_sms, s);
-    if (d.bn == 256) return launch_igemm<256, 2>(kp, plan->num_sms, s);
+    if (d.bn == 128) return launch_igemm<128, 2>(kp, plan->num_sms, s, plan->stat_scratch_bytes);
+    if (d.bn == 256) return launch_igemm<256, 2>(kp, plan->num_sms, s, plan->stat_scratch_bytes);
     set_err("igemm: CTA pairs need bn 128 or 256");
     return -2;
   }
   switch (d.bn) {
-    case 64: return launch_igemm<64, 1>(kp, plan->num_sms, s);
-    case 128: return launch_igemm<128, 1>(kp, plan->num_sms, s);
-    default: return launch_igemm<256, 1>(kp, plan->num_sms, s);
+    case 64: return launch_igemm<64, 1>(kp, plan->num_sms, s, plan->stat_scratch_bytes);
+    case 128: return launch_igemm<128, 1>(kp, plan->num_sms, s, plan->stat_scratch_bytes);
+    default: return launch_igemm<256, 1>(kp, plan->num_sms, s, plan->stat_scratch_bytes);
   }
 }

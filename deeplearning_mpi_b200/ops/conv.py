@@ -125,9 +125,31 @@ def _get_plan(key, build):
     return ent[0]
 
 
+_DETERMINISTIC = os.environ.get("DMPI_DETERMINISTIC", "1") == "1"
+_STAT_SCRATCH_BYTES = 512 << 10  # >= (148 CTAs * 2 * 256 columns + 1) * 4
+_stat_scratch = {}
+
+
+def _stat_scratch_for_current_stream(device) -> torch.Tensor:
+    """Zero-initialised scratch for the deterministic BatchNorm statistics, one per (device, stream): launches on one
+    stream are ordered, so they can share it (the kernel leaves its ticket counter at zero)."""
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    t = _stat_scratch.get(key)
+    if t is None:
+        t = torch.zeros(_STAT_SCRATCH_BYTES // 4, dtype=torch.float32, device=device)
+        _stat_scratch[key] = t
+    return t
+
+
 def _run_igemm(plan, a, b, out, bias, stats, addend=None, add_strides=(0, 0, 0)):
     s0 = stats[0].data_ptr() if stats is not None else None
     s1 = stats[1].data_ptr() if stats is not None else None
+    if stats is not None:
+        if _DETERMINISTIC:
+            scratch = _stat_scratch_for_current_stream(a.device)
+            N.cuda().dmpi_conv_plan_set_stat_scratch(plan, scratch.data_ptr(), _STAT_SCRATCH_BYTES)
+        else:
+            N.cuda().dmpi_conv_plan_set_stat_scratch(plan, None, 0)
     if addend is None:
         rc = N.cuda().dmpi_igemm_run(plan, a.data_ptr(), b.data_ptr(), out.data_ptr(),
                                      bias.data_ptr() if bias is not None else None, s0, s1, N.stream_ptr())

@@ -78,6 +78,11 @@ typedef struct dmpi_conv_plan dmpi_conv_plan;
 dmpi_conv_plan* dmpi_conv_plan_create(const dmpi_conv_desc* desc);
 void dmpi_conv_plan_destroy(dmpi_conv_plan* plan);
 
+/* Deterministic BatchNorm statistics for dmpi_igemm_run*: zero-initialised device scratch of at least
+ * (CTAs * 2 * bn + 64) * 4 bytes (512 KiB covers every configuration on 148 SMs) that no concurrently running launch
+ * shares.  With it the per-channel sums are added in a fixed order (bit-reproducible); without it fp32 atomics. */
+void dmpi_conv_plan_set_stat_scratch(dmpi_conv_plan* plan, void* scratch, long long bytes);
+
 /* D = A (*) B with fused bias / ReLU / BatchNorm statistics.  Returns 0 or a negative error. */
 int dmpi_igemm_run(dmpi_conv_plan* plan, const void* a, const void* b, void* out, const float* bias,
                    float* stat_sum, float* stat_sqsum, void* stream);

@@ -294,3 +294,29 @@ def test_umma_row_shifted_descriptors():
             torch.cuda.synchronize()
             ref = (y.float().t() @ x[shift:shift + 64].float()) if mode else (x[shift:shift + 128].float() @ w.float().t())
             _close(out, ref, 1e-2, f"umma_shift mode={mode} shift={shift}")
+
+
+def test_fprop_statistics_are_bit_reproducible():
+    """The per-channel sums of the conv epilogue are added in a fixed order (last-CTA reduction of per-CTA partials):
+    repeated launches must agree bit for bit, for one and several N tiles, CTA pairs, patch mode and the 4-view
+    transposed convolution (several column groups per channel)."""
+    from deeplearning_mpi_b200.ops import conv as C
+
+    _torch_setup()
+    for (n, h, c, k, R, pad) in [(64, 56, 64, 64, 1, 0), (32, 28, 128, 512, 1, 0), (16, 28, 256, 256, 3, 1),
+                                 (16, 56, 64, 64, 3, 1), (8, 14, 512, 1024, 1, 0)]:
+        x = _rand(n, h, h, c)
+        wt = _rand(k, c, R, R, scale=(c * R * R) ** -0.5)
+        w2d = _w2d(wt)
+        runs = []
+        for _ in range(3):
+            ssum = torch.zeros(k, device=_dev())
+            ssq = torch.zeros(k, device=_dev())
+            y = C.conv2d_fprop(x, w2d, R, R, 1, pad, stats=(ssum, ssq))
+            torch.cuda.synchronize()
+            runs.append((ssum.clone(), ssq.clone()))
+        yf = y.float()
+        _close(runs[0][0], yf.sum(dim=(0, 1, 2)), 2e-3, f"det_stats_sum{(n, h, c, k, R)}")
+        _close(runs[0][1], (yf * yf).sum(dim=(0, 1, 2)), 2e-3, f"det_stats_sq{(n, h, c, k, R)}")
+        for r in runs[1:]:
+            assert torch.equal(r[0], runs[0][0]) and torch.equal(r[1], runs[0][1]), f"not reproducible: {(n, h, c, k, R)}"
