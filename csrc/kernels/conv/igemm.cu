@@ -43,6 +43,7 @@ constexpr int kStatWarps = 4;
 constexpr int kTileM = 128;
 constexpr int kBlockK = 64;  // bf16 elements = one 128-byte swizzle row
 constexpr int kABytes = kTileM * kBlockK * 2;
+constexpr int kDetInFlight = 6;  // partial-sum rows a thread of the last-CTA reduction keeps in flight
 constexpr int kStatHdr = 64;  // floats reserved at the head of the statistics scratch (ticket counter)
 
 // CG = 1: one CTA per tile.  CG = 2: a CTA pair (cluster of two SMs of one TPC) works on a 256-row tile with
@@ -725,35 +726,63 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
     __threadfence();
     const int grid = static_cast<int>(gridDim.x);
     const int nnt = p.num_n_tiles;
-    const int l = threadIdx.x & 7;
-    for (int ch0 = 0; ch0 < p.stat_mod; ch0 += kThreads / 8) {
-      const int ch = ch0 + (threadIdx.x >> 3);
-      float t1 = 0.f, t2 = 0.f;
-      if (ch < p.stat_mod) {
-        for (int gcol = ch; gcol < p.n_out; gcol += p.stat_mod) {  // column groups that share the channel (convT)
+    // L lanes share a quad of 4 channels (16-byte loads); each lane takes every L-th CTA of the tile's list, ascending
+    const int cpt = ((grid / CG + nnt - 1) / nnt) * CG;  // CTAs per N tile (upper bound)
+    // L lanes per quad: as many as keep the whole channel range in ONE pass (each pass is a chain of L2 round trips)
+    const int nq_all = p.stat_mod >> 2;
+    int L = 8;
+    while (L > 1 && (kThreads / L < nq_all || L > cpt)) L >>= 1;
+    const int l = threadIdx.x & (L - 1);
+    const int quads_per_pass = kThreads / L;
+    const int nquads = p.stat_mod >> 2;
+    for (int q0 = 0; q0 < nquads; q0 += quads_per_pass) {
+      const int quad = q0 + threadIdx.x / L;
+      float4 t1 = make_float4(0.f, 0.f, 0.f, 0.f), t2 = t1;
+      if (quad < nquads) {
+        for (int gcol = quad * 4; gcol < p.n_out; gcol += p.stat_mod) {  // column groups that share the channels (convT)
           const int n_blk = gcol / BN, cc = gcol - n_blk * BN;
-          // CTAs that worked on this N tile: blockIdx = CG * (n_blk + j * nnt) + r
-          int idx = 0;
-          for (int u = n_blk; u * CG < grid; u += nnt) {
+          const float* base = p.stat_scratch + kStatHdr + cc;
+          // list entry idx of this tile: CTA blockIdx = CG * (n_blk + (idx / CG) * nnt) + idx % CG
+          int idx = l;
+          while (true) {
+            float4 a1[kDetInFlight], a2[kDetInFlight];
+            int nv = 0;
 #pragma unroll
-            for (int r = 0; r < CG; ++r, ++idx) {
-              const int b = u * CG + r;
-              if ((idx & 7) == l && b < grid) {
-                t1 += __ldcg(p.stat_scratch + kStatHdr + (b * 2 + 0) * BN + cc);
-                t2 += __ldcg(p.stat_scratch + kStatHdr + (b * 2 + 1) * BN + cc);
+            for (int k = 0; k < kDetInFlight; ++k) {  // independent CTAs in flight, added in list order below
+              const int id = idx + k * L;
+              const int b = CG * (n_blk + (id / CG) * nnt) + (id % CG);
+              if (b < grid) {
+                a1[k] = __ldcg(reinterpret_cast<const float4*>(base + static_cast<size_t>(b * 2 + 0) * BN));
+                a2[k] = __ldcg(reinterpret_cast<const float4*>(base + static_cast<size_t>(b * 2 + 1) * BN));
+                nv = k + 1;
               }
             }
+#pragma unroll
+            for (int k = 0; k < kDetInFlight; ++k) {
+              if (k < nv) {
+                t1.x += a1[k].x; t1.y += a1[k].y; t1.z += a1[k].z; t1.w += a1[k].w;
+                t2.x += a2[k].x; t2.y += a2[k].y; t2.z += a2[k].z; t2.w += a2[k].w;
+              }
+            }
+            if (nv < kDetInFlight) break;
+            idx += kDetInFlight * L;
           }
         }
       }
-#pragma unroll
-      for (int o = 1; o < 8; o <<= 1) {
-        t1 += __shfl_xor_sync(0xffffffffu, t1, o);
-        t2 += __shfl_xor_sync(0xffffffffu, t2, o);
+      for (int o = 1; o < L; o <<= 1) {
+        t1.x += __shfl_xor_sync(0xffffffffu, t1.x, o); t1.y += __shfl_xor_sync(0xffffffffu, t1.y, o);
+        t1.z += __shfl_xor_sync(0xffffffffu, t1.z, o); t1.w += __shfl_xor_sync(0xffffffffu, t1.w, o);
+        t2.x += __shfl_xor_sync(0xffffffffu, t2.x, o); t2.y += __shfl_xor_sync(0xffffffffu, t2.y, o);
+        t2.z += __shfl_xor_sync(0xffffffffu, t2.z, o); t2.w += __shfl_xor_sync(0xffffffffu, t2.w, o);
       }
-      if (l == 0 && ch < p.stat_mod) {
-        p.stat_sum[ch] += t1;
-        p.stat_sq[ch] += t2;
+      if (l == 0 && quad < nquads) {
+        float4* s1 = reinterpret_cast<float4*>(p.stat_sum + quad * 4);
+        float4* s2 = reinterpret_cast<float4*>(p.stat_sq + quad * 4);
+        float4 v1 = *s1, v2 = *s2;
+        v1.x += t1.x; v1.y += t1.y; v1.z += t1.z; v1.w += t1.w;
+        v2.x += t2.x; v2.y += t2.y; v2.z += t2.z; v2.w += t2.w;
+        *s1 = v1;
+        *s2 = v2;
       }
     }
     if (threadIdx.x == 0) *reinterpret_cast<uint32_t*>(p.stat_scratch) = 0u;  // ready for the next launch

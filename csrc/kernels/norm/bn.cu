@@ -16,6 +16,7 @@
 namespace dmpi {
 
 constexpr int kBnThreads = 256;
+constexpr int kDetHdr = 64;  // floats at the head of the deterministic-reduction scratch (ticket counters)
 constexpr int kMaxC = 2048;
 
 struct BnFwdArgs {
@@ -158,12 +159,16 @@ struct BnBwdArgs {
 
 // Pass 1: per-channel reductions.  Thread (tx, ty): tx owns 8 consecutive channels, ty strides rows.
 // kFromY selects the ReLU-mask source at compile time (the two variants need different per-channel registers).
-template <bool kFromY>
-__global__ void __launch_bounds__(kBnThreads, 4) bn_bwd_reduce_kernel(const BnBwdArgs a) {
+// kDet selects the deterministic variant: grid = (C/64 channel slabs, row blocks), a block covers 64 channels x 32 rows
+// per step, every block parks its 128 partial sums in `partials` and the last block of a slab (ticket counter) adds
+// the slab's partials in row-block order — no floating-point atomics, so the result is bit-reproducible.
+template <bool kFromY, bool kDet>
+__global__ void __launch_bounds__(kBnThreads, 4) bn_bwd_reduce_kernel(const BnBwdArgs a, float* partials) {
   const int vecC = a.C >> 3;
-  const int tx = threadIdx.x % vecC;  // host guarantees vecC divides or is <= blockDim
-  const int ty = threadIdx.x / vecC;
-  const int rows_per_block = blockDim.x / vecC;
+  // tx: global 8-channel group of this thread; ty: its row inside the block's row step
+  const int tx = kDet ? static_cast<int>(blockIdx.x) * 8 + (threadIdx.x & 7) : threadIdx.x % vecC;
+  const int ty = kDet ? (threadIdx.x >> 3) : threadIdx.x / vecC;
+  const int rows_per_block = kDet ? 32 : blockDim.x / vecC;
   const int c0 = tx << 3;
   // s2 accumulates dz * (y - mean); the common factor invstd is applied once per block after the reduction.
   float s1[8], s2[8], mean[8], sc[8], sh[8];
@@ -181,8 +186,9 @@ __global__ void __launch_bounds__(kBnThreads, 4) bn_bwd_reduce_kernel(const BnBw
     }
   }
   if (ty < rows_per_block) {
-    const long long stride = static_cast<long long>(gridDim.x) * rows_per_block;
-    for (long long row = blockIdx.x * static_cast<long long>(rows_per_block) + ty; row < a.M; row += 2 * stride) {
+    const long long stride = static_cast<long long>(kDet ? gridDim.y : gridDim.x) * rows_per_block;
+    for (long long row = (kDet ? blockIdx.y : blockIdx.x) * static_cast<long long>(rows_per_block) + ty; row < a.M;
+         row += 2 * stride) {
       const long long row2 = row + stride;
       const bool has2 = row2 < a.M;
       uint4 g[2], yv[2], av[2];
@@ -233,6 +239,42 @@ __global__ void __launch_bounds__(kBnThreads, 4) bn_bwd_reduce_kernel(const BnBw
     r2[threadIdx.x * 8 + j] = s2[j];
   }
   __syncthreads();
+  if (kDet) {
+    // thread q < 128: quantity q / 64 (sum dz | sum dz*(y-mean)) of slab channel q % 64, rows added in ty order
+    __shared__ uint32_t is_last;
+    const int slab = blockIdx.x, RB = gridDim.y;
+    uint32_t* tickets = reinterpret_cast<uint32_t*>(partials);          // [kDetHdr] header: one ticket per slab
+    float* part = partials + kDetHdr + static_cast<size_t>(slab) * RB * 128;
+    if (threadIdx.x < 128) {
+      const float* src = threadIdx.x < 64 ? r1 : r2;
+      const int ch = threadIdx.x & 63;
+      float t = 0.f;
+#pragma unroll 8
+      for (int r = 0; r < 32; ++r) t += src[(r * 8 + (ch >> 3)) * 8 + (ch & 7)];
+      part[blockIdx.y * 128 + threadIdx.x] = t;
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) is_last = (atomicAdd(&tickets[slab], 1u) == static_cast<uint32_t>(RB - 1)) ? 1u : 0u;
+    __syncthreads();
+    if (is_last) {
+      __threadfence();
+      // 256 threads: quantity q = t % 128, the even / odd row blocks go to the two halves, each in ascending order
+      const int q = threadIdx.x & 127, half = threadIdx.x >> 7;
+      float t = 0.f;
+      for (int rb = half; rb < RB; rb += 2) t += __ldcg(part + rb * 128 + q);
+      r1[threadIdx.x] = t;
+      __syncthreads();
+      if (threadIdx.x < 128) {
+        const float total = r1[threadIdx.x] + r1[threadIdx.x + 128];
+        const int c = slab * 64 + (threadIdx.x & 63);
+        if (threadIdx.x < 64) a.acc[c] = total;
+        else a.acc[a.C + c] = total * a.invstd[c];
+      }
+      if (threadIdx.x == 0) tickets[slab] = 0u;  // ready for the next launch
+    }
+    return;
+  }
   // thread t < C handles channel t (loop if C > blockDim)
   for (int c = threadIdx.x; c < a.C; c += blockDim.x) {
     const int ctx = c >> 3, cj = c & 7;
@@ -475,12 +517,30 @@ extern "C" int dmpi_bn_backward_ex(const void* dout, const void* y, const void* 
                                beta, relu_from_y, nullptr, acc, dgamma, dbeta, stream);
 }
 
+extern "C" int dmpi_bn_backward_det(const void* dout, const void* y, const void* act, void* dy, void* dres, long long M,
+                                    int C, long long ld_dout, long long ldy, long long ld_act, long long ld_dy,
+                                    long long ld_dres, const float* mean, const float* invstd, const float* gamma,
+                                    const float* beta, int relu_from_y, const void* relu_mask, float* acc,
+                                    float* dgamma, float* dbeta, void* det_scratch, long long det_bytes, void* stream);
+
 // `relu_mask` (optional): the bit mask dmpi_bn_forward_mask wrote; used as the ReLU gate instead of `act`.
 extern "C" int dmpi_bn_backward_mask(const void* dout, const void* y, const void* act, void* dy, void* dres, long long M,
                                      int C, long long ld_dout, long long ldy, long long ld_act, long long ld_dy,
                                      long long ld_dres, const float* mean, const float* invstd, const float* gamma,
                                      const float* beta, int relu_from_y, const void* relu_mask, float* acc,
                                      float* dgamma, float* dbeta, void* stream) {
+  return dmpi_bn_backward_det(dout, y, act, dy, dres, M, C, ld_dout, ldy, ld_act, ld_dy, ld_dres, mean, invstd, gamma,
+                              beta, relu_from_y, relu_mask, acc, dgamma, dbeta, nullptr, 0, stream);
+}
+
+// `det_scratch` (optional, zero-initialised, not shared with a concurrently running launch; 1 MiB covers every shape):
+// with it the channel reductions are added in a fixed order (bit-reproducible) and `acc` need not be zeroed; without it
+// they use fp32 atomics onto the zeroed `acc`.
+extern "C" int dmpi_bn_backward_det(const void* dout, const void* y, const void* act, void* dy, void* dres, long long M,
+                                    int C, long long ld_dout, long long ldy, long long ld_act, long long ld_dy,
+                                    long long ld_dres, const float* mean, const float* invstd, const float* gamma,
+                                    const float* beta, int relu_from_y, const void* relu_mask, float* acc,
+                                    float* dgamma, float* dbeta, void* det_scratch, long long det_bytes, void* stream) {
   if (C % 8 != 0) return -1;
   const int vecC = C / 8;
   BnBwdArgs a;
@@ -515,8 +575,29 @@ extern "C" int dmpi_bn_backward_mask(const void* dout, const void* y, const void
   long long blocks = (M + rows_per_block * 8 - 1) / (rows_per_block * 8);
   if (blocks > 148 * 8) blocks = 148 * 8;
   if (blocks < 1) blocks = 1;
-  if (a.relu_from_y) bn_bwd_reduce_kernel<true><<<static_cast<int>(blocks), threads, threads * 16 * sizeof(float), s>>>(a);
-  else bn_bwd_reduce_kernel<false><<<static_cast<int>(blocks), threads, threads * 16 * sizeof(float), s>>>(a);
+  bool det = false;
+  if (det_scratch != nullptr && C % 64 == 0) {
+    const int slabs = C / 64;
+    long long rb = (M + 32 * 8 - 1) / (32 * 8);  // >= 8 rows per thread
+    long long cap = (148LL * 8) / slabs;
+    if (cap > 296) cap = 296;  // bounds the fixed-order tail of the last block (296 x 128 floats per slab)
+    if (cap < 1) cap = 1;
+    if (rb > cap) rb = cap;
+    if (rb < 1) rb = 1;
+    if ((kDetHdr + static_cast<long long>(slabs) * rb * 128) * 4 <= det_bytes && slabs <= kDetHdr) {
+      det = true;
+      const dim3 grid(slabs, static_cast<unsigned>(rb));
+      float* part = static_cast<float*>(det_scratch);
+      if (a.relu_from_y) bn_bwd_reduce_kernel<true, true><<<grid, kBnThreads, kBnThreads * 16 * sizeof(float), s>>>(a, part);
+      else bn_bwd_reduce_kernel<false, true><<<grid, kBnThreads, kBnThreads * 16 * sizeof(float), s>>>(a, part);
+    }
+  }
+  if (!det) {
+    if (a.relu_from_y)
+      bn_bwd_reduce_kernel<true, false><<<static_cast<int>(blocks), threads, threads * 16 * sizeof(float), s>>>(a, nullptr);
+    else
+      bn_bwd_reduce_kernel<false, false><<<static_cast<int>(blocks), threads, threads * 16 * sizeof(float), s>>>(a, nullptr);
+  }
   bn_bwd_apply_kernel<<<stream_grid(M, rows_per_block), threads, 0, s>>>(a);
   return cudaGetLastError() == cudaSuccess ? 0 : -2;
 }

@@ -150,6 +150,7 @@ def _bind_cuda(lib) -> None:
     _sig(lib, "dmpi_bn_backward_ex", I, [VP, VP, VP, VP, VP, I64, I, I64, I64, I64, I64, I64, VP, VP, VP, VP, I, VP, VP, VP, VP])
     _sig(lib, "dmpi_bn_forward_mask", I, [VP, VP, VP, I64, I, I64, I64, I64, VP, VP, VP, VP, VP, VP, VP, VP, VP, F, F, I, I, VP, VP])
     _sig(lib, "dmpi_bn_backward_mask", I, [VP, VP, VP, VP, VP, I64, I, I64, I64, I64, I64, I64, VP, VP, VP, VP, I, VP, VP, VP, VP, VP])
+    _sig(lib, "dmpi_bn_backward_det", I, [VP, VP, VP, VP, VP, I64, I, I64, I64, I64, I64, I64, VP, VP, VP, VP, I, VP, VP, VP, VP, VP, I64, VP])
     _sig(lib, "dmpi_bn_stats", I, [VP, I64, I, I64, VP, VP, VP])
     # pool
     _sig(lib, "dmpi_maxpool_forward", I, [VP, VP, VP, I, I, I, I, I, I, I, I, I, I64, I64, I64, I64, I64, I64, VP])

@@ -125,7 +125,7 @@ def _get_plan(key, build):
     return ent[0]
 
 
-_DETERMINISTIC = os.environ.get("DMPI_DETERMINISTIC", "1") == "1"
+_DETERMINISTIC = os.environ.get("DMPI_DETERMINISTIC_CONV", os.environ.get("DMPI_DETERMINISTIC", "1")) == "1"
 _STAT_SCRATCH_BYTES = 512 << 10  # >= (148 CTAs * 2 * 256 columns + 1) * 4
 _stat_scratch = {}
 

@@ -4,6 +4,8 @@ from __future__ import annotations
 
 from typing import Optional, Tuple
 
+import os
+
 import torch
 
 from .. import _native as N
@@ -33,6 +35,21 @@ def _rows_ld(x: torch.Tensor) -> Tuple[int, int]:
 
 
 # ------------------------------------------------------------------------------------------ BatchNorm
+_DETERMINISTIC = os.environ.get("DMPI_DETERMINISTIC_BN", os.environ.get("DMPI_DETERMINISTIC", "1")) == "1"
+_BN_DET_BYTES = 1 << 20
+_bn_det = {}
+
+
+def _bn_det_scratch(device) -> torch.Tensor:
+    """Zero-initialised scratch of the deterministic BatchNorm backward reduction, one per (device, stream)."""
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    t = _bn_det.get(key)
+    if t is None:
+        t = torch.zeros(_BN_DET_BYTES // 4, dtype=torch.float32, device=device)
+        _bn_det[key] = t
+    return t
+
+
 def bn_forward(y, res, out, ssum, ssq, gamma, beta, save_mean, save_invstd, running_mean, running_var, nbt,
                eps: float, momentum: float, training: bool, relu: bool, relu_mask=None) -> None:
     """``relu_mask`` (uint8 [M, C/8], optional) receives one bit per output element (value > 0) for the backward pass."""
@@ -58,9 +75,11 @@ def bn_backward(dout, y, act, dy, dres, mean, invstd, gamma, acc, dgamma, dbeta,
     _, ld_dy = _rows_ld(dy)
     ld_dres = _rows_ld(dres)[1] if dres is not None else 0
     C = y.shape[-1]
-    rc = N.cuda().dmpi_bn_backward_mask(_p(dout), _p(y), _p(act), _p(dy), _p(dres), M, C, ld_dout, ldy, ld_act, ld_dy,
-                                        ld_dres, _p(mean), _p(invstd), _p(gamma), _p(beta), int(relu_from_y),
-                                        _p(relu_mask), _p(acc), _p(dgamma), _p(dbeta), N.stream_ptr())
+    scratch = _bn_det_scratch(dout.device) if _DETERMINISTIC else None
+    rc = N.cuda().dmpi_bn_backward_det(_p(dout), _p(y), _p(act), _p(dy), _p(dres), M, C, ld_dout, ldy, ld_act, ld_dy,
+                                       ld_dres, _p(mean), _p(invstd), _p(gamma), _p(beta), int(relu_from_y),
+                                       _p(relu_mask), _p(acc), _p(dgamma), _p(dbeta), _p(scratch),
+                                       _BN_DET_BYTES if scratch is not None else 0, N.stream_ptr())
     N.count_launch(2)
     _chk(rc, "dmpi_bn_backward")
 

@@ -45,6 +45,14 @@ int dmpi_bn_backward_mask(const void* dout, const void* y, const void* act, void
                           const float* mean, const float* invstd, const float* gamma, const float* beta,
                           int relu_from_y, const void* relu_mask, float* acc, float* dgamma, float* dbeta,
                           void* stream);
+/* Same with deterministic channel reductions: `det_scratch` is zero-initialised device memory (1 MiB covers every
+ * shape) that no concurrently running launch shares; the partial sums of the thread blocks are added in a fixed order
+ * instead of with fp32 atomics, and `acc` need not be zeroed. */
+int dmpi_bn_backward_det(const void* dout, const void* y, const void* act, void* dy, void* dres, long long M, int C,
+                         long long ld_dout, long long ldy, long long ld_act, long long ld_dy, long long ld_dres,
+                         const float* mean, const float* invstd, const float* gamma, const float* beta,
+                         int relu_from_y, const void* relu_mask, float* acc, float* dgamma, float* dbeta,
+                         void* det_scratch, long long det_bytes, void* stream);
 /* Same computation for callers that cannot allocate the scratch (GPU memory fully owned by the host application's
  * pool, latency-critical paths where cudaMalloc/cudaFree would stall the device, plug-ins barred from any allocator).
  * This entry point has no counterpart in the reference; it exists for such embedders only.
