@@ -208,7 +208,6 @@ __global__ void __launch_bounds__(kBnThreads, 4) bn_bwd_reduce_kernel(const BnBw
         if (u == 1 && !has2) break;
         const uint32_t gi[4] = {g[u].x, g[u].y, g[u].z, g[u].w}, yi[4] = {yv[u].x, yv[u].y, yv[u].z, yv[u].w},
                        ai[4] = {av[u].x, av[u].y, av[u].z, av[u].w};
-#pragma unroll
         uint32_t ri[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
