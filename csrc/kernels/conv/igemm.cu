@@ -698,11 +698,15 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
           }
         }
         if (p.stat_scratch != nullptr) {
-          __threadfence();
+          // release: the barrier orders every thread's partial stores before thread 0's fence + ticket (one fence per
+          // CTA instead of 128); acquire on the other side: fence after drawing the last ticket, then the CTA barrier
           named_bar_sync(2, kStatThreads);
           if (st == 0) {
+            __threadfence();
             uint32_t* ticket = reinterpret_cast<uint32_t*>(p.stat_scratch);  // fixed place: launches of every shape share it
-            *last_flag = (atomicAdd(ticket, 1u) == gridDim.x - 1) ? 1u : 0u;
+            const bool last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+            if (last) __threadfence();
+            *last_flag = last ? 1u : 0u;
           }
         }
       }
@@ -723,7 +727,6 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
   // order.  8 lanes share a channel (each takes every 8th CTA of that channel's list, ascending) and combine with a
   // fixed shuffle tree, so the summation order is a function of the launch geometry only.
   if (p.stat_scratch != nullptr && *last_flag != 0u) {
-    __threadfence();
     const int grid = static_cast<int>(gridDim.x);
     const int nnt = p.num_n_tiles;
     // L lanes share a quad of 4 channels (16-byte loads); each lane takes every L-th CTA of the tile's list, ascending

@@ -252,12 +252,15 @@ __global__ void __launch_bounds__(kBnThreads, 4) bn_bwd_reduce_kernel(const BnBw
       for (int r = 0; r < 32; ++r) t += src[(r * 8 + (ch >> 3)) * 8 + (ch & 7)];
       part[blockIdx.y * 128 + threadIdx.x] = t;
     }
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) is_last = (atomicAdd(&tickets[slab], 1u) == static_cast<uint32_t>(RB - 1)) ? 1u : 0u;
+    __syncthreads();  // orders every thread's partial store before thread 0's fence + ticket (release)
+    if (threadIdx.x == 0) {
+      __threadfence();
+      const bool last = atomicAdd(&tickets[slab], 1u) == static_cast<uint32_t>(RB - 1);
+      if (last) __threadfence();  // acquire
+      is_last = last ? 1u : 0u;
+    }
     __syncthreads();
     if (is_last) {
-      __threadfence();
       // 256 threads: quantity q = t % 128, the even / odd row blocks go to the two halves, each in ascending order
       const int q = threadIdx.x & 127, half = threadIdx.x >> 7;
       float t = 0.f;
