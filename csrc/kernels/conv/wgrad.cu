@@ -203,15 +203,25 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
       mbar_wait(tfull, 0);
       tc_fence_after_sync();
       const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+      // deterministic mode: the partial tile goes to scratch [tile][split][128][G*BN]; wgrad_reduce_kernel adds the
+      // splits in order.  Otherwise red.add straight into the gradient.
+      float* part = p.stat_scratch == nullptr ? nullptr
+                        : p.stat_scratch + (static_cast<size_t>(blockIdx.x) * gridDim.y + blockIdx.y) * (128 * G * BN) +
+                              static_cast<size_t>(q * 32 + lane) * (G * BN);
 #pragma unroll 1
-      for (int g = 0; g < ntap; ++g) {
-        float* dst_row = p.dw + static_cast<long long>(krow) * p.w_ld + p.tap_woff[tap0 + g] + c_blk * BN;
+      for (int g = 0; g < (part ? G : ntap); ++g) {
+        float* dst_row = p.dw + static_cast<long long>(krow) * p.w_ld + p.tap_woff[tap0 + (g < ntap ? g : 0)] + c_blk * BN;
 #pragma unroll 1
         for (int chunk = 0; chunk < BN / 32; ++chunk) {
           uint32_t v[32];
           tmem_ld_32x32(t_addr + g * BN + chunk * 32, v);
           tmem_ld_wait();
-          if (krow < p.k_out) {
+          if (part != nullptr) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+              *reinterpret_cast<uint4*>(part + g * BN + chunk * 32 + j) =
+                  g < ntap ? make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]) : make_uint4(0, 0, 0, 0);
+          } else if (krow < p.k_out) {
             const int c0 = c_blk * BN + chunk * 32;
 #pragma unroll
             for (int j = 0; j < 32; j += 4) {
@@ -223,6 +233,11 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
         }
       }
     }
+  } else if (warp >= 4 && p.stat_scratch != nullptr) {
+    // no pixel tiles for this split: its partial must still read as zero
+    float* part = p.stat_scratch + (static_cast<size_t>(blockIdx.x) * gridDim.y + blockIdx.y) * (128 * G * BN) +
+                  static_cast<size_t>((warp - 4) * 32 + lane) * (G * BN);
+    for (int j = 0; j < G * BN; j += 4) *reinterpret_cast<uint4*>(part + j) = make_uint4(0, 0, 0, 0);
   }
   tc_fence_before_sync();
   if (CG == 2) {
@@ -231,6 +246,45 @@ __global__ void __launch_bounds__(kWThreads, 1) wgrad_kernel(const __grid_consta
   } else {
     __syncthreads();
     if (warp == 2) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+  }
+}
+
+// Deterministic split-K: adds the partial tiles of wgrad_kernel in split order and accumulates onto the gradient.
+// grid = (tiles, 16): a block owns 8 accumulator rows of one tile.
+__global__ void __launch_bounds__(256) wgrad_reduce_kernel(const __grid_constant__ ConvKernelParams p, int G, int BN,
+                                                           int CG, int splits) {
+  const int tile = blockIdx.x;
+  const int c_blk = CG == 2 ? (tile / p.num_k_tiles) % p.num_c_tiles : tile % p.num_c_tiles;
+  const int k_blk = CG == 2 ? tile % p.num_k_tiles : (tile / p.num_c_tiles) % p.num_k_tiles;
+  const int tap0 = (tile / (p.num_c_tiles * p.num_k_tiles)) * G;
+  const int ntap = (p.ntaps - tap0) < G ? (p.ntaps - tap0) : G;
+  const int cols = G * BN, q4 = cols >> 2;
+  const float* base = p.stat_scratch + static_cast<size_t>(tile) * splits * (128 * cols);
+  for (int i = threadIdx.x; i < 8 * q4; i += blockDim.x) {
+    const int row = blockIdx.y * 8 + i / q4, col = (i % q4) * 4;
+    const int g = col / BN, cc = col - g * BN;
+    const int krow = k_blk * 128 + row, c = c_blk * BN + cc;
+    if (g >= ntap || krow >= p.k_out || c >= p.c_total) continue;
+    float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float* src = base + static_cast<size_t>(row) * cols + col;
+    int sidx = 0;
+    for (; sidx + 4 <= splits; sidx += 4) {  // four splits in flight, added in split order
+      float4 v[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) v[k] = __ldcg(reinterpret_cast<const float4*>(src + static_cast<size_t>(sidx + k) * (128 * cols)));
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        t.x += v[k].x; t.y += v[k].y; t.z += v[k].z; t.w += v[k].w;
+      }
+    }
+    for (; sidx < splits; ++sidx) {
+      const float4 v = __ldcg(reinterpret_cast<const float4*>(src + static_cast<size_t>(sidx) * (128 * cols)));
+      t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w;
+    }
+    float4* dst = reinterpret_cast<float4*>(p.dw + static_cast<long long>(krow) * p.w_ld + p.tap_woff[tap0 + g] + c);
+    float4 d = *dst;
+    d.x += t.x; d.y += t.y; d.z += t.z; d.w += t.w;
+    *dst = d;
   }
 }
 
@@ -259,9 +313,12 @@ static int launch_wgrad(const ConvKernelParams& kp, cudaStream_t stream) {
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, wgrad_kernel<BN, G, CG>, kp) == cudaSuccess ? 0 : -11;
+    if (cudaLaunchKernelEx(&cfg, wgrad_kernel<BN, G, CG>, kp) != cudaSuccess) return -11;
+  } else {
+    wgrad_kernel<BN, G, CG><<<grid, kWThreads, Cfg::kSmemBytes, stream>>>(kp);
   }
-  wgrad_kernel<BN, G, CG><<<grid, kWThreads, Cfg::kSmemBytes, stream>>>(kp);
+  if (kp.stat_scratch != nullptr)
+    wgrad_reduce_kernel<<<dim3(grid.x, 16), 256, 0, stream>>>(kp, G, BN, CG, kp.splits);
   return cudaGetLastError() == cudaSuccess ? 0 : -11;
 }
 
@@ -318,6 +375,13 @@ extern "C" int dmpi_wgrad_run(dmpi_conv_plan* plan, const void* dy, const void* 
   }
   if (splits > kp.num_m_tiles) splits = kp.num_m_tiles > 0 ? kp.num_m_tiles : 1;
   kp.splits = splits;
+  {
+    // deterministic split-K needs one partial tile per CTA in the scratch the caller attached to the plan
+    const long long need = static_cast<long long>(groups) * kp.num_k_tiles * kp.num_c_tiles * splits * 128LL * G * d.bn * 4;
+    const bool aligned = d.c_total % 4 == 0 && d.w_ld % 4 == 0 && (reinterpret_cast<uintptr_t>(dw) & 15) == 0;
+    kp.stat_scratch = (plan->stat_scratch != nullptr && need <= plan->stat_scratch_bytes && aligned)
+                          ? static_cast<float*>(plan->stat_scratch) : nullptr;
+  }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (d.bn == 64) {
     if (G == 3) return launch_wgrad<64, 3>(kp, s);

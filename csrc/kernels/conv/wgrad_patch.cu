@@ -40,6 +40,7 @@ struct WgradPatchParams {
   int x_bytes, y_bytes, x_stride, y_stride, stages;
   int k_tiles, c_tiles, splits;
   int k_out, c_total;
+  float* partials;  // deterministic split-K: [tile][split][5][128][64] floats, added in split order by the reduce kernel
 };
 
 __global__ void __launch_bounds__(kWpThreads, 1) wgrad_patch_kernel(const __grid_constant__ WgradPatchParams p) {
@@ -168,7 +169,13 @@ __global__ void __launch_bounds__(kWpThreads, 1) wgrad_patch_kernel(const __grid
           uint32_t v[32];
           tmem_ld_32x32(t_addr + g * 64 + chunk * 32, v);
           tmem_ld_wait();
-          if (live) {
+          if (p.partials != nullptr) {
+            float* part = p.partials + ((static_cast<size_t>(blockIdx.x) * gridDim.y + blockIdx.y) * kWpGroups + g) * (128 * 64) +
+                          m * 64 + chunk * 32;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+              *reinterpret_cast<uint4*>(part + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+          } else if (live) {
             // lanes hold consecutive input channels: every red below is one coalesced 128-byte request per filter
             float* dst = p.dw + static_cast<long long>(k_blk * 64 + chunk * 32) * p.w_ld + p.tap_woff[tap] + c;
 #pragma unroll
@@ -183,9 +190,51 @@ __global__ void __launch_bounds__(kWpThreads, 1) wgrad_patch_kernel(const __grid
       }
     }
   }
+  else if (warp >= 4 && p.partials != nullptr) {
+    // no pixel tiles for this split: its partial must still read as zero
+    const int m = (warp - 4) * 32 + lane;
+    for (int g = 0; g < kWpGroups; ++g) {
+      float* part = p.partials + ((static_cast<size_t>(blockIdx.x) * gridDim.y + blockIdx.y) * kWpGroups + g) * (128 * 64) + m * 64;
+      for (int j = 0; j < 64; j += 4) *reinterpret_cast<uint4*>(part + j) = make_uint4(0, 0, 0, 0);
+    }
+  }
   tc_fence_before_sync();
   __syncthreads();
   if (warp == 2) tmem_dealloc<kWpTmemCols>(tmem_base);
+}
+
+// Deterministic split-K: grid = (tiles, 5 tap pairs); adds the partial tiles in split order onto the gradient.
+__global__ void __launch_bounds__(256) wgrad_patch_reduce_kernel(const __grid_constant__ WgradPatchParams p) {
+  const int tile = blockIdx.x, g = blockIdx.y;
+  const int c_blk = tile % p.c_tiles, k_blk = tile / p.c_tiles;
+  const size_t split_stride = static_cast<size_t>(kWpGroups) * 128 * 64;
+  const float* base = p.partials + (static_cast<size_t>(tile) * p.splits * kWpGroups + g) * (128 * 64);
+  for (int i = threadIdx.x; i < 128 * 16; i += blockDim.x) {
+    const int m = i >> 4, j = (i & 15) * 4;
+    const int tap = 2 * g + (m >> 6), c = c_blk * 64 + (m & 63);
+    if (tap >= 9 || c >= p.c_total) continue;
+    float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float* src = base + m * 64 + j;
+    int sidx = 0;
+    for (; sidx + 4 <= p.splits; sidx += 4) {
+      float4 v[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) v[k] = __ldcg(reinterpret_cast<const float4*>(src + (sidx + k) * split_stride));
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        t.x += v[k].x; t.y += v[k].y; t.z += v[k].z; t.w += v[k].w;
+      }
+    }
+    for (; sidx < p.splits; ++sidx) {
+      const float4 v = __ldcg(reinterpret_cast<const float4*>(src + sidx * split_stride));
+      t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w;
+    }
+    const float tv[4] = {t.x, t.y, t.z, t.w};
+    float* dst = p.dw + static_cast<long long>(k_blk * 64 + j) * p.w_ld + p.tap_woff[tap] + c;
+#pragma unroll
+    for (int e = 0; e < 4; ++e)
+      if (k_blk * 64 + j + e < p.k_out) dst[static_cast<long long>(e) * p.w_ld] += tv[e];
+  }
 }
 
 }  // namespace dmpi
@@ -279,6 +328,11 @@ extern "C" int dmpi_wgrad_patch_run(dmpi_conv_plan* plan, const void* dy, const 
     attr_smem = 227 * 1024;
   }
   dim3 grid(tiles, splits, 1);
+  const long long need = static_cast<long long>(tiles) * splits * kWpGroups * 128 * 64 * 4;
+  p.partials = (plan->stat_scratch != nullptr && need <= plan->stat_scratch_bytes) ? static_cast<float*>(plan->stat_scratch)
+                                                                                      : nullptr;
   wgrad_patch_kernel<<<grid, kWpThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
+  if (p.partials != nullptr)
+    wgrad_patch_reduce_kernel<<<dim3(tiles, kWpGroups), 256, 0, static_cast<cudaStream_t>(stream)>>>(p);
   return cudaGetLastError() == cudaSuccess ? 0 : -11;
 }

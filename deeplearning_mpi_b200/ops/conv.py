@@ -125,7 +125,13 @@ def _get_plan(key, build):
     return ent[0]
 
 
-_DETERMINISTIC = os.environ.get("DMPI_DETERMINISTIC_CONV", os.environ.get("DMPI_DETERMINISTIC", "1")) == "1"
+# DMPI_DETERMINISTIC: 0 = fp32 atomics everywhere; 1 (default) = order-independent BatchNorm statistics and backward
+# reductions (bit-identical forward, gradients equal to ~1e-7; costs ~2 % of a ResNet-50 step); 2 = additionally the
+# split-K weight gradients are added in split order (bit-identical gradients, what cudnn.deterministic asks of the
+# reference; costs another ~5 %: one partial tile per CTA written and re-read).
+_DET_LEVEL = os.environ.get("DMPI_DETERMINISTIC", "1")
+_DETERMINISTIC = os.environ.get("DMPI_DETERMINISTIC_CONV", "0" if _DET_LEVEL == "0" else "1") == "1"
+_DETERMINISTIC_WGRAD = os.environ.get("DMPI_DETERMINISTIC_WGRAD", "1" if _DET_LEVEL == "2" else "0") == "1"
 _STAT_SCRATCH_BYTES = 512 << 10  # >= (148 CTAs * 2 * 256 columns + 1) * 4
 _stat_scratch = {}
 
@@ -139,6 +145,25 @@ def _stat_scratch_for_current_stream(device) -> torch.Tensor:
         t = torch.zeros(_STAT_SCRATCH_BYTES // 4, dtype=torch.float32, device=device)
         _stat_scratch[key] = t
     return t
+
+
+_WGRAD_DET_BYTES = 32 << 20  # one partial tile per CTA of a one-wave launch (<= 29 MiB on 148 SMs)
+_wgrad_scratch = {}
+
+
+def _det_wgrad_plan(plan, device):
+    """Attaches (or detaches) the scratch that makes a weight-gradient launch add its split-K partials in a fixed
+    order (deterministic) instead of with red.add; one scratch per (device, stream)."""
+    if _DETERMINISTIC_WGRAD:
+        key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+        t = _wgrad_scratch.get(key)
+        if t is None:
+            t = torch.empty(_WGRAD_DET_BYTES // 4, dtype=torch.float32, device=device)
+            _wgrad_scratch[key] = t
+        N.cuda().dmpi_conv_plan_set_stat_scratch(plan, t.data_ptr(), _WGRAD_DET_BYTES)
+    else:
+        N.cuda().dmpi_conv_plan_set_stat_scratch(plan, None, 0)
+    return plan
 
 
 def _run_igemm(plan, a, b, out, bias, stats, addend=None, add_strides=(0, 0, 0)):
@@ -475,7 +500,8 @@ def conv2d_wgrad(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, R: int, S:
         d.splits = 0
         return d
 
-    rc = N.cuda().dmpi_wgrad_run(_get_plan(key, build), dy.data_ptr(), x.data_ptr(), dw.data_ptr(), N.stream_ptr())
+    rc = N.cuda().dmpi_wgrad_run(_det_wgrad_plan(_get_plan(key, build), dw.device), dy.data_ptr(), x.data_ptr(),
+                                 dw.data_ptr(), N.stream_ptr())
     N.count_launch()
     _check(rc, "dmpi_wgrad_run")
 
@@ -516,7 +542,7 @@ def _conv2d_wgrad_patch(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, pad
         d.splits = int(os.environ.get("DMPI_WGRAD_PATCH_SPLITS", "0"))
         return d
 
-    rc = N.cuda().dmpi_wgrad_patch_run(_get_plan(key, build), dy.data_ptr(), x.data_ptr(), dw.data_ptr(),
+    rc = N.cuda().dmpi_wgrad_patch_run(_det_wgrad_plan(_get_plan(key, build), dw.device), dy.data_ptr(), x.data_ptr(), dw.data_ptr(),
                                        N.stream_ptr())
     N.count_launch()
     _check(rc, "dmpi_wgrad_patch_run")
@@ -582,7 +608,8 @@ def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor) -> None:
         d.bn = bn
         return d
 
-    rc = N.cuda().dmpi_wgrad_run(_get_plan(key, build), dy.data_ptr(), x.data_ptr(), dw.data_ptr(), N.stream_ptr())
+    rc = N.cuda().dmpi_wgrad_run(_det_wgrad_plan(_get_plan(key, build), dw.device), dy.data_ptr(), x.data_ptr(),
+                                 dw.data_ptr(), N.stream_ptr())
     N.count_launch()
     _check(rc, "dmpi_wgrad_run")
 
@@ -685,7 +712,8 @@ def convt2x2_wgrad(dout: torch.Tensor, x: torch.Tensor, dw: torch.Tensor) -> Non
         return d
 
     # M side = x (rows of dw are input channels), N side = the four dout quadrants.
-    rc = N.cuda().dmpi_wgrad_run(_get_plan(key, build), x.data_ptr(), dout.data_ptr(), dw.data_ptr(), N.stream_ptr())
+    rc = N.cuda().dmpi_wgrad_run(_det_wgrad_plan(_get_plan(key, build), dw.device), x.data_ptr(), dout.data_ptr(),
+                                 dw.data_ptr(), N.stream_ptr())
     N.count_launch()
     _check(rc, "dmpi_wgrad_run")
 
@@ -786,6 +814,7 @@ def smallc_wgrad(dy: torch.Tensor, xp: torch.Tensor, dwwin: torch.Tensor, R: int
         d.bn = 64
         return d
 
-    rc = N.cuda().dmpi_wgrad_run(_get_plan(key, build), dy.data_ptr(), xp.data_ptr(), dwwin.data_ptr(), N.stream_ptr())
+    rc = N.cuda().dmpi_wgrad_run(_det_wgrad_plan(_get_plan(key, build), dwwin.device), dy.data_ptr(), xp.data_ptr(),
+                                 dwwin.data_ptr(), N.stream_ptr())
     N.count_launch()
     _check(rc, "dmpi_wgrad_run")

@@ -35,7 +35,7 @@ def _rows_ld(x: torch.Tensor) -> Tuple[int, int]:
 
 
 # ------------------------------------------------------------------------------------------ BatchNorm
-_DETERMINISTIC = os.environ.get("DMPI_DETERMINISTIC_BN", os.environ.get("DMPI_DETERMINISTIC", "1")) == "1"
+_DETERMINISTIC = os.environ.get("DMPI_DETERMINISTIC_BN", "0" if os.environ.get("DMPI_DETERMINISTIC", "1") == "0" else "1") == "1"
 _BN_DET_BYTES = 1 << 20
 _bn_det = {}
 

@@ -402,27 +402,42 @@ def test_wgrad_side_stream_matches_default():
 
 
 def test_training_step_is_reproducible():
-    """Same weights, same batch, twice: the forward pass is bit-identical and the gradients agree to fp32 summation
-    order (only the split-K weight-gradient adds are unordered, and they do not feed back into the step).  Before the
-    BatchNorm reductions were made order-independent, the same comparison gave ~20 % (ReLU gate flips downstream of
-    1-ulp differences in the batch statistics)."""
+    """Same weights, same batch, twice.  Default (level 1): the forward pass is bit-identical and the gradients agree to
+    fp32 summation order (only the split-K weight-gradient adds are unordered, and they do not feed back into the step).
+    Level 2 (deterministic split-K as well): the whole gradient arena is bit-identical.  Before the BatchNorm reductions
+    were made order-independent the same comparison gave ~20 % (ReLU gate flips downstream of 1-ulp differences in the
+    batch statistics)."""
     import deeplearning_mpi_b200.nn as dnn
     from deeplearning_mpi_b200.models import resnet50
+    from deeplearning_mpi_b200.ops import conv as CV
     from deeplearning_mpi_b200.utils.arena import ensure_arena
 
     torch.manual_seed(11)
     base = resnet50(num_classes=10)
     x, y = torch.randn(16, 3, 96, 96).to(DEV), torch.randint(0, 10, (16,)).to(DEV)
-    outs, grads = [], []
-    for _ in range(2):
-        m = copy.deepcopy(base).to(DEV)
-        m.train()
-        out = m(x)
-        dnn.cross_entropy(out, y).backward()
-        torch.cuda.synchronize()
-        outs.append(out.detach().clone())
-        grads.append(ensure_arena(m).flat_g.clone())
-    assert torch.equal(outs[0], outs[1]), "forward pass is not bit-reproducible"
-    rel = ((grads[0] - grads[1]).norm() / (grads[1].norm() + 1e-20)).item()
-    print(f"run-to-run gradient rel diff = {rel:.3e}")
-    assert rel < 1e-5
+
+    def twice():
+        outs, grads = [], []
+        for _ in range(2):
+            m = copy.deepcopy(base).to(DEV)
+            m.train()
+            out = m(x)
+            dnn.cross_entropy(out, y).backward()
+            torch.cuda.synchronize()
+            outs.append(out.detach().clone())
+            grads.append(ensure_arena(m).flat_g.clone())
+        assert torch.equal(outs[0], outs[1]), "forward pass is not bit-reproducible"
+        return grads
+
+    saved = CV._DETERMINISTIC_WGRAD
+    try:
+        CV._DETERMINISTIC_WGRAD = False
+        g = twice()
+        rel = ((g[0] - g[1]).norm() / (g[1].norm() + 1e-20)).item()
+        print(f"level 1: run-to-run gradient rel diff = {rel:.3e}")
+        assert rel < 1e-5
+        CV._DETERMINISTIC_WGRAD = True
+        g = twice()
+        assert torch.equal(g[0], g[1]), "level 2: gradients are not bit-reproducible"
+    finally:
+        CV._DETERMINISTIC_WGRAD = saved
