@@ -6,13 +6,16 @@
 //   filter tap is a coordinate offset and the halo is TMA's out-of-bounds zero fill.  Stride-2
 //   convolutions use one strided view per input parity class, so every tap is still a dense box.
 // * B tiles (BN filters x 64 channels) come from the K-major bf16 weight shadow.
-// * tcgen05.mma (cta_group::1, M=128, N=BN, K=16) accumulates in TMEM; two accumulator stages let the
-//   epilogue of tile i overlap the main loop of tile i+1.
+// * tcgen05.mma (M=128, N=BN, K=16; cta_group::1, or cta_group::2 with 256-row tiles, see IgemmCfg) accumulates in
+//   TMEM; two accumulator stages let the epilogue of tile i overlap the main loop of tile i+1.
+// * Patch mode (stride-1 3x3): one shared-memory patch of input pixels per (tile, channel block) serves all nine
+//   taps through row-shifted descriptors; the filter taps stream through a second ring or stay resident.
 // * The epilogue is a two-stage pipeline of its own, in sub-tiles of min(BN, 128) columns:
 //     converter warps   read TMEM (tcgen05.ld), add bias / a residual tensor / ReLU, round to bf16 and stage the
 //                       sub-tile in 128B-swizzled shared memory (two buffers);
 //     store/stat warps  issue the TMA store into the (possibly strided / channel-sliced) output view and accumulate
-//                       the per-channel sum and sum of squares of the stored values for BatchNorm.
+//                       the per-channel sum and sum of squares of the stored values for BatchNorm (published with
+//                       atomics, or, with a scratch attached, as per-CTA partials that the last CTA adds in order).
 //   The two groups hand buffers over through mbarriers only, so conversion of sub-tile i+1 overlaps the store and
 //   the statistics of sub-tile i.  (ncu on the K=64 1x1 layers showed the old single-group epilogue, not the main
 //   loop, pacing the kernel: ~740 dependent warp instructions per tile on two warps per scheduler.)
