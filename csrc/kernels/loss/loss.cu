@@ -143,36 +143,53 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(const float* __restrict__
 #pragma unroll
     for (int j = 0; j < 8; ++j) adw[k][j] = 0.f;
   }
-  for (long long pix = blockIdx.x * static_cast<long long>(nslab) + slab; pix < M;
-       pix += static_cast<long long>(gridDim.x) * nslab) {
-    const uint4 v = *reinterpret_cast<const uint4*>(x + pix * ldx + cv * 8);
-    const uint32_t vi[4] = {v.x, v.y, v.z, v.w};
-    float xv[8], g[8];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      xv[2 * j] = bf16lo(vi[j]);
-      xv[2 * j + 1] = bf16hi(vi[j]);
-    }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) g[j] = 0.f;
+  // two pixels per iteration with both loads issued up front (the kernel is a pure stream: one 16-byte load per
+  // pixel and thread left the memory system idle)
+  const long long stride = static_cast<long long>(gridDim.x) * nslab;
+  for (long long pix0 = blockIdx.x * static_cast<long long>(nslab) + slab; pix0 < M; pix0 += 2 * stride) {
+    const long long pix1 = pix0 + stride;
+    const bool has1 = pix1 < M;
+    uint4 vv[2];
+    float dd[2][kHeadMaxK];
+    vv[0] = *reinterpret_cast<const uint4*>(x + pix0 * ldx + cv * 8);
+    vv[1] = has1 ? *reinterpret_cast<const uint4*>(x + pix1 * ldx + cv * 8) : make_uint4(0, 0, 0, 0);
 #pragma unroll
     for (int k = 0; k < kHeadMaxK; ++k) {
-      if (k < K) {
-        const float d = dy[pix * K + k];
-        if (cv == 0) adb[k] += d;
+      dd[0][k] = k < K ? dy[pix0 * K + k] : 0.f;
+      dd[1][k] = (k < K && has1) ? dy[pix1 * K + k] : 0.f;
+    }
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          g[j] = fmaf(d, sw[k * C + cv * 8 + j], g[j]);
-          adw[k][j] = fmaf(d, xv[j], adw[k][j]);
+    for (int u = 0; u < 2; ++u) {
+      if (u == 1 && !has1) break;
+      const long long pix = u == 0 ? pix0 : pix1;
+      const uint32_t vi[4] = {vv[u].x, vv[u].y, vv[u].z, vv[u].w};
+      float xv[8], g[8];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        xv[2 * j] = bf16lo(vi[j]);
+        xv[2 * j + 1] = bf16hi(vi[j]);
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) g[j] = 0.f;
+#pragma unroll
+      for (int k = 0; k < kHeadMaxK; ++k) {
+        if (k < K) {
+          const float d = dd[u][k];
+          if (cv == 0) adb[k] += d;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            g[j] = fmaf(d, sw[k * C + cv * 8 + j], g[j]);
+            adw[k][j] = fmaf(d, xv[j], adw[k][j]);
+          }
         }
       }
+      uint4 o;
+      o.x = pack_bf16x2(g[0], g[1]);
+      o.y = pack_bf16x2(g[2], g[3]);
+      o.z = pack_bf16x2(g[4], g[5]);
+      o.w = pack_bf16x2(g[6], g[7]);
+      *reinterpret_cast<uint4*>(dx + pix * ld_dx + cv * 8) = o;
     }
-    uint4 o;
-    o.x = pack_bf16x2(g[0], g[1]);
-    o.y = pack_bf16x2(g[2], g[3]);
-    o.z = pack_bf16x2(g[4], g[5]);
-    o.w = pack_bf16x2(g[6], g[7]);
-    *reinterpret_cast<uint4*>(dx + pix * ld_dx + cv * 8) = o;
   }
 #pragma unroll
   for (int k = 0; k < kHeadMaxK; ++k) {
@@ -226,7 +243,7 @@ extern "C" int dmpi_head_backward(const float* dy, const void* x, const float* w
   const int threads = (256 / vecC) * vecC;
   const int nslab = threads / vecC;
   long long blocks = (M + nslab * 16 - 1) / (nslab * 16);
-  if (blocks > 148 * 4) blocks = 148 * 4;
+  if (blocks > 148 * 8) blocks = 148 * 8;
   if (blocks < 1) blocks = 1;
   const size_t smem = (2 * K * C + K) * sizeof(float);
   head_bwd_kernel<<<static_cast<int>(blocks), threads, smem, static_cast<cudaStream_t>(stream)>>>(
