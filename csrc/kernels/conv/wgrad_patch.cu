@@ -63,9 +63,14 @@ __global__ void __launch_bounds__(kWpThreads, 1) wgrad_patch_kernel(const __grid
   const int pt_end = static_cast<int>((static_cast<long long>(p.num_m_tiles) * (split + 1)) / p.splits);
   const int num_it = pt_end - pt_begin;
 
-  // zero the whole ring once: the regions beyond the TMA boxes are read (K rounding, row shifts) but never written
-  for (int i = threadIdx.x * 16; i < S * stage_bytes; i += kWpThreads * 16)
-    *reinterpret_cast<uint4*>(smem + i) = make_uint4(0, 0, 0, 0);
+  // zero, once, the regions beyond the TMA boxes: they are read (K rounding, row shifts) but never written
+  for (int st = 0; st < S; ++st) {
+    uint8_t* sx = smem + st * stage_bytes;
+    for (int i = p.x_bytes + threadIdx.x * 16; i < p.x_stride; i += kWpThreads * 16)
+      *reinterpret_cast<uint4*>(sx + i) = make_uint4(0, 0, 0, 0);
+    for (int i = p.x_stride + p.y_bytes + threadIdx.x * 16; i < stage_bytes; i += kWpThreads * 16)
+      *reinterpret_cast<uint4*>(sx + i) = make_uint4(0, 0, 0, 0);
+  }
   fence_proxy_async_smem();
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&p.x_map);

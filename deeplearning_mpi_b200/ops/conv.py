@@ -466,7 +466,7 @@ def conv2d_wgrad(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, R: int, S:
     assert xn == n and c % 64 == 0 and dw.dtype == torch.float32
     bn = _wgrad_bn(c)
     if (_WGRAD_PATCH and R == 3 and S == 3 and stride == 1 and pad == 1 and k % 64 == 0
-            and (_WGRAD_PATCH == 2 or k <= _WGRAD_PATCH_MAXK)):
+            and (_WGRAD_PATCH == 2 or (k <= _WGRAD_PATCH_MAXK and n * oh * ow >= _WGRAD_PATCH_MIN_PIXELS))):
         # k <= 64 is where the tap-group kernel wastes half of every M = 128 MMA (bench/wgrad_ab.py: 512x512 192->64
         # 1772 -> 858 us, 128->64 811 -> 575 us; at k = 128 the two kernels tie or the tap-group one wins)
         return _conv2d_wgrad_patch(dy, x, dw, pad)
@@ -508,6 +508,7 @@ def conv2d_wgrad(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, R: int, S:
 
 _WGRAD_PATCH = int(os.environ.get("DMPI_WGRAD_PATCH", "1"))  # 0 off, 1 automatic, 2 every eligible 3x3
 _WGRAD_PATCH_MAXK = int(os.environ.get("DMPI_WGRAD_PATCH_MAXK", "64"))
+_WGRAD_PATCH_MIN_PIXELS = 1 << 16  # below this the launch is latency-bound and the tap-group kernel is 2 % ahead
 
 
 def _conv2d_wgrad_patch(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, pad: int) -> None:
