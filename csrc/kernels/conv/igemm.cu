@@ -46,7 +46,7 @@ constexpr int kStatWarps = 4;
 constexpr int kTileM = 128;
 constexpr int kBlockK = 64;  // bf16 elements = one 128-byte swizzle row
 constexpr int kABytes = kTileM * kBlockK * 2;
-constexpr int kDetInFlight = 6;  // partial-sum rows a thread of the last-CTA reduction keeps in flight
+constexpr int kDetInFlight = 8;  // partial-sum rows a thread of the last-CTA reduction keeps in flight
 constexpr int kStatHdr = 64;  // floats reserved at the head of the statistics scratch (ticket counter)
 
 // CG = 1: one CTA per tile.  CG = 2: a CTA pair (cluster of two SMs of one TPC) works on a 256-row tile with
@@ -736,7 +736,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
     const int cpt = ((grid / CG + nnt - 1) / nnt) * CG;  // CTAs per N tile (upper bound)
     // L lanes per quad: as many as keep the whole channel range in ONE pass (each pass is a chain of L2 round trips)
     const int nq_all = p.stat_mod >> 2;
-    int L = 8;
+    int L = 32;
     while (L > 1 && (kThreads / L < nq_all || L > cpt)) L >>= 1;
     const int l = threadIdx.x & (L - 1);
     const int quads_per_pass = kThreads / L;
