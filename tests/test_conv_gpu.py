@@ -320,3 +320,25 @@ def test_fprop_statistics_are_bit_reproducible():
         _close(runs[0][1], (yf * yf).sum(dim=(0, 1, 2)), 2e-3, f"det_stats_sq{(n, h, c, k, R)}")
         for r in runs[1:]:
             assert torch.equal(r[0], runs[0][0]) and torch.equal(r[1], runs[0][1]), f"not reproducible: {(n, h, c, k, R)}"
+
+
+def test_fprop_statistics_atomics_mode():
+    """DMPI_DETERMINISTIC=0 path: the per-channel sums are published with fp32 atomics instead of the last-CTA
+    reduction; same values up to summation order."""
+    from deeplearning_mpi_b200.ops import conv as C
+
+    _torch_setup()
+    saved = C._DETERMINISTIC
+    try:
+        C._DETERMINISTIC = False
+        for (n, h, c, k, R, pad) in [(64, 56, 64, 64, 1, 0), (16, 28, 256, 256, 3, 1), (8, 14, 512, 1024, 1, 0)]:
+            x = _rand(n, h, h, c)
+            wt = _rand(k, c, R, R, scale=(c * R * R) ** -0.5)
+            ssum = torch.zeros(k, device=_dev())
+            ssq = torch.zeros(k, device=_dev())
+            y = C.conv2d_fprop(x, _w2d(wt), R, R, 1, pad, stats=(ssum, ssq))
+            yf = y.float()
+            _close(ssum, yf.sum(dim=(0, 1, 2)), 2e-3, f"atomic_stats_sum{(n, h, c, k, R)}")
+            _close(ssq, (yf * yf).sum(dim=(0, 1, 2)), 2e-3, f"atomic_stats_sq{(n, h, c, k, R)}")
+    finally:
+        C._DETERMINISTIC = saved
