@@ -21,7 +21,7 @@ for (n, h, c, k) in shapes:
     w2d = (torch.randn(k, 9 * c, device=dev) * (9 * c) ** -0.5).bfloat16()
     ssum = torch.zeros(k, device=dev); ssq = torch.zeros(k, device=dev)
     res = []
-    for mode in (0, 2):
+    for mode in (0, 1):  # 0: per-tap loads; 1: the planner's patch rules (resident filter for N <= 64, CTA pairs above)
         C._PATCH = mode
         res.append(timeit(lambda: C.conv2d_fprop(x, w2d, 3, 3, 1, 1, stats=(ssum, ssq))))
     fl = 2.0 * n * h * h * k * c * 9

@@ -174,11 +174,11 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
     }
     if (p.patch) {
       for (int i = 0; i < kMaxPA; ++i) {
-        mbar_init(&pa_full[i], 1);
+        mbar_init(&pa_full[i], CG);  // pair: the leader's expect_tx arrival + the peer's plain arrival
         mbar_init(&pa_empty[i], 1);
       }
       for (int i = 0; i < kMaxPB; ++i) {
-        mbar_init(&pb_full[i], 1);
+        mbar_init(&pb_full[i], CG);
         mbar_init(&pb_empty[i], 1);
       }
     }
@@ -207,12 +207,20 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
       uint32_t pha = 0, phb = 0;
       bool first = true;
       TileWalk tk;
-      for (tk.init(p, 1, 0); tk.remaining > 0; tk.next(p)) {
+      for (tk.init(p, CG, rank); tk.remaining > 0; tk.next(p)) {
         const int w0 = tk.tw * p.box_w, h0 = tk.th * p.box_h, n0 = tk.tn * p.box_n;
         for (int cb = 0; cb < p.cblocks; ++cb) {
           mbar_wait_spin(&pa_empty[sa], pha ^ 1u);
-          mbar_arrive_expect_tx(&pa_full[sa], static_cast<uint32_t>(p.pa_bytes));
-          tma_load_4d(ring_a + sa * p.pa_stride, &p.a_map[0], &pa_full[sa], cb * kBlockK, w0 - p.halo, h0 - p.halo, n0);
+          if (CG == 1) {
+            mbar_arrive_expect_tx(&pa_full[sa], static_cast<uint32_t>(p.pa_bytes));
+            tma_load_4d(ring_a + sa * p.pa_stride, &p.a_map[0], &pa_full[sa], cb * kBlockK, w0 - p.halo, h0 - p.halo, n0);
+          } else {
+            // CTA pair: each CTA brings the patch of its own M tile; both report to the leader's barrier
+            const uint32_t lead = mapa_u32(smem_u32(&pa_full[sa]), 0);
+            if (rank == 0) mbar_arrive_expect_tx(&pa_full[sa], 2u * static_cast<uint32_t>(p.pa_bytes));
+            else mbar_arrive_cluster(lead);
+            tma_load_4d_pair(ring_a + sa * p.pa_stride, &p.a_map[0], lead, cb * kBlockK, w0 - p.halo, h0 - p.halo, n0);
+          }
           if (++sa == p.pa_stages) {
             sa = 0;
             pha ^= 1u;
@@ -221,9 +229,18 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
           for (int t = 0; t < p.ntaps; ++t) {
             const int slot = p.b_resident ? cb * p.ntaps + t : sb;
             if (!p.b_resident) mbar_wait_spin(&pb_empty[sb], phb ^ 1u);
-            mbar_arrive_expect_tx(&pb_full[slot], Cfg::kBBytes);
-            tma_load_2d(ring_b + slot * Cfg::kBBytes, &p.b_map, &pb_full[slot], p.tap_koff[t] + cb * kBlockK,
-                        tk.n_blk * BN);
+            if (CG == 1) {
+              mbar_arrive_expect_tx(&pb_full[slot], Cfg::kBBytes);
+              tma_load_2d(ring_b + slot * Cfg::kBBytes, &p.b_map, &pb_full[slot], p.tap_koff[t] + cb * kBlockK,
+                          tk.n_blk * BN);
+            } else {
+              // each CTA of the pair loads its half of the filter-tap tile
+              const uint32_t lead = mapa_u32(smem_u32(&pb_full[slot]), 0);
+              if (rank == 0) mbar_arrive_expect_tx(&pb_full[slot], 2u * Cfg::kBBytes);
+              else mbar_arrive_cluster(lead);
+              tma_load_2d_pair(ring_b + slot * Cfg::kBBytes, &p.b_map, lead, p.tap_koff[t] + cb * kBlockK,
+                               tk.n_blk * BN + rank * Cfg::kBRows);
+            }
             if (!p.b_resident && ++sb == p.pb_stages) {
               sb = 0;
               phb ^= 1u;
@@ -277,7 +294,27 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
     const bool leader = elect_one();
     const uint32_t hi = umma_desc_hi(1024);
     if (p.patch) {
-      constexpr uint32_t idesc = umma_idesc_bf16(kTileM, BN, 0, 0);
+      // (CTA pairs: only the leader CTA issues; both CTAs' patches sit at the same shared-memory offsets, each CTA's
+      // filter-tap slot holds its half of the tile)
+      constexpr uint32_t idesc = umma_idesc_bf16(kTileM * CG, BN, 0, 0);
+      const bool issuer = leader && rank == 0;
+      auto mma4 = [&](uint32_t d, uint32_t a_lo, uint32_t b_lo, uint32_t accum0) {
+        if (CG == 2) {
+          umma_bf16_pair_lohi(d, a_lo, hi, b_lo, hi, idesc, accum0);
+          umma_bf16_pair_lohi(d, a_lo + 2, hi, b_lo + 2, hi, idesc, 1u);
+          umma_bf16_pair_lohi(d, a_lo + 4, hi, b_lo + 4, hi, idesc, 1u);
+          umma_bf16_pair_lohi(d, a_lo + 6, hi, b_lo + 6, hi, idesc, 1u);
+        } else {
+          umma_bf16_lohi(d, a_lo, hi, b_lo, hi, idesc, accum0);
+          umma_bf16_lohi(d, a_lo + 2, hi, b_lo + 2, hi, idesc, 1u);
+          umma_bf16_lohi(d, a_lo + 4, hi, b_lo + 4, hi, idesc, 1u);
+          umma_bf16_lohi(d, a_lo + 6, hi, b_lo + 6, hi, idesc, 1u);
+        }
+      };
+      auto commit = [&](uint64_t* bar) {
+        if (CG == 2) umma_commit_pair(bar, 0b11);
+        else umma_commit(bar);
+      };
       const uint32_t ring_a = smem_u32(smem);
       const uint32_t ring_b = ring_a + p.pa_stages * p.pa_stride;
       const uint32_t a_lo_ring = umma_desc_lo(ring_a, 0);
@@ -302,7 +339,9 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
       uint32_t acc_phase = 0;
       bool first = true;
       TileWalk tk;
-      for (tk.init(p, 1, 0); tk.remaining > 0; --tk.remaining) {
+      tk.init(p, CG, rank);
+      if (rank != 0) tk.remaining = 0;  // the peer CTA's MMA warp issues nothing (its barriers live in the leader)
+      for (; tk.remaining > 0; --tk.remaining) {
         mbar_wait_spin(&tempty[acc], acc_phase ^ 1u);
         tc_fence_after_sync();
         const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
@@ -314,15 +353,12 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
           if (ntaps == 9 && resident && !first) {
             // whole filter resident: no barrier traffic inside the tile
             const uint32_t b_cb = b_lo0 + static_cast<uint32_t>(cb * 9) * pb_step;
-            if (leader) {
+            if (issuer) {
 #pragma unroll
               for (int t = 0; t < 9; ++t) {
                 const uint32_t a_lo = a_lo0 + ts[t];
                 const uint32_t b_lo = b_cb + static_cast<uint32_t>(t) * pb_step;
-                umma_bf16_lohi(d_tmem, a_lo, hi, b_lo, hi, idesc, t == 0 ? accum : 1u);
-                umma_bf16_lohi(d_tmem, a_lo + 2, hi, b_lo + 2, hi, idesc, 1u);
-                umma_bf16_lohi(d_tmem, a_lo + 4, hi, b_lo + 4, hi, idesc, 1u);
-                umma_bf16_lohi(d_tmem, a_lo + 6, hi, b_lo + 6, hi, idesc, 1u);
+                mma4(d_tmem, a_lo, b_lo, t == 0 ? accum : 1u);
               }
             }
             accum = 1u;
@@ -331,14 +367,11 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
             for (int t = 0; t < 9; ++t) {
               mbar_wait_spin(&pb_full[sb], phb);
               tc_fence_after_sync();
-              if (leader) {
+              if (issuer) {
                 const uint32_t a_lo = a_lo0 + ts[t];
                 const uint32_t b_lo = b_lo0 + static_cast<uint32_t>(sb) * pb_step;
-                umma_bf16_lohi(d_tmem, a_lo, hi, b_lo, hi, idesc, accum);
-                umma_bf16_lohi(d_tmem, a_lo + 2, hi, b_lo + 2, hi, idesc, 1u);
-                umma_bf16_lohi(d_tmem, a_lo + 4, hi, b_lo + 4, hi, idesc, 1u);
-                umma_bf16_lohi(d_tmem, a_lo + 6, hi, b_lo + 6, hi, idesc, 1u);
-                umma_commit(&pb_empty[sb]);
+                mma4(d_tmem, a_lo, b_lo, accum);
+                commit(&pb_empty[sb]);
               }
               accum = 1u;
               if (++sb == pb_stages) {
@@ -357,12 +390,9 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
               }
               const uint32_t a_lo = a_lo0 + tap_shift[t];
               const uint32_t b_lo = b_lo0 + static_cast<uint32_t>(slot) * pb_step;
-              if (leader) {
-                umma_bf16_lohi(d_tmem, a_lo, hi, b_lo, hi, idesc, accum);
-                umma_bf16_lohi(d_tmem, a_lo + 2, hi, b_lo + 2, hi, idesc, 1u);
-                umma_bf16_lohi(d_tmem, a_lo + 4, hi, b_lo + 4, hi, idesc, 1u);
-                umma_bf16_lohi(d_tmem, a_lo + 6, hi, b_lo + 6, hi, idesc, 1u);
-                if (!resident) umma_commit(&pb_empty[sb]);
+              if (issuer) {
+                mma4(d_tmem, a_lo, b_lo, accum);
+                if (!resident) commit(&pb_empty[sb]);
               }
               accum = 1u;
               if (!resident && ++sb == pb_stages) {
@@ -371,14 +401,14 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
               }
             }
           }
-          if (leader) umma_commit(&pa_empty[sa]);
+          if (issuer) commit(&pa_empty[sa]);
           if (++sa == pa_stages) {
             sa = 0;
             pha ^= 1u;
           }
         }
         first = false;
-        if (leader) umma_commit(&tfull[acc]);
+        if (issuer) commit(&tfull[acc]);
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1u;
       }
@@ -999,7 +1029,7 @@ extern "C" int dmpi_igemm_run_add(dmpi_conv_plan* plan, const void* a, const voi
     // ring geometry: as many filter-tap stages as fit next to 2-3 patch stages; the whole filter stays resident when
     // it fits and every tile of the launch uses the same N tile
     const int ph = d.box_h + 2 * d.halo;
-    if (d.box_n != 1 || d.a_nviews != 1 || d.cta_group == 2 || (d.box_h - 1) * kp.pw + d.box_w > kTileM) {
+    if (d.box_n != 1 || d.a_nviews != 1 || (d.box_h - 1) * kp.pw + d.box_w > kTileM) {
       set_err("igemm: illegal patch-mode geometry");
       return -12;
     }
@@ -1007,13 +1037,16 @@ extern "C" int dmpi_igemm_run_add(dmpi_conv_plan* plan, const void* a, const voi
     const int rows_alloc = read_rows > kp.pw * ph ? read_rows : kp.pw * ph;
     kp.pa_bytes = kp.pw * ph * 128;
     kp.pa_stride = ((rows_alloc * 128 + 1023) / 1024) * 1024;
-    const int ring = d.bn == 64 ? IgemmCfg<64, 1>::kRingBytes : (d.bn == 128 ? IgemmCfg<128, 1>::kRingBytes : IgemmCfg<256, 1>::kRingBytes);
-    const int bbytes = d.bn * kBlockK * 2;
+    const bool pair = d.cta_group == 2;
+    const int ring = d.bn == 64 ? IgemmCfg<64, 1>::kRingBytes
+                                : (d.bn == 128 ? (pair ? IgemmCfg<128, 2>::kRingBytes : IgemmCfg<128, 1>::kRingBytes)
+                                               : (pair ? IgemmCfg<256, 2>::kRingBytes : IgemmCfg<256, 1>::kRingBytes));
+    const int bbytes = (pair ? d.bn / 2 : d.bn) * kBlockK * 2;  // a CTA of a pair holds half of every filter-tap tile
     const int taps_total = d.ntaps * d.cblocks;
     // prefer a configuration in which the whole filter stays resident (then only patches stream); 3 patch stages
     // if they fit beside it, else 2
     int pa = 3;
-    const bool can_reside = kp.num_n_tiles == 1 && taps_total <= 12;
+    const bool can_reside = !pair && kp.num_n_tiles == 1 && taps_total <= 12;
     if (can_reside && ring - 3 * kp.pa_stride < taps_total * bbytes && ring - 2 * kp.pa_stride >= taps_total * bbytes) pa = 2;
     if (ring - pa * kp.pa_stride < 4 * bbytes) pa = 2;
     int pb = (ring - pa * kp.pa_stride) / bbytes;
@@ -1024,7 +1057,7 @@ extern "C" int dmpi_igemm_run_add(dmpi_conv_plan* plan, const void* a, const voi
     }
     kp.pa_stages = pa;
     kp.pb_stages = pb;
-    kp.b_resident = (kp.num_n_tiles == 1 && taps_total <= pb) ? 1 : 0;
+    kp.b_resident = (!pair && kp.num_n_tiles == 1 && taps_total <= pb) ? 1 : 0;
   }
   if (!plan->maps_valid || plan->cached_a != a || plan->cached_b != b || plan->cached_o != out) {
     if (d.patch) {

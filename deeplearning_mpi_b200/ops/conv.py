@@ -224,23 +224,37 @@ def choose_patch_tile(ow: int, oh: int, halo: int = 1) -> Optional[Tuple[int, in
     return best
 
 
-def _patch_ok(R, S, stride, pad, c_in, ow, oh, n_out=64):
-    """Patch mode pays where the whole filter stays resident in shared memory (C_in = 64, N <= 64: 88 vs 136 us on
-    56x56x64 3x3); with streamed filter taps the weight traffic dominates and it only ties (DMPI_PATCH=2 forces it)."""
+_PATCH_PAIR = int(os.environ.get("DMPI_PATCH_PAIR", "1"))  # patch mode together with CTA pairs for N >= 128
+
+
+def _patch_ok(R, S, stride, pad, c_in, ow, oh, n_out=64, cg=1):
+    """Patch-mode tile for a 3x3 stride-1 layer, or None.  With N <= 64 the whole filter stays resident in shared
+    memory (56x56x64: 88 vs 136 us).  With wider N the filter taps stream; that only pays together with CTA pairs
+    (each CTA loads its own patch and half of every tap tile, ~2.3x less L2 -> SM traffic than per-tap loads), so the
+    single-CTA streamed variant is used only when forced (DMPI_PATCH=2)."""
     if not _PATCH or R != S or R != 3 or stride != 1 or pad != 1 or c_in % 64 != 0:
         return None
-    if _PATCH != 2 and n_out > 64:  # bench/igemm_patch_ab.py: 64->64 1.5-1.9x, 128/192->64 +5-12 %, N >= 128 ties
-        return None
+    if _PATCH != 2 and n_out > 64:
+        # bench/igemm_patch_ab.py: with CTA pairs the 128-wide tile gains 8-15 % on large images (256x256: 318 -> 282 us)
+        # and ties on small ones; the 256-wide tile loses 8-12 % (its per-tap loads were already amortised)
+        # (on 28x28 it costs ResNet-50 1.4 %: only the wide images, whose row-segment tiles waste no accumulator rows)
+        if not (cg == 2 and _PATCH_PAIR and _pick_bn(n_out, 9 * c_in) == 128 and ow >= 128):
+            return None
     t = choose_patch_tile(ow, oh, pad)
     if t is None or t[2] < _PATCH_MIN_EFF:
         return None
     # two patch stages plus at least two filter-tap tiles must fit in the kernel's operand ring (igemm.cu: kRingBytes)
     bn = _pick_bn(n_out, 9 * c_in)
-    ring = {64: 192, 128: 160, 256: 144}[bn] * 1024
+    if cg == 2:
+        ring = {128: 144, 256: 160}[bn] * 1024
+        tap_bytes = bn * 64
+    else:
+        ring = {64: 192, 128: 160, 256: 144}[bn] * 1024
+        tap_bytes = bn * 128
     pw = t[0] + 2 * pad
     rows = max(128 + 2 * pad * pw + 2 * pad, pw * (t[1] + 2 * pad))
     stride = -(-rows * 128 // 1024) * 1024
-    if ring - 2 * stride < 2 * bn * 128:
+    if ring - 2 * stride < 2 * tap_bytes:
         return None
     return t
 
@@ -264,9 +278,7 @@ def conv2d_fprop(x: torch.Tensor, w2d: torch.Tensor, R: int, S: int, stride: int
             and _is_flat(n, oh, ow, osn, osh, osw))
     bn = _pick_bn(kout, R * S * c)
     cg = _pick_cg(bn, R * S * c)
-    ptile = _patch_ok(R, S, stride, pad, c, ow, oh, kout)
-    if ptile is not None:
-        cg = 1
+    ptile = _patch_ok(R, S, stride, pad, c, ow, oh, kout, cg)
     key = ("fprop", n, h, w, c, sn, sh, sw, kout, R, S, stride, pad, osn, osh, osw, bias is not None,
            stats is not None, relu, bn, cg, ptile)
 
@@ -349,9 +361,7 @@ def conv2d_dgrad(dy: torch.Tensor, wt2d: torch.Tensor, R: int, S: int, stride: i
     cg = _pick_cg(bn, ktot)
     if stride == 1:
         flat = R == 1 and S == 1 and pad == 0 and _is_flat(n, oh, ow, sn, sh, sw) and _is_flat(n, ih, iw, osn, osh, osw)
-        ptile = _patch_ok(R, S, 1, pad, k, iw, ih, c)
-        if ptile is not None:
-            cg = 1
+        ptile = _patch_ok(R, S, 1, pad, k, iw, ih, c, cg)
         key = ("dgrad1", n, oh, ow, k, sn, sh, sw, c, R, S, pad, osn, osh, osw, bn, cg, ptile)
 
         def build():
