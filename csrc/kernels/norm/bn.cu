@@ -157,13 +157,20 @@ struct BnBwdArgs {
                       // BatchNorm+ReLU without residual (same fp32 fma as the forward) and saves one tensor read per pass
 };
 
+// Where the ReLU gate of the backward pass comes from (compile-time: the variants need different registers).
+constexpr int kGateNone = 0;  // no ReLU
+constexpr int kGateY = 1;     // recomputed as (y*scale + shift > 0)
+constexpr int kGateBits = 2;  // the bit mask written by the forward pass
+constexpr int kGateAct = 3;   // the saved forward output (> 0)
+
 // Pass 1: per-channel reductions.  Thread (tx, ty): tx owns 8 consecutive channels, ty strides rows.
-// kFromY selects the ReLU-mask source at compile time (the two variants need different per-channel registers).
 // kDet selects the deterministic variant: grid = (C/64 channel slabs, row blocks), a block covers 64 channels x 32 rows
 // per step, every block parks its 128 partial sums in `partials` and the last block of a slab (ticket counter) adds
 // the slab's partials in row-block order — no floating-point atomics, so the result is bit-reproducible.
-template <bool kFromY, bool kDet>
-__global__ void __launch_bounds__(kBnThreads, 4) bn_bwd_reduce_kernel(const BnBwdArgs a, float* partials) {
+// U rows per thread are in flight: a read-only pass needs ~100 KB of loads in flight per SM to approach the HBM rate
+// (loaded latency ~1.7 us); two rows per thread on four resident blocks gave 32-64 KB and 3.3-5 of 6.5 TB/s.
+template <int kGate, bool kDet, int U>
+__global__ void __launch_bounds__(kBnThreads, 2) bn_bwd_reduce_kernel(const BnBwdArgs a, float* partials) {
   const int vecC = a.C >> 3;
   // tx: global 8-channel group of this thread; ty: its row inside the block's row step
   const int tx = kDet ? static_cast<int>(blockIdx.x) * 8 + (threadIdx.x & 7) : threadIdx.x % vecC;
@@ -177,7 +184,7 @@ __global__ void __launch_bounds__(kBnThreads, 4) bn_bwd_reduce_kernel(const BnBw
     s1[j] = s2[j] = 0.f;
     mean[j] = a.mean[c0 + j];
     sc[j] = sh[j] = 0.f;
-    if (kFromY) {
+    if (kGate == kGateY) {
       const float g = a.gamma ? a.gamma[c0 + j] : 1.f;
       const float b = a.beta ? a.beta[c0 + j] : 0.f;
       const float istd = a.invstd[c0 + j];
@@ -187,32 +194,37 @@ __global__ void __launch_bounds__(kBnThreads, 4) bn_bwd_reduce_kernel(const BnBw
   }
   if (ty < rows_per_block) {
     const long long stride = static_cast<long long>(kDet ? gridDim.y : gridDim.x) * rows_per_block;
-    for (long long row = (kDet ? blockIdx.y : blockIdx.x) * static_cast<long long>(rows_per_block) + ty; row < a.M;
-         row += 2 * stride) {
-      const long long row2 = row + stride;
-      const bool has2 = row2 < a.M;
-      uint4 g[2], yv[2], av[2];
-      av[0] = av[1] = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);
-      g[0] = *reinterpret_cast<const uint4*>(a.dout + row * a.ld_dout + c0);
-      yv[0] = *reinterpret_cast<const uint4*>(a.y + row * a.ldy + c0);
-      if (!kFromY && a.relu_mask) av[0] = expand_relu_bits(a.relu_mask[row * vecC + tx]);
-      else if (!kFromY && a.act) av[0] = *reinterpret_cast<const uint4*>(a.act + row * a.ld_act + c0);
-      if (has2) {
-        g[1] = *reinterpret_cast<const uint4*>(a.dout + row2 * a.ld_dout + c0);
-        yv[1] = *reinterpret_cast<const uint4*>(a.y + row2 * a.ldy + c0);
-        if (!kFromY && a.relu_mask) av[1] = expand_relu_bits(a.relu_mask[row2 * vecC + tx]);
-        else if (!kFromY && a.act) av[1] = *reinterpret_cast<const uint4*>(a.act + row2 * a.ld_act + c0);
+    // The masked gradient is the residual branch's gradient; writing it here lets the apply pass read it back
+    // instead of dout + gate (measured: storing it from the apply pass instead is 6 % slower overall).
+    const bool write_dres = (kGate == kGateBits || kGate == kGateAct) && a.dres != nullptr;
+    for (long long row0 = (kDet ? blockIdx.y : blockIdx.x) * static_cast<long long>(rows_per_block) + ty; row0 < a.M;
+         row0 += U * stride) {
+      uint4 g[U], yv[U], av[kGate == kGateAct ? U : 1];
+      uint32_t mb[kGate == kGateBits ? U : 1];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long row = row0 + u * stride;
+        if (row < a.M) {
+          g[u] = *reinterpret_cast<const uint4*>(a.dout + row * a.ld_dout + c0);
+          yv[u] = *reinterpret_cast<const uint4*>(a.y + row * a.ldy + c0);
+          if (kGate == kGateBits) mb[u] = a.relu_mask[row * vecC + tx];
+          if (kGate == kGateAct) av[u] = *reinterpret_cast<const uint4*>(a.act + row * a.ld_act + c0);
+        }
       }
 #pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        if (u == 1 && !has2) break;
+      for (int u = 0; u < U; ++u) {
+        const long long row = row0 + u * stride;
+        if (row >= a.M) break;
+        uint4 gate = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);
+        if (kGate == kGateBits) gate = expand_relu_bits(mb[u]);
+        if (kGate == kGateAct) gate = av[u];
         const uint32_t gi[4] = {g[u].x, g[u].y, g[u].z, g[u].w}, yi[4] = {yv[u].x, yv[u].y, yv[u].z, yv[u].w},
-                       ai[4] = {av[u].x, av[u].y, av[u].z, av[u].w};
+                       ai[4] = {gate.x, gate.y, gate.z, gate.w};
         uint32_t ri[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const bool m0 = kFromY ? fmaf(bf16lo(yi[j]), sc[2 * j], sh[2 * j]) > 0.f : bf16lo(ai[j]) > 0.f;
-          const bool m1 = kFromY ? fmaf(bf16hi(yi[j]), sc[2 * j + 1], sh[2 * j + 1]) > 0.f : bf16hi(ai[j]) > 0.f;
+          const bool m0 = kGate == kGateY ? fmaf(bf16lo(yi[j]), sc[2 * j], sh[2 * j]) > 0.f : bf16lo(ai[j]) > 0.f;
+          const bool m1 = kGate == kGateY ? fmaf(bf16hi(yi[j]), sc[2 * j + 1], sh[2 * j + 1]) > 0.f : bf16hi(ai[j]) > 0.f;
           const float d0 = m0 ? bf16lo(gi[j]) : 0.f;
           const float d1 = m1 ? bf16hi(gi[j]) : 0.f;
           s1[2 * j] += d0;
@@ -221,10 +233,7 @@ __global__ void __launch_bounds__(kBnThreads, 4) bn_bwd_reduce_kernel(const BnBw
           s2[2 * j + 1] = fmaf(d1, bf16hi(yi[j]) - mean[2 * j + 1], s2[2 * j + 1]);
           ri[j] = (m0 ? (gi[j] & 0x0000FFFFu) : 0u) | (m1 ? (gi[j] & 0xFFFF0000u) : 0u);
         }
-        // The masked gradient is the residual branch's gradient; writing it here lets the apply pass read it back
-        // instead of dout + act (one tensor read less).
-        if (!kFromY && a.dres && (a.act || a.relu_mask))
-          *reinterpret_cast<uint4*>(a.dres + (u == 0 ? row : row2) * a.ld_dres + c0) = make_uint4(ri[0], ri[1], ri[2], ri[3]);
+        if (write_dres) *reinterpret_cast<uint4*>(a.dres + row * a.ld_dres + c0) = make_uint4(ri[0], ri[1], ri[2], ri[3]);
       }
     }
   }
@@ -261,14 +270,32 @@ __global__ void __launch_bounds__(kBnThreads, 4) bn_bwd_reduce_kernel(const BnBw
     }
     __syncthreads();
     if (is_last) {
-      // 256 threads: quantity q = t % 128, the even / odd row blocks go to the two halves, each in ascending order
-      const int q = threadIdx.x & 127, half = threadIdx.x >> 7;
-      float t = 0.f;
-      for (int rb = half; rb < RB; rb += 2) t += __ldcg(part + rb * 128 + q);
-      r1[threadIdx.x] = t;
+      // 8 warps x 32 lanes: a lane owns four of the slab's 128 quantities (one 16-byte load per row block), warp w adds
+      // row blocks w, w + 8, ... in ascending order with eight loads in flight; the eight warp sums are then added in
+      // warp order.  The order depends on the launch geometry only.
+      const int quad = threadIdx.x & 31, grp = threadIdx.x >> 5;
+      const float4* src = reinterpret_cast<const float4*>(part) + quad;  // row block stride: 32 float4
+      float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+      int rb = grp;
+      for (; rb + 56 < RB; rb += 64) {
+        float4 v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = __ldcg(src + static_cast<size_t>(rb + 8 * k) * 32);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          t.x += v[k].x; t.y += v[k].y; t.z += v[k].z; t.w += v[k].w;
+        }
+      }
+      for (; rb < RB; rb += 8) {
+        const float4 v = __ldcg(src + static_cast<size_t>(rb) * 32);
+        t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w;
+      }
+      reinterpret_cast<float4*>(r1)[grp * 32 + quad] = t;  // (r1 / r2 were last read before the ticket barrier)
       __syncthreads();
       if (threadIdx.x < 128) {
-        const float total = r1[threadIdx.x] + r1[threadIdx.x + 128];
+        float total = 0.f;
+#pragma unroll
+        for (int w = 0; w < kBnThreads / 32; ++w) total += r1[w * 128 + threadIdx.x];
         const int c = slab * 64 + (threadIdx.x & 63);
         if (threadIdx.x < 64) a.acc[c] = total;
         else a.acc[a.C + c] = total * a.invstd[c];
@@ -291,7 +318,10 @@ __global__ void __launch_bounds__(kBnThreads, 4) bn_bwd_reduce_kernel(const BnBw
 }
 
 // Pass 2: dy = gamma * invstd * (dz - mean(dz) - xhat * mean(dz * xhat)); block 0 also emits dgamma/dbeta.
-__global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_kernel(const BnBwdArgs a) {
+// kGate: gate applied to `dout` here; kGateNone also covers the case where the reduce pass already stored the gated
+// gradient in dres (kFromDres: read that back instead of dout).  U rows per thread in flight.
+template <int kGate, bool kFromDres, int U>
+__global__ void __launch_bounds__(kBnThreads, U >= 4 ? 2 : 3) bn_bwd_apply_kernel(const BnBwdArgs a) {
   // Thread (tx, ty): tx owns 8 consecutive channels for the whole kernel, so the per-channel constants live in
   // registers and the streaming loop is pure load / FMA / store:  dy = A*dz + B*y + D  with
   //   A = gamma*invstd,  B = -A*invstd*mean(dz*xhat),  D = -A*mean(dz) - B*mean.
@@ -309,7 +339,7 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_kernel(const BnBwdArg
     const float g = a.gamma ? a.gamma[c] : 1.f;
     const float istd = a.invstd[c], mean = a.mean[c];
     sc[j] = g * istd;
-    sh[j] = (a.relu_from_y && a.beta ? a.beta[c] : 0.f) - mean * g * istd;
+    sh[j] = (kGate == kGateY && a.beta ? a.beta[c] : 0.f) - mean * g * istd;
     kA[j] = g * istd;
     kB[j] = -kA[j] * istd * (sdzx * invM);
     kD[j] = -kA[j] * (sdz * invM) - kB[j] * mean;
@@ -320,38 +350,37 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_kernel(const BnBwdArg
   }
   if (ty >= rows_per_block) return;
   const long long stride = static_cast<long long>(gridDim.x) * rows_per_block;
-  for (long long row = blockIdx.x * static_cast<long long>(rows_per_block) + ty; row < a.M; row += 2 * stride) {
-    // two rows per iteration: all loads are issued before the first use
-    const long long row2 = row + stride;
-    const bool has2 = row2 < a.M;
-    uint4 g[2], yv[2], av[2];
-    // with a residual branch the reduce pass already stored the masked gradient in dres: read that back
-    const bool has_gate = a.act != nullptr || a.relu_mask != nullptr;
-    const bool masked = a.dres != nullptr && has_gate;
-    const __nv_bfloat16* gsrc = masked ? a.dres : a.dout;
-    const long long ldg = masked ? a.ld_dres : a.ld_dout;
-    g[0] = *reinterpret_cast<const uint4*>(gsrc + row * ldg + c0);
-    yv[0] = *reinterpret_cast<const uint4*>(a.y + row * a.ldy + c0);
-    av[0] = av[1] = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);
-    if (a.relu_mask && !masked) av[0] = expand_relu_bits(a.relu_mask[row * vecC + tx]);
-    else if (a.act && !masked) av[0] = *reinterpret_cast<const uint4*>(a.act + row * a.ld_act + c0);
-    if (has2) {
-      g[1] = *reinterpret_cast<const uint4*>(gsrc + row2 * ldg + c0);
-      yv[1] = *reinterpret_cast<const uint4*>(a.y + row2 * a.ldy + c0);
-      if (a.relu_mask && !masked) av[1] = expand_relu_bits(a.relu_mask[row2 * vecC + tx]);
-      else if (a.act && !masked) av[1] = *reinterpret_cast<const uint4*>(a.act + row2 * a.ld_act + c0);
+  const __nv_bfloat16* gsrc = kFromDres ? a.dres : a.dout;
+  const long long ldg = kFromDres ? a.ld_dres : a.ld_dout;
+  const bool write_dres = !kFromDres && a.dres != nullptr;
+  for (long long row0 = blockIdx.x * static_cast<long long>(rows_per_block) + ty; row0 < a.M; row0 += U * stride) {
+    // all loads of the U rows are issued before the first use
+    uint4 g[U], yv[U], av[kGate == kGateAct ? U : 1];
+    uint32_t mb[kGate == kGateBits ? U : 1];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long row = row0 + u * stride;
+      if (row < a.M) {
+        g[u] = *reinterpret_cast<const uint4*>(gsrc + row * ldg + c0);
+        yv[u] = *reinterpret_cast<const uint4*>(a.y + row * a.ldy + c0);
+        if (kGate == kGateBits) mb[u] = a.relu_mask[row * vecC + tx];
+        if (kGate == kGateAct) av[u] = *reinterpret_cast<const uint4*>(a.act + row * a.ld_act + c0);
+      }
     }
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
-      if (u == 1 && !has2) break;
-      const long long r = u == 0 ? row : row2;
+    for (int u = 0; u < U; ++u) {
+      const long long r = row0 + u * stride;
+      if (r >= a.M) break;
+      uint4 gate = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);
+      if (kGate == kGateBits) gate = expand_relu_bits(mb[u]);
+      if (kGate == kGateAct) gate = av[u];
       const uint32_t gi[4] = {g[u].x, g[u].y, g[u].z, g[u].w}, yi[4] = {yv[u].x, yv[u].y, yv[u].z, yv[u].w},
-                     ai[4] = {av[u].x, av[u].y, av[u].z, av[u].w};
+                     ai[4] = {gate.x, gate.y, gate.z, gate.w};
       uint32_t oi[4], ri[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const bool m0 = a.relu_from_y ? fmaf(bf16lo(yi[j]), sc[2 * j], sh[2 * j]) > 0.f : bf16lo(ai[j]) > 0.f;
-        const bool m1 = a.relu_from_y ? fmaf(bf16hi(yi[j]), sc[2 * j + 1], sh[2 * j + 1]) > 0.f : bf16hi(ai[j]) > 0.f;
+        const bool m0 = kGate == kGateY ? fmaf(bf16lo(yi[j]), sc[2 * j], sh[2 * j]) > 0.f : bf16lo(ai[j]) > 0.f;
+        const bool m1 = kGate == kGateY ? fmaf(bf16hi(yi[j]), sc[2 * j + 1], sh[2 * j + 1]) > 0.f : bf16hi(ai[j]) > 0.f;
         const float d0 = m0 ? bf16lo(gi[j]) : 0.f;
         const float d1 = m1 ? bf16hi(gi[j]) : 0.f;
         oi[j] = pack_bf16x2(fmaf(kA[2 * j], d0, fmaf(kB[2 * j], bf16lo(yi[j]), kD[2 * j])),
@@ -359,7 +388,7 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_kernel(const BnBwdArg
         ri[j] = pack_bf16x2(d0, d1);
       }
       *reinterpret_cast<uint4*>(a.dy + r * a.ld_dy + c0) = make_uint4(oi[0], oi[1], oi[2], oi[3]);
-      if (a.dres && !masked) *reinterpret_cast<uint4*>(a.dres + r * a.ld_dres + c0) = make_uint4(ri[0], ri[1], ri[2], ri[3]);
+      if (write_dres) *reinterpret_cast<uint4*>(a.dres + r * a.ld_dres + c0) = make_uint4(ri[0], ri[1], ri[2], ri[3]);
     }
   }
 }
@@ -432,6 +461,46 @@ static int grid_for(long long work_items, int threads) {
 }  // namespace dmpi
 
 using namespace dmpi;
+
+
+static int gate_kind(const dmpi::BnBwdArgs& a) {
+  if (a.relu_from_y) return dmpi::kGateY;
+  if (a.relu_mask) return dmpi::kGateBits;
+  if (a.act) return dmpi::kGateAct;
+  return dmpi::kGateNone;
+}
+
+// Four rows in flight per thread in both passes (measured per ResNet-50 shape with bench/bn_bwd_shapes.py: 2 rows
+// -12 %, 8 rows in the reduce pass -6 %; the act-gated apply variant keeps 2 rows for its third load stream).
+template <bool kDet>
+static void launch_bwd_reduce(const dmpi::BnBwdArgs& a, float* part, dim3 grid, int threads, cudaStream_t s) {
+  using namespace dmpi;
+  const size_t smem = static_cast<size_t>(threads) * 16 * sizeof(float);
+  switch (gate_kind(a)) {
+    case kGateY: bn_bwd_reduce_kernel<kGateY, kDet, 4><<<grid, threads, smem, s>>>(a, part); break;
+    case kGateBits: bn_bwd_reduce_kernel<kGateBits, kDet, 4><<<grid, threads, smem, s>>>(a, part); break;
+    case kGateAct: bn_bwd_reduce_kernel<kGateAct, kDet, 4><<<grid, threads, smem, s>>>(a, part); break;
+    default: bn_bwd_reduce_kernel<kGateNone, kDet, 4><<<grid, threads, smem, s>>>(a, part); break;
+  }
+}
+
+static void launch_bwd_apply(const dmpi::BnBwdArgs& a, int rows_per_block, int threads, cudaStream_t s) {
+  using namespace dmpi;
+  const int gate = gate_kind(a);
+  // the reduce pass already gated dout into dres: read that back, no gate needed here
+  const bool from_dres = a.dres != nullptr && (gate == kGateBits || gate == kGateAct);
+  // one wave: every block is resident (2 per SM for the 4-row variants, 3 for the 2-row one) and strides over the rows
+  const long long cap = 148LL * ((gate == kGateAct && !from_dres) ? 3 : 2);
+  long long blocks = (a.M + 8LL * rows_per_block - 1) / (8LL * rows_per_block);  // >= 8 rows per thread
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  const int grid = static_cast<int>(blocks);
+  if (from_dres) bn_bwd_apply_kernel<kGateNone, true, 4><<<grid, threads, 0, s>>>(a);
+  else if (gate == kGateY) bn_bwd_apply_kernel<kGateY, false, 4><<<grid, threads, 0, s>>>(a);
+  else if (gate == kGateBits) bn_bwd_apply_kernel<kGateBits, false, 4><<<grid, threads, 0, s>>>(a);
+  else if (gate == kGateAct) bn_bwd_apply_kernel<kGateAct, false, 2><<<grid, threads, 0, s>>>(a);
+  else bn_bwd_apply_kernel<kGateNone, false, 4><<<grid, threads, 0, s>>>(a);
+}
 
 extern "C" int dmpi_bn_forward_mask(const void* y, const void* res, void* out, long long M, int C, long long ldy,
                                     long long ldr, long long ldo, const float* sum, const float* sqsum,
@@ -569,38 +638,32 @@ extern "C" int dmpi_bn_backward_det(const void* dout, const void* y, const void*
   if (a.relu_mask) a.act = nullptr;
   a.relu_from_y = (relu_from_y && act == nullptr && relu_mask == nullptr) ? 1 : 0;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  // reduce: block = vecC * rows_per_block threads (vecC <= 256 for C <= 2048)
+  // reduce: block = vecC * rows_per_block threads (vecC <= 256 for C <= 2048); two blocks of 256 threads are resident
+  // per SM (launch bounds), and the grid is one such wave at most so that no block waits for a second wave
+  const long long wave = 148LL * 2;
   int threads = kBnThreads;
   if (vecC > threads) return -3;
   threads = (threads / vecC) * vecC;
   const int rows_per_block = threads / vecC;
   long long blocks = (M + rows_per_block * 8 - 1) / (rows_per_block * 8);
-  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks > wave) blocks = wave;
   if (blocks < 1) blocks = 1;
   bool det = false;
   if (det_scratch != nullptr && C % 64 == 0) {
     const int slabs = C / 64;
     long long rb = (M + 32 * 8 - 1) / (32 * 8);  // >= 8 rows per thread
-    long long cap = (148LL * 8) / slabs;
-    if (cap > 296) cap = 296;  // bounds the fixed-order tail of the last block (296 x 128 floats per slab)
+    long long cap = wave / slabs;
     if (cap < 1) cap = 1;
     if (rb > cap) rb = cap;
     if (rb < 1) rb = 1;
     if ((kDetHdr + static_cast<long long>(slabs) * rb * 128) * 4 <= det_bytes && slabs <= kDetHdr) {
       det = true;
       const dim3 grid(slabs, static_cast<unsigned>(rb));
-      float* part = static_cast<float*>(det_scratch);
-      if (a.relu_from_y) bn_bwd_reduce_kernel<true, true><<<grid, kBnThreads, kBnThreads * 16 * sizeof(float), s>>>(a, part);
-      else bn_bwd_reduce_kernel<false, true><<<grid, kBnThreads, kBnThreads * 16 * sizeof(float), s>>>(a, part);
+      launch_bwd_reduce<true>(a, static_cast<float*>(det_scratch), grid, kBnThreads, s);
     }
   }
-  if (!det) {
-    if (a.relu_from_y)
-      bn_bwd_reduce_kernel<true, false><<<static_cast<int>(blocks), threads, threads * 16 * sizeof(float), s>>>(a, nullptr);
-    else
-      bn_bwd_reduce_kernel<false, false><<<static_cast<int>(blocks), threads, threads * 16 * sizeof(float), s>>>(a, nullptr);
-  }
-  bn_bwd_apply_kernel<<<stream_grid(M, rows_per_block), threads, 0, s>>>(a);
+  if (!det) launch_bwd_reduce<false>(a, nullptr, dim3(static_cast<unsigned>(blocks)), threads, s);
+  launch_bwd_apply(a, rows_per_block, threads, s);
   return cudaGetLastError() == cudaSuccess ? 0 : -2;
 }
 
