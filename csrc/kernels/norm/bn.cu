@@ -41,7 +41,9 @@ struct BnFwdArgs {
                        // read 1/16 of the bytes of `out` for the ReLU gate of a residual block
 };
 
-__global__ void __launch_bounds__(kBnThreads) bn_fwd_kernel(const BnFwdArgs a) {
+// kRes: a residual tensor is added; U rows per thread are in flight (all loads issued before the first use).
+template <bool kRes, int U>
+__global__ void __launch_bounds__(kBnThreads, 3) bn_fwd_kernel(const BnFwdArgs a) {
   extern __shared__ float sm[];  // scale[C], shift[C]
   float* scale = sm;
   float* shift = sm + a.C;
@@ -88,22 +90,23 @@ __global__ void __launch_bounds__(kBnThreads) bn_fwd_kernel(const BnFwdArgs a) {
     sh[j] = shift[c0 + j];
   }
   const long long stride = static_cast<long long>(gridDim.x) * rows_per_block;
-  for (long long row = blockIdx.x * static_cast<long long>(rows_per_block) + ty; row < a.M; row += 2 * stride) {
-    const long long row2 = row + stride;
-    const bool has2 = row2 < a.M;
-    uint4 v[2], r[2];
-    r[0] = r[1] = make_uint4(0, 0, 0, 0);
-    v[0] = *reinterpret_cast<const uint4*>(a.y + row * a.ldy + c0);
-    if (a.res) r[0] = *reinterpret_cast<const uint4*>(a.res + row * a.ldr + c0);
-    if (has2) {
-      v[1] = *reinterpret_cast<const uint4*>(a.y + row2 * a.ldy + c0);
-      if (a.res) r[1] = *reinterpret_cast<const uint4*>(a.res + row2 * a.ldr + c0);
+  for (long long row0 = blockIdx.x * static_cast<long long>(rows_per_block) + ty; row0 < a.M; row0 += U * stride) {
+    uint4 v[U], r[kRes ? U : 1];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long row = row0 + u * stride;
+      if (row < a.M) {
+        v[u] = *reinterpret_cast<const uint4*>(a.y + row * a.ldy + c0);
+        if (kRes) r[u] = *reinterpret_cast<const uint4*>(a.res + row * a.ldr + c0);
+      }
     }
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
-      if (u == 1 && !has2) break;
+    for (int u = 0; u < U; ++u) {
+      const long long row = row0 + u * stride;
+      if (row >= a.M) break;
+      const uint4 rr = kRes ? r[kRes ? u : 0] : make_uint4(0, 0, 0, 0);
       const uint32_t vi[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
-      const uint32_t ri[4] = {r[u].x, r[u].y, r[u].z, r[u].w};
+      const uint32_t ri[4] = {rr.x, rr.y, rr.z, rr.w};
       uint32_t oi[4];
       uint32_t bits = 0;
 #pragma unroll
@@ -119,8 +122,8 @@ __global__ void __launch_bounds__(kBnThreads) bn_fwd_kernel(const BnFwdArgs a) {
         bits |= ((oi[j] & 0x7FFFu) != 0u && !(oi[j] & 0x8000u) ? 1u : 0u) << (2 * j);
         bits |= ((oi[j] & 0x7FFF0000u) != 0u && !(oi[j] & 0x80000000u) ? 1u : 0u) << (2 * j + 1);
       }
-      *reinterpret_cast<uint4*>(a.out + (u == 0 ? row : row2) * a.ldo + c0) = make_uint4(oi[0], oi[1], oi[2], oi[3]);
-      if (a.relu_mask) a.relu_mask[(u == 0 ? row : row2) * vecC + tx] = static_cast<uint8_t>(bits);
+      *reinterpret_cast<uint4*>(a.out + row * a.ldo + c0) = make_uint4(oi[0], oi[1], oi[2], oi[3]);
+      if (a.relu_mask) a.relu_mask[row * vecC + tx] = static_cast<uint8_t>(bits);
     }
   }
 }
@@ -551,8 +554,15 @@ extern "C" int dmpi_bn_forward_mask(const void* y, const void* res, void* out, l
   const int vecC = C / 8;
   if (vecC > kBnThreads) return -3;
   const int threads = (kBnThreads / vecC) * vecC;  // a whole number of rows per block
-  const int grid = stream_grid(M, threads / vecC);
-  bn_fwd_kernel<<<grid, threads, 2 * C * sizeof(float), static_cast<cudaStream_t>(stream)>>>(a);
+  // one wave of resident blocks (3 per SM, see the launch bounds), at least 8 rows per thread
+  const int rows_per_block = threads / vecC;
+  long long blocks = (M + 8LL * rows_per_block - 1) / (8LL * rows_per_block);
+  if (blocks > 148 * 3) blocks = 148 * 3;
+  if (blocks < 1) blocks = 1;
+  const int grid = static_cast<int>(blocks);
+  const size_t smem = 2 * static_cast<size_t>(C) * sizeof(float);
+  if (a.res) bn_fwd_kernel<true, 4><<<grid, threads, smem, static_cast<cudaStream_t>(stream)>>>(a);
+  else bn_fwd_kernel<false, 4><<<grid, threads, smem, static_cast<cudaStream_t>(stream)>>>(a);
   return cudaGetLastError() == cudaSuccess ? 0 : -2;
 }
 

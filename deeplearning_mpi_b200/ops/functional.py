@@ -117,7 +117,8 @@ class ConvBnAct(torch.autograd.Function):
         # residual + ReLU: the backward gate cannot be recomputed from y alone; one bit per element is 1/16 of the
         # bytes of re-reading `out`
         mask = None
-        if training and relu and residual is not None and torch.is_grad_enabled() and _RELU_MASK:
+        # (grad mode is off inside Function.forward: ask the context whether a backward pass can follow)
+        if training and relu and residual is not None and any(ctx.needs_input_grad) and _RELU_MASK:
             mask = torch.empty((y.numel() // 8,), dtype=torch.uint8, device=y.device)
         K.bn_forward(y, residual, out, stats[0] if training else None, stats[1] if training else None, _nb(gamma),
                      _nb(beta), mean, invstd, bn.running_mean if track else None, bn.running_var if track else None,
