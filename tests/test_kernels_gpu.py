@@ -135,6 +135,25 @@ def test_maxpool(k, s, p, hw):
     _close(dx2, xr.grad.permute(0, 2, 3, 1) + add.float(), 1e-2, "maxpool_bwd_addend")
 
 
+@pytest.mark.parametrize("k,p", [(3, 1), (2, 0)])
+def test_maxpool_backward_quads_nonsquare(k, p):
+    """Stride-2 pooling of an even, non-square image runs the one-thread-per-input-quad backward kernel."""
+    from deeplearning_mpi_b200.ops import kernels as K
+
+    torch.manual_seed(5)
+    x = torch.randn(3, 12, 20, 128, device=DEV).bfloat16()
+    y, idx = K.maxpool_forward(x, k, 2, p, True)
+    xr = x.float().permute(0, 3, 1, 2).clone().requires_grad_(True)
+    yr = F.max_pool2d(xr, k, 2, p)
+    dy = torch.randn_like(y.float()).bfloat16()
+    yr.backward(dy.float().permute(0, 3, 1, 2))
+    add = torch.randn(3, 12, 20, 128, device=DEV).bfloat16()
+    dx = K.maxpool_backward(dy, idx, tuple(x.shape), k, 2, p)
+    _close(dx, xr.grad.permute(0, 2, 3, 1), 1e-2, "maxpool_bwd_quad")
+    dx2 = K.maxpool_backward(dy, idx, tuple(x.shape), k, 2, p, addend=add)
+    _close(dx2, xr.grad.permute(0, 2, 3, 1) + add.float(), 1e-2, "maxpool_bwd_quad_addend")
+
+
 def test_avgpool():
     from deeplearning_mpi_b200.ops import kernels as K
 
