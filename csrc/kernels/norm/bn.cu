@@ -43,7 +43,7 @@ struct BnFwdArgs {
 
 // kRes: a residual tensor is added; U rows per thread are in flight (all loads issued before the first use).
 template <bool kRes, int U>
-__global__ void __launch_bounds__(kBnThreads, 3) bn_fwd_kernel(const BnFwdArgs a) {
+__global__ void __launch_bounds__(kBnThreads) bn_fwd_kernel(const BnFwdArgs a) {
   extern __shared__ float sm[];  // scale[C], shift[C]
   float* scale = sm;
   float* shift = sm + a.C;
@@ -442,23 +442,15 @@ __global__ void __launch_bounds__(kBnThreads) bn_stats_kernel(const __nv_bfloat1
   }
 }
 
-// Row-streaming kernels: each block handles rows_per_block rows per step and two steps per loop iteration; enough
-// blocks to fill the machine (8 resident 256-thread blocks on each of the 148 SMs) but no more than there is work.
-static int stream_grid(long long rows, int rows_per_block) {
-  // at least 8 rows per thread: the per-thread prologue (per-channel constants from ~5 small arrays) costs as much
-  // as streaming several rows, which made the small late-layer launches latency-bound (22 us for 75 MB of traffic)
+// Row-streaming kernels run as ONE wave of resident blocks that stride over the rows (`per_sm` = resident blocks per
+// SM at the kernel's register count), with at least 8 rows per thread: the per-thread prologue (per-channel constants
+// from ~5 small arrays) costs as much as streaming several rows, which made the small late-layer launches
+// latency-bound.
+static int wave_grid(long long rows, int rows_per_block, int per_sm) {
   long long blocks = (rows + 8LL * rows_per_block - 1) / (8LL * rows_per_block);
-  const long long cap = 148LL * 8;
+  const long long cap = 148LL * per_sm;
   if (blocks > cap) blocks = cap;
   return blocks < 1 ? 1 : static_cast<int>(blocks);
-}
-
-static int grid_for(long long work_items, int threads) {
-  long long blocks = (work_items + threads - 1) / threads;
-  const long long cap = 148LL * 8;
-  if (blocks > cap) blocks = cap;
-  if (blocks < 1) blocks = 1;
-  return static_cast<int>(blocks);
 }
 
 }  // namespace dmpi
@@ -493,11 +485,7 @@ static void launch_bwd_apply(const dmpi::BnBwdArgs& a, int rows_per_block, int t
   // the reduce pass already gated dout into dres: read that back, no gate needed here
   const bool from_dres = a.dres != nullptr && (gate == kGateBits || gate == kGateAct);
   // one wave: every block is resident (2 per SM for the 4-row variants, 3 for the 2-row one) and strides over the rows
-  const long long cap = 148LL * ((gate == kGateAct && !from_dres) ? 3 : 2);
-  long long blocks = (a.M + 8LL * rows_per_block - 1) / (8LL * rows_per_block);  // >= 8 rows per thread
-  if (blocks > cap) blocks = cap;
-  if (blocks < 1) blocks = 1;
-  const int grid = static_cast<int>(blocks);
+  const int grid = wave_grid(a.M, rows_per_block, (gate == kGateAct && !from_dres) ? 3 : 2);
   if (from_dres) bn_bwd_apply_kernel<kGateNone, true, 4><<<grid, threads, 0, s>>>(a);
   else if (gate == kGateY) bn_bwd_apply_kernel<kGateY, false, 4><<<grid, threads, 0, s>>>(a);
   else if (gate == kGateBits) bn_bwd_apply_kernel<kGateBits, false, 4><<<grid, threads, 0, s>>>(a);
@@ -554,15 +542,14 @@ extern "C" int dmpi_bn_forward_mask(const void* y, const void* res, void* out, l
   const int vecC = C / 8;
   if (vecC > kBnThreads) return -3;
   const int threads = (kBnThreads / vecC) * vecC;  // a whole number of rows per block
-  // one wave of resident blocks (3 per SM, see the launch bounds), at least 8 rows per thread
   const int rows_per_block = threads / vecC;
-  long long blocks = (M + 8LL * rows_per_block - 1) / (8LL * rows_per_block);
-  if (blocks > 148 * 3) blocks = 148 * 3;
-  if (blocks < 1) blocks = 1;
-  const int grid = static_cast<int>(blocks);
+  // one wave of resident blocks (3 per SM at 72-80 registers), at least 8 rows per thread, 4 rows in flight
+  // (bench/bn_fwd_shapes.py: 2 rows x 8 blocks per SM and 4 rows x 6 are within 3 % of this)
+  const int grid = wave_grid(M, rows_per_block, 3);
   const size_t smem = 2 * static_cast<size_t>(C) * sizeof(float);
-  if (a.res) bn_fwd_kernel<true, 4><<<grid, threads, smem, static_cast<cudaStream_t>(stream)>>>(a);
-  else bn_fwd_kernel<false, 4><<<grid, threads, smem, static_cast<cudaStream_t>(stream)>>>(a);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (a.res) bn_fwd_kernel<true, 4><<<grid, threads, smem, st>>>(a);
+  else bn_fwd_kernel<false, 4><<<grid, threads, smem, st>>>(a);
   return cudaGetLastError() == cudaSuccess ? 0 : -2;
 }
 
