@@ -69,9 +69,12 @@ __global__ void __launch_bounds__(256) bce_kernel(const float* __restrict__ x, c
 // ---- narrow 1x1 head: y[p, k] = sum_c x[p, c] * w[k, c] + b[k],  k < K <= 8, C % 8 == 0, C <= 512 ----
 constexpr int kHeadMaxK = 8;
 
+// KT: compile-time bound on K (1 for the UNet's single-class head).  Four pixels per thread in flight.
+template <int KT>
 __global__ void __launch_bounds__(256) head_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
                                                        const float* __restrict__ b, float* __restrict__ y, long long M,
                                                        int C, int K, long long ldx) {
+  constexpr int U = KT == 1 ? 4 : 2;
   extern __shared__ float sw[];  // [K][C]
   for (int i = threadIdx.x; i < K * C; i += blockDim.x) sw[i] = w[i];
   __syncthreads();
@@ -79,49 +82,68 @@ __global__ void __launch_bounds__(256) head_fwd_kernel(const __nv_bfloat16* __re
   const int sub = threadIdx.x & 7;
   const int lane = threadIdx.x & 31;
   const long long warp0 = ((blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x) >> 5) * 4;
-  for (long long p0 = warp0; p0 < M; p0 += (static_cast<long long>(gridDim.x) * blockDim.x) >> 3) {
+  const long long wstride = (static_cast<long long>(gridDim.x) * blockDim.x) >> 3;  // pixels per grid step
+  for (long long p0 = warp0; p0 < M; p0 += U * wstride) {
     // warp-uniform loop (the shuffles below need every lane); lanes past the end clamp to the last pixel
-    const long long pix_raw = p0 + (lane >> 3);
-    const bool pvalid = pix_raw < M;
-    const long long pix = pvalid ? pix_raw : M - 1;
-    float acc[kHeadMaxK];
+    long long pix[U];
+    bool pvalid[U];
+    float acc[U][KT];
 #pragma unroll
-    for (int k = 0; k < kHeadMaxK; ++k) acc[k] = 0.f;
+    for (int u = 0; u < U; ++u) {
+      const long long pix_raw = p0 + u * wstride + (lane >> 3);
+      pvalid[u] = pix_raw < M;
+      pix[u] = pvalid[u] ? pix_raw : M - 1;
+#pragma unroll
+      for (int k = 0; k < KT; ++k) acc[u][k] = 0.f;
+    }
     for (int c0 = sub * 8; c0 < C; c0 += 64) {
-      const uint4 v = *reinterpret_cast<const uint4*>(x + pix * ldx + c0);
-      const uint32_t vi[4] = {v.x, v.y, v.z, v.w};
-      float xv[8];
+      uint4 v[U];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        xv[2 * j] = bf16lo(vi[j]);
-        xv[2 * j + 1] = bf16hi(vi[j]);
-      }
+      for (int u = 0; u < U; ++u) v[u] = *reinterpret_cast<const uint4*>(x + pix[u] * ldx + c0);
 #pragma unroll
-      for (int k = 0; k < kHeadMaxK; ++k) {
-        if (k < K) {
+      for (int u = 0; u < U; ++u) {
+        const uint32_t vi[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+        float xv[8];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) acc[k] = fmaf(xv[j], sw[k * C + c0 + j], acc[k]);
+        for (int j = 0; j < 4; ++j) {
+          xv[2 * j] = bf16lo(vi[j]);
+          xv[2 * j + 1] = bf16hi(vi[j]);
+        }
+#pragma unroll
+        for (int k = 0; k < KT; ++k) {
+          if (k < K) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[u][k] = fmaf(xv[j], sw[k * C + c0 + j], acc[u][k]);
+          }
         }
       }
     }
 #pragma unroll
-    for (int k = 0; k < kHeadMaxK; ++k) {
-      if (k < K) {
-        float v = acc[k];
-        v += __shfl_xor_sync(0xffffffffu, v, 1);
-        v += __shfl_xor_sync(0xffffffffu, v, 2);
-        v += __shfl_xor_sync(0xffffffffu, v, 4);
-        if (sub == 0 && pvalid) y[pix * K + k] = v + (b ? b[k] : 0.f);
+    for (int u = 0; u < U; ++u)
+#pragma unroll
+      for (int k = 0; k < KT; ++k) {
+        if (k < K) {
+          float v = acc[u][k];
+          v += __shfl_xor_sync(0xffffffffu, v, 1);
+          v += __shfl_xor_sync(0xffffffffu, v, 2);
+          v += __shfl_xor_sync(0xffffffffu, v, 4);
+          if (sub == 0 && pvalid[u]) y[pix[u] * K + k] = v + (b ? b[k] : 0.f);
+        }
       }
-    }
   }
 }
 
 // dx[p, c] = sum_k dy[p, k] * w[k, c]  (bf16 out);  dw[k, c] += sum_p dy[p,k] x[p,c];  db[k] += sum_p dy[p,k]
+// KT: compile-time bound on K (1 for the UNet's single-class head: the weights of the thread's 8 channels then live in
+// registers and the loop is one load, 16 FMAs and one store per pixel; kHeadMaxK otherwise).  Four pixels per
+// iteration with every load issued up front: the kernel is a pure stream (1.07 GB for the 512x512 UNet) and one or
+// two 16-byte loads per thread left the memory system idle (1.9 TB/s).
+template <int KT>
 __global__ void __launch_bounds__(256) head_bwd_kernel(const float* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                                                        const float* __restrict__ w, __nv_bfloat16* __restrict__ dx,
                                                        float* __restrict__ dw, float* __restrict__ db, long long M,
                                                        int C, int K, long long ldx, long long ld_dx) {
+  constexpr int U = KT == 1 ? 4 : 2;
   extern __shared__ float sm[];  // w[K][C], then accumulators dw[K][C] + db[K]
   float* sw = sm;
   float* sdw = sm + K * C;
@@ -135,33 +157,36 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(const float* __restrict__
   const int vecC = C >> 3;
   const int cv = threadIdx.x % vecC;  // host picks blockDim multiple of vecC
   const int slab = threadIdx.x / vecC, nslab = blockDim.x / vecC;
-  float adw[kHeadMaxK][8];
-  float adb[kHeadMaxK];
+  float adw[KT][8];
+  float adb[KT];
+  float wr[KT == 1 ? 8 : 1];  // K = 1: this thread's weights
 #pragma unroll
-  for (int k = 0; k < kHeadMaxK; ++k) {
+  for (int k = 0; k < KT; ++k) {
     adb[k] = 0.f;
 #pragma unroll
     for (int j = 0; j < 8; ++j) adw[k][j] = 0.f;
   }
-  // two pixels per iteration with both loads issued up front (the kernel is a pure stream: one 16-byte load per
-  // pixel and thread left the memory system idle)
-  const long long stride = static_cast<long long>(gridDim.x) * nslab;
-  for (long long pix0 = blockIdx.x * static_cast<long long>(nslab) + slab; pix0 < M; pix0 += 2 * stride) {
-    const long long pix1 = pix0 + stride;
-    const bool has1 = pix1 < M;
-    uint4 vv[2];
-    float dd[2][kHeadMaxK];
-    vv[0] = *reinterpret_cast<const uint4*>(x + pix0 * ldx + cv * 8);
-    vv[1] = has1 ? *reinterpret_cast<const uint4*>(x + pix1 * ldx + cv * 8) : make_uint4(0, 0, 0, 0);
+  if (KT == 1) {
 #pragma unroll
-    for (int k = 0; k < kHeadMaxK; ++k) {
-      dd[0][k] = k < K ? dy[pix0 * K + k] : 0.f;
-      dd[1][k] = (k < K && has1) ? dy[pix1 * K + k] : 0.f;
+    for (int j = 0; j < 8; ++j) wr[j] = sw[cv * 8 + j];
+  }
+  const long long stride = static_cast<long long>(gridDim.x) * nslab;
+  for (long long pix0 = blockIdx.x * static_cast<long long>(nslab) + slab; pix0 < M; pix0 += U * stride) {
+    uint4 vv[U];
+    float dd[U][KT];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long pix = pix0 + u * stride;
+      if (pix < M) {
+        vv[u] = *reinterpret_cast<const uint4*>(x + pix * ldx + cv * 8);
+#pragma unroll
+        for (int k = 0; k < KT; ++k) dd[u][k] = k < K ? dy[pix * K + k] : 0.f;
+      }
     }
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
-      if (u == 1 && !has1) break;
-      const long long pix = u == 0 ? pix0 : pix1;
+    for (int u = 0; u < U; ++u) {
+      const long long pix = pix0 + u * stride;
+      if (pix >= M) break;
       const uint32_t vi[4] = {vv[u].x, vv[u].y, vv[u].z, vv[u].w};
       float xv[8], g[8];
 #pragma unroll
@@ -172,13 +197,13 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(const float* __restrict__
 #pragma unroll
       for (int j = 0; j < 8; ++j) g[j] = 0.f;
 #pragma unroll
-      for (int k = 0; k < kHeadMaxK; ++k) {
+      for (int k = 0; k < KT; ++k) {
         if (k < K) {
           const float d = dd[u][k];
           if (cv == 0) adb[k] += d;
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            g[j] = fmaf(d, sw[k * C + cv * 8 + j], g[j]);
+            g[j] = fmaf(d, KT == 1 ? wr[KT == 1 ? j : 0] : sw[k * C + cv * 8 + j], g[j]);
             adw[k][j] = fmaf(d, xv[j], adw[k][j]);
           }
         }
@@ -192,7 +217,7 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(const float* __restrict__
     }
   }
 #pragma unroll
-  for (int k = 0; k < kHeadMaxK; ++k) {
+  for (int k = 0; k < KT; ++k) {
     if (k < K) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) atomicAdd(&sdw[k * C + cv * 8 + j], adw[k][j]);
@@ -231,7 +256,8 @@ extern "C" int dmpi_head_forward(const void* x, const float* w, const float* b, 
   if (K < 1 || K > kHeadMaxK || C % 64 != 0) return -1;
   long long blocks = (M * 8 + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
-  head_fwd_kernel<<<static_cast<int>(blocks), 256, K * C * sizeof(float), static_cast<cudaStream_t>(stream)>>>(
+  auto kern = K == 1 ? head_fwd_kernel<1> : head_fwd_kernel<kHeadMaxK>;
+  kern<<<static_cast<int>(blocks), 256, K * C * sizeof(float), static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(x), w, b, y, M, C, K, ldx);
   return cudaGetLastError() == cudaSuccess ? 0 : -2;
 }
@@ -246,7 +272,8 @@ extern "C" int dmpi_head_backward(const float* dy, const void* x, const float* w
   if (blocks > 148 * 8) blocks = 148 * 8;
   if (blocks < 1) blocks = 1;
   const size_t smem = (2 * K * C + K) * sizeof(float);
-  head_bwd_kernel<<<static_cast<int>(blocks), threads, smem, static_cast<cudaStream_t>(stream)>>>(
+  auto kern = K == 1 ? head_bwd_kernel<1> : head_bwd_kernel<kHeadMaxK>;
+  kern<<<static_cast<int>(blocks), threads, smem, static_cast<cudaStream_t>(stream)>>>(
       dy, static_cast<const __nv_bfloat16*>(x), w, static_cast<__nv_bfloat16*>(dx), dw, db, M, C, K, ldx, ld_dx);
   return cudaGetLastError() == cudaSuccess ? 0 : -2;
 }

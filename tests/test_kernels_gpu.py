@@ -185,12 +185,12 @@ def test_losses():
     _close(d, x.grad, 1e-4, "bce_grad")
 
 
-@pytest.mark.parametrize("kc", [1, 2])
-def test_head(kc):
+@pytest.mark.parametrize("kc,shape", [(1, (2, 32, 32)), (2, (2, 32, 32)), (1, (5, 157, 129)), (3, (3, 37, 29))])
+def test_head(kc, shape):
     from deeplearning_mpi_b200.ops import kernels as K
 
     torch.manual_seed(3)
-    x = torch.randn(2, 32, 32, 64, device=DEV).bfloat16()
+    x = torch.randn(*shape, 64, device=DEV).bfloat16()
     w = torch.randn(kc, 64, device=DEV) * 0.1
     b = torch.randn(kc, device=DEV)
     y = K.head_forward(x, w, b)
