@@ -407,17 +407,25 @@ __global__ void __launch_bounds__(kBnThreads) bn_stats_kernel(const __nv_bfloat1
 #pragma unroll
   for (int j = 0; j < 8; ++j) s1[j] = s2[j] = 0.f;
   if (ty < rows_per_block) {
-    for (long long row = blockIdx.x * static_cast<long long>(rows_per_block) + ty; row < M;
-         row += static_cast<long long>(gridDim.x) * rows_per_block) {
-      const uint4 v = *reinterpret_cast<const uint4*>(y + row * ld + c0);
-      const uint32_t vi[4] = {v.x, v.y, v.z, v.w};
+    constexpr int U = 4;  // rows in flight per thread (a read-only stream: see bn_bwd_reduce_kernel)
+    const long long stride = static_cast<long long>(gridDim.x) * rows_per_block;
+    for (long long row0 = blockIdx.x * static_cast<long long>(rows_per_block) + ty; row0 < M; row0 += U * stride) {
+      uint4 v[U];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float a0 = bf16lo(vi[j]), a1 = bf16hi(vi[j]);
-        s1[2 * j] += a0;
-        s1[2 * j + 1] += a1;
-        s2[2 * j] = fmaf(a0, a0, s2[2 * j]);
-        s2[2 * j + 1] = fmaf(a1, a1, s2[2 * j + 1]);
+      for (int u = 0; u < U; ++u)
+        if (row0 + u * stride < M) v[u] = *reinterpret_cast<const uint4*>(y + (row0 + u * stride) * ld + c0);
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (row0 + u * stride >= M) break;
+        const uint32_t vi[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float a0 = bf16lo(vi[j]), a1 = bf16hi(vi[j]);
+          s1[2 * j] += a0;
+          s1[2 * j + 1] += a1;
+          s2[2 * j] = fmaf(a0, a0, s2[2 * j]);
+          s2[2 * j + 1] = fmaf(a1, a1, s2[2 * j + 1]);
+        }
       }
     }
   }
@@ -671,10 +679,7 @@ extern "C" int dmpi_bn_stats(const void* y, long long M, int C, long long ld, fl
   if (vecC > threads) return -3;
   threads = (threads / vecC) * vecC;
   const int rows_per_block = threads / vecC;
-  long long blocks = (M + rows_per_block * 8 - 1) / (rows_per_block * 8);
-  if (blocks > 148 * 8) blocks = 148 * 8;
-  if (blocks < 1) blocks = 1;
-  bn_stats_kernel<<<static_cast<int>(blocks), threads, threads * 16 * sizeof(float), static_cast<cudaStream_t>(stream)>>>(
+  bn_stats_kernel<<<wave_grid(M, rows_per_block, 4), threads, threads * 16 * sizeof(float), static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(y), M, C, ld, sum, sqsum);
   return cudaGetLastError() == cudaSuccess ? 0 : -2;
 }
