@@ -32,6 +32,7 @@ import torch.nn as nn
 
 from .. import _native as N
 from ..utils.arena import ParamArena, _round_up, ensure_arena
+from ..utils.runtime import FaultInjector
 from . import dist as D
 
 _MIB = 1 << 20
@@ -48,6 +49,7 @@ class DistributedDataParallel(nn.Module):
         self.require_backward_grad_sync = True
         self._st = st
         self.world, self.rank = st.world, st.rank
+        self._fault = FaultInjector()  # DMPI_FAULT test hook; inactive unless the variable is set
         if find_unused_parameters:
             raise NotImplementedError("find_unused_parameters is not used by the reference and not supported")
         params = [p for p in module.parameters() if p.requires_grad]
@@ -263,6 +265,8 @@ class DistributedDataParallel(nn.Module):
 
     def forward(self, *inputs, **kwargs):
         if torch.is_grad_enabled() and self.training:
+            if self._fault.active and self.require_backward_grad_sync:
+                self._fault.tick(self.rank)
             self._sync_buffers()
             if self.require_backward_grad_sync:
                 self._arm()

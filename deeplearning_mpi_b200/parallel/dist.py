@@ -297,12 +297,15 @@ def _bootstrap_store(rank: int, world: int, timeout_s: float) -> TCPStore:
 
 
 def init_process_group(backend: str = "nccl", init_method: Optional[str] = None, rank: Optional[int] = None,
-                       world_size: Optional[int] = None, timeout_s: float = 300.0, **_ignored) -> None:
+                       world_size: Optional[int] = None, timeout_s: float = 300.0, timeout=None, **_ignored) -> None:
     """Same call shapes as the reference: ``init_process_group(backend)`` and
-    ``init_process_group(backend, rank=WORLD_RANK, world_size=WORLD_SIZE)``."""
+    ``init_process_group(backend, rank=WORLD_RANK, world_size=WORLD_SIZE)``.  ``timeout`` (a ``datetime.timedelta``, as
+    in torch.distributed) or ``timeout_s`` bounds the rendezvous and, on the gloo path, every collective."""
     global _state
     if _state is not None:
         raise RuntimeError("trying to initialize the default process group twice!")
+    if timeout is not None:
+        timeout_s = timeout.total_seconds() if hasattr(timeout, "total_seconds") else float(timeout)
     backend = (backend or "nccl").lower()
     rank = _env_int("RANK") if rank is None or rank < 0 else int(rank)
     world = _env_int("WORLD_SIZE") if world_size is None or world_size < 0 else int(world_size)
@@ -315,7 +318,10 @@ def init_process_group(backend: str = "nccl", init_method: Optional[str] = None,
         import torch.distributed as tdist
 
         if not tdist.is_initialized():
-            tdist.init_process_group("gloo", rank=rank, world_size=world)
+            import datetime
+
+            tdist.init_process_group("gloo", rank=rank, world_size=world,
+                                     timeout=datetime.timedelta(seconds=timeout_s))
         _state = GroupState("gloo", backend, rank, world, local_rank, torch.device("cpu"))
         return
 

@@ -67,6 +67,48 @@ class CudaTimer:
         return self.e0.elapsed_time(self.e1)
 
 
+class FaultInjector:
+    """Test hook: ``DMPI_FAULT="rank=1,step=2,kind=exit"`` makes rank 1 fail at its third
+    synchronising training forward.  kinds: ``exit`` (the process dies without cleanup, like a killed worker),
+    ``raise`` (a Python exception, which the trainers let propagate to a non-zero exit code), ``stall=<seconds>``
+    (the rank goes silent; peers must run into their collective timeout instead of hanging forever).
+    Parsed once per process; inactive (and free) when the variable is unset."""
+
+    def __init__(self, spec: Optional[str] = None):
+        spec = os.environ.get("DMPI_FAULT", "") if spec is None else spec
+        self.rank = self.step = -1
+        self.kind, self.stall_s = "", 0.0
+        for item in filter(None, (x.strip() for x in spec.split(","))):
+            k, _, v = item.partition("=")
+            if k == "rank":
+                self.rank = int(v)
+            elif k == "step":
+                self.step = int(v)
+            elif k == "kind":
+                self.kind = v
+            elif k == "stall":
+                self.kind, self.stall_s = "stall", float(v)
+            else:
+                raise ValueError(f"DMPI_FAULT: unknown field {item!r}")
+        if self.kind not in ("", "exit", "raise", "stall"):
+            raise ValueError(f"DMPI_FAULT: unknown kind {self.kind!r}")
+        self.active = self.kind != "" and self.rank >= 0 and self.step >= 0
+        self.count = 0
+
+    def tick(self, rank: int) -> None:
+        """Called once per synchronising training forward of the DDP wrapper."""
+        if not self.active:
+            return
+        step, self.count = self.count, self.count + 1
+        if rank != self.rank or step != self.step:
+            return
+        if self.kind == "exit":
+            os._exit(17)
+        if self.kind == "raise":
+            raise RuntimeError(f"DMPI_FAULT: injected failure on rank {rank} at step {step}")
+        time.sleep(self.stall_s)
+
+
 class nvtx_range:
     """NVTX range (shows up in nsys / ncu timelines); no-op without CUDA."""
 
