@@ -1,6 +1,6 @@
 """Per-layer timing of the tcgen05 conv kernels vs cuDNN (bf16, channels_last) on ResNet-50 shapes.
 Writes gpurun_out/conv_bench.txt.  CUDA-event timed, L2 flushed between iterations."""
-import os, sys, json
+import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch, torch.nn.functional as F
 from deeplearning_mpi_b200.ops import conv as C

@@ -1,6 +1,6 @@
 """Regenerates docs/sass/summary.txt: per-kernel counts of the Blackwell-specific SASS mnemonics in libdmpi_cuda.so.
 Runs on CPU (cuobjdump only):  python bench/sass_summary.py"""
-import collections, os, re, subprocess, sys
+import collections, os, re, subprocess
 
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 lib = os.path.join(root, "deeplearning_mpi_b200", "_lib", "libdmpi_cuda.so")

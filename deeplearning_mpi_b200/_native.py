@@ -9,7 +9,6 @@ fails to load we raise instead of silently falling back to eager PyTorch.
 from __future__ import annotations
 
 import ctypes as C
-import os
 from pathlib import Path
 
 _LIB_DIR = Path(__file__).resolve().parent / "_lib"

@@ -4,7 +4,6 @@ ref:pytorch/resnet/main.py:148, ref:pytorch/unet/train.py:255, ref:pytorch/hello
 from __future__ import annotations
 
 import ctypes as C
-import time
 from typing import List, Optional
 
 from .. import _native as N

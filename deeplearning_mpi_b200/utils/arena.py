@@ -16,7 +16,7 @@ ref:pytorch/resnet/main.py:139 / ref:pytorch/unet/train.py:216) but are stored p
 from __future__ import annotations
 
 import ctypes as C
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 from typing import Callable, Dict, List, Optional, Sequence, Tuple
 
 import numpy as np

@@ -1,6 +1,4 @@
 """Numerics of the non-GEMM sm_100a kernels against plain PyTorch fp32 references."""
-import ctypes as C
-
 import pytest
 import torch
 import torch.nn.functional as F
@@ -277,8 +275,6 @@ def test_layout():
 
 
 def test_transpose_table():
-    import numpy as np
-
     from deeplearning_mpi_b200.ops import kernels as K
     from deeplearning_mpi_b200.utils.arena import build_transpose_table
 
