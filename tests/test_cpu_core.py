@@ -214,3 +214,47 @@ def test_choose_box_and_dice_and_dataset(tmp_path):
     item = ds[0]
     assert item["image"].shape == (3, 10, 15) and item["mask"].shape == (10, 15)
     assert item["image"].max() <= 1.0 and set(item["mask"].unique().tolist()) <= {0.0, 1.0}
+
+
+def test_conv_planner_invariants():
+    """Host-side tile planning of the implicit GEMM (ops/conv.py) over every image size the models can produce: the
+    patch-mode tile must fit the 128 accumulator rows and the kernel's operand ring, and the N-tile / CTA-pair choice
+    must stay inside what igemm.cu instantiates (BN 64 / 128 / 256, pairs only for BN >= 128)."""
+    from deeplearning_mpi_b200.ops import conv as CV
+
+    for ow in list(range(1, 140)) + [160, 224, 256, 384, 512, 1000]:
+        for oh in (1, 2, 7, 14, 28, 56, 57, 112, 512):
+            t = CV.choose_patch_tile(ow, oh, 1)
+            if t is None:
+                assert ow < 8
+                continue
+            tw, th, eff = t
+            pw = tw + 2
+            assert 8 <= tw <= 128 and 1 <= th <= oh and (th - 1) * pw + tw <= 128
+            tiles = -(-ow // tw) * -(-oh // th)
+            assert abs(eff - ow * oh / (tiles * 128.0)) < 1e-9 and 0 < eff <= 1.0
+    for n_out in (8, 64, 65, 128, 192, 256, 512, 1000, 2048):
+        for ktot in (64, 128, 256, 576, 4608):
+            bn = CV._pick_bn(n_out, ktot)
+            assert bn in (64, 128, 256) and (bn == 64) == (n_out <= 64)
+            assert bn != 256 or n_out % 256 == 0
+            cg = CV._pick_cg(bn, ktot)
+            assert cg in (1, 2) and (cg == 1 or bn >= 128)
+    ring = {(64, 1): 192, (128, 1): 160, (256, 1): 144, (128, 2): 144, (256, 2): 160}  # KiB, igemm.cu IgemmCfg
+    for c_in in (64, 128, 256):
+        for n_out in (64, 128, 256):
+            for ow, oh in ((56, 56), (28, 28), (128, 128), (256, 256), (512, 512), (20, 12)):
+                bn = CV._pick_bn(n_out, 9 * c_in)
+                cg = CV._pick_cg(bn, 9 * c_in)
+                t = CV._patch_ok(3, 3, 1, 1, c_in, ow, oh, n_out, cg)
+                if t is None:
+                    continue
+                pw = t[0] + 2
+                rows = max(128 + 2 * pw + 2, pw * (t[1] + 2))
+                patch_bytes = -(-rows * 128 // 1024) * 1024
+                tap_bytes = bn * 64 * 2 // cg
+                assert 2 * patch_bytes + 2 * tap_bytes <= ring[(bn, cg)] * 1024
+                assert t[2] >= CV._PATCH_MIN_EFF
+    # everything that is not a stride-1 pad-1 3x3 on whole 64-channel blocks stays on the per-tap path
+    assert CV._patch_ok(1, 1, 1, 0, 64, 56, 56) is None and CV._patch_ok(3, 3, 2, 1, 64, 56, 56) is None
+    assert CV._patch_ok(3, 3, 1, 1, 32, 56, 56) is None
