@@ -258,3 +258,27 @@ def test_conv_planner_invariants():
     # everything that is not a stride-1 pad-1 3x3 on whole 64-channel blocks stays on the per-tap path
     assert CV._patch_ok(1, 1, 1, 0, 64, 56, 56) is None and CV._patch_ok(3, 3, 2, 1, 64, 56, 56) is None
     assert CV._patch_ok(3, 3, 1, 1, 32, 56, 56) is None
+
+
+def test_fault_injector_spec():
+    """DMPI_FAULT parsing (utils/runtime.py::FaultInjector): inactive by default, fires once on the named rank / step,
+    rejects unknown fields."""
+    from deeplearning_mpi_b200.utils.runtime import FaultInjector
+
+    assert not FaultInjector("").active
+    f = FaultInjector("rank=1,step=2,kind=raise")
+    assert f.active and (f.rank, f.step, f.kind) == (1, 2, "raise")
+    for _ in range(5):
+        f.tick(0)  # another rank: counts steps, never fires
+    f = FaultInjector("rank=1,step=2,kind=raise")
+    f.tick(1), f.tick(1)
+    with pytest.raises(RuntimeError, match="injected failure on rank 1 at step 2"):
+        f.tick(1)
+    f.tick(1)  # later steps run normally
+    s = FaultInjector("rank=0,step=0,stall=0.01")
+    assert s.kind == "stall" and s.stall_s == 0.01
+    s.tick(0)
+    with pytest.raises(ValueError):
+        FaultInjector("rank=1,when=now")
+    with pytest.raises(ValueError):
+        FaultInjector("rank=1,step=1,kind=explode")
