@@ -75,20 +75,20 @@ def test_unet_example_gloo_world2(tmp_path):
     assert len(logs) >= 1 and "FINAL TRAINING RESULTS" in logs[0].read_text()
 
 
-@pytest.mark.parametrize("kind", ["exit", "raise", "stall=60"])
+@pytest.mark.parametrize("kind", ["exit", "raise", "stall=150"])
 def test_fault_injection_never_hangs(kind):
     """a rank that dies (exit), throws (raise) or goes silent (stall) in the middle of training must turn
     into a non-zero exit code of the job within the collective timeout, never into a hang or a clean exit."""
     import time
 
-    env = dict(os.environ, OMP_NUM_THREADS="2", FAULT_TEST_TIMEOUT_S="20",
+    env = dict(os.environ, OMP_NUM_THREADS="2", FAULT_TEST_TIMEOUT_S="45",
                DMPI_FAULT=f"rank=1,step=2,{kind if kind.startswith('stall') else 'kind=' + kind}")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
            "127.0.0.1", "--master-port", str(_free_port()), os.path.join(ROOT, "tests", "mp", "fault_worker.py")]
     t0 = time.time()
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=ROOT, env=env)
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=400, cwd=ROOT, env=env)
     out = r.stdout + r.stderr
     assert r.returncode != 0, out[-3000:]
     assert "FAULT_WORKER_DONE rank=0" not in out, out[-3000:]
     assert "FAULT_WORKER rank=0 finished step 1" in out and "FAULT_WORKER rank=0 finished step 2" not in out, out[-3000:]
-    assert time.time() - t0 < 200
+    assert time.time() - t0 < 300  # the collective timeout of the survivors is 45 s
