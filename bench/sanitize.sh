@@ -1,17 +1,22 @@
 #!/usr/bin/env bash
-# compute-sanitizer passes over the single-GPU kernel tests.  Run on a GPU box from the repository root:
-#   gpurun --timeout 1500 -- 'bash bench/sanitize.sh > gpurun_out/sanitize.log 2>&1'
-# memcheck covers every kernel test; racecheck / synccheck (10-50x slower) cover the shared-memory heavy kernels only.
-# The multi-rank P2P kernels are excluded: the tools serialise kernels, and ranks that wait on each other need to run
-# concurrently (their single-launch emulation in tests/test_kernels_gpu.py IS covered).
+# compute-sanitizer over the single-GPU kernel tests, ONE tool per invocation (and per gpurun call):
+#   gpurun --timeout 1200 -- 'bash bench/sanitize.sh memcheck  > gpurun_out/sanitize_memcheck.log 2>&1'
+#   gpurun --timeout 1200 -- 'bash bench/sanitize.sh racecheck > gpurun_out/sanitize_racecheck.log 2>&1'
+# memcheck covers every kernel test; racecheck / synccheck / initcheck (10-50x slower) cover the shared-memory heavy
+# kernels only.  The multi-rank P2P kernels are excluded: the tools serialise kernels, and ranks that wait on each other
+# need to run concurrently (their single-launch emulation in tests/test_kernels_gpu.py IS covered).
+# If a bounded mbarrier wait trips under the tool's slow-down, rebuild first with
+#   DMPI_NVCC_EXTRA="-DDMPI_MBAR_TIMEOUT_NS=0" python build.py --force      (csrc/common/ptx.cuh)
 set -u
+tool="${1:-memcheck}"
 CS=/usr/local/cuda/bin/compute-sanitizer
-PY="python -m pytest -x -q -m gpu"
+PY="python -m pytest -x -q -m gpu -p no:cacheprovider"
+export DMPI_COMM_TIMEOUT_S=0
 rc=0
-$CS --tool memcheck --error-exitcode 9 --launch-timeout 120 $PY tests/test_kernels_gpu.py tests/test_conv_gpu.py || rc=$?
-echo "memcheck rc=$rc"
-for tool in racecheck synccheck; do
-  $CS --tool $tool --error-exitcode 9 $PY tests/test_kernels_gpu.py -k "bn or maxpool or head or allreduce" || rc=$?
-  echo "$tool rc=$rc"
-done
+if [ "$tool" = "memcheck" ]; then
+  $CS --tool memcheck --error-exitcode 9 --launch-timeout 120 $PY tests/test_kernels_gpu.py tests/test_conv_gpu.py || rc=$?
+else
+  $CS --tool "$tool" --error-exitcode 9 $PY tests/test_kernels_gpu.py -k "bn or maxpool or head or allreduce" || rc=$?
+fi
+echo "$tool rc=$rc"
 exit $rc

@@ -30,6 +30,7 @@ NVCC_FLAGS = [
     "-ccbin", CXX, "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC", "-Xptxas", "-v",
 ]
+NVCC_FLAGS += os.environ.get("DMPI_NVCC_EXTRA", "").split()  # e.g. -DDMPI_ABLATE (bench builds only)
 CXX_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-Wall", "-pthread"]
 
 CUDA_SOURCES = sorted(str(p.relative_to(ROOT)) for p in (ROOT / "csrc").rglob("*.cu"))

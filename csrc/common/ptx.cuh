@@ -52,8 +52,14 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return done != 0;
 }
-// Bounded wait: a protocol bug traps (the launch fails with an error) after ~4 s instead of
-// hanging the GPU.  The check costs one globaltimer read per 4096 failed polls.
+// Bounded wait: a protocol bug traps (the launch fails with an error) instead of hanging the GPU.  The bound is
+// DMPI_MBAR_TIMEOUT_NS at compile time (default 4 s; 0 removes the check).  Builds that run under compute-sanitizer, a
+// debugger or on a time-sliced GPU — where a healthy kernel can legitimately sit in a wait for seconds of wall clock —
+// use DMPI_NVCC_EXTRA="-DDMPI_MBAR_TIMEOUT_NS=0" (bench/sanitize.sh does).  The check costs one globaltimer read per
+// 4096 failed polls.
+#ifndef DMPI_MBAR_TIMEOUT_NS
+#define DMPI_MBAR_TIMEOUT_NS 4000000000ull
+#endif
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   uint64_t t0 = 0;
@@ -62,7 +68,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     if ((++spins & 4095u) == 0) {
       uint64_t now = globaltimer_ns();
       if (t0 == 0) t0 = now;
-      else if (now - t0 > 4000000000ull) __trap();
+      else if (DMPI_MBAR_TIMEOUT_NS != 0ull && now - t0 > DMPI_MBAR_TIMEOUT_NS) __trap();
     }
   }
 }
@@ -70,7 +76,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 // Pure polling variant for the single-thread roles (TMA producer, MMA issuer): mbarrier.try_wait may park the thread
 // for a system-defined time slice and is not woken promptly by arrivals that come from the peer CTA of a pair
 // (measured: ~5 us per pipeline round trip with try_wait vs ~1 us when polling), so latency-critical single threads
-// use test_wait.  Same ~4 s trap bound.
+// use test_wait.  Same trap bound.
 __device__ __forceinline__ bool mbar_test_wait(uint64_t* bar, uint32_t parity) {
   uint32_t done;
   asm volatile(
@@ -88,7 +94,7 @@ __device__ __forceinline__ void mbar_wait_spin(uint64_t* bar, uint32_t parity) {
     if ((++spins & 0xFFFFu) == 0) {
       uint64_t now = globaltimer_ns();
       if (t0 == 0) t0 = now;
-      else if (now - t0 > 4000000000ull) __trap();
+      else if (DMPI_MBAR_TIMEOUT_NS != 0ull && now - t0 > DMPI_MBAR_TIMEOUT_NS) __trap();
     }
   }
 }

@@ -17,13 +17,16 @@
 // Synchronisation: per-block monotonically increasing epochs on a signal pad; flag stores are
 // st.release.sys after a CTA barrier, waits are ld.acquire.sys.  Block b of rank r only ever
 // synchronises with block b of the peers, so no grid-wide barrier is required.  Waits are bounded
-// (trap after ~20 s) so a dead peer cannot hang the GPU forever.
+// (trap after DMPI_COMM_TIMEOUT_S seconds, default 600, 0 = never) so a dead peer cannot hang the GPU forever
+//  while a peer that is legitimately late — rank 0 alone evaluating and checkpointing between epochs,
+// ref:pytorch/resnet/main.py:136-139 — is simply waited for.
 //
 // Single-GPU emulation (tests): blockIdx.y selects a virtual rank; all W "ranks" are buffers of one device
 // and run inside ONE launch, as required when ranks must wait on each other on a single GPU.
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "../../common/ptx.cuh"
 #include "../../../include/dmpi_comm.h"
@@ -31,6 +34,9 @@
 namespace dmpi {
 
 constexpr int kCommThreads = 512;
+constexpr int kInFlight = 4;  // 16-byte vectors per thread and peer issued before the first use (NVLink latency ~2 us)
+
+__device__ unsigned long long g_comm_timeout_ns = 600ull * 1000000000ull;  // 0: wait forever
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -72,7 +78,7 @@ __device__ __forceinline__ void spin_until_ge(const uint32_t* flag, uint32_t tar
     if ((++spins & 1023u) == 0) {
       const uint64_t now = globaltimer_ns();
       if (t0 == 0) t0 = now;
-      else if (now - t0 > 20000000000ull) __trap();
+      else if (g_comm_timeout_ns != 0ull && now - t0 > g_comm_timeout_ns) __trap();
     }
   }
 }
@@ -89,9 +95,13 @@ __device__ __forceinline__ void block_barrier(const dmpi_comm_ptrs& p, int rank,
 }
 
 // ------------------------------------------------------------------------------------------------ all-reduce
-template <bool kBf16>
+// MAXW bounds the world size at compile time so that the loads of kInFlightBytes / MAXW vectors per peer can be held
+// in registers at once: a peer load takes ~2 us over NVLink, and with one vector per thread in flight (the first
+// version of this kernel) a W = 2 launch of 32 blocks kept only 0.5 MB on the wire — latency-bound at 0.8x NCCL.
+template <bool kBf16, int MAXW>
 __global__ void __launch_bounds__(kCommThreads) allreduce_twoshot_kernel(const dmpi_comm_ptrs p, long long off_bytes,
                                                                          long long nvec, float scale) {
+  constexpr int U = 16 / MAXW;  // vectors per thread and peer in flight: 8 (W <= 2), 4 (W <= 4), 2 (W <= 8)
   const int rank = p.rank_base + blockIdx.y;
   const int blk = blockIdx.x;
   const int W = p.world;
@@ -99,52 +109,62 @@ __global__ void __launch_bounds__(kCommThreads) allreduce_twoshot_kernel(const d
   block_barrier(p, rank, blk, e + 1);
 
   const long long v_begin = nvec * rank / W, v_end = nvec * (rank + 1) / W;
-  uint4* bufs[DMPI_MAX_RANKS];
+  uint4* bufs[MAXW];
 #pragma unroll
-  for (int q = 0; q < DMPI_MAX_RANKS; ++q)
-    bufs[q] = reinterpret_cast<uint4*>(static_cast<char*>(p.data[q < W ? q : 0]) + off_bytes);
+  for (int q = 0; q < MAXW; ++q) bufs[q] = reinterpret_cast<uint4*>(static_cast<char*>(p.data[q < W ? q : 0]) + off_bytes);
 
-  for (long long i = v_begin + static_cast<long long>(blk) * blockDim.x + threadIdx.x; i < v_end;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    uint4 in[DMPI_MAX_RANKS];
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i0 = v_begin + static_cast<long long>(blk) * blockDim.x + threadIdx.x; i0 < v_end; i0 += stride * U) {
+    uint4 in[U][MAXW];
 #pragma unroll
-    for (int q = 0; q < DMPI_MAX_RANKS; ++q)
-      if (q < W) in[q] = ld_peer_u4(bufs[q] + i);
-    uint4 out;
-    if (kBf16) {
-      float a[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * stride;
+      if (i < v_end) {
 #pragma unroll
-      for (int q = 0; q < DMPI_MAX_RANKS; ++q)
-        if (q < W) {
-          const uint32_t w4[4] = {in[q].x, in[q].y, in[q].z, in[q].w};
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            a[2 * j] += bf16lo(w4[j]);
-            a[2 * j + 1] += bf16hi(w4[j]);
-          }
-        }
-      out.x = pack_bf16x2(a[0] * scale, a[1] * scale);
-      out.y = pack_bf16x2(a[2] * scale, a[3] * scale);
-      out.z = pack_bf16x2(a[4] * scale, a[5] * scale);
-      out.w = pack_bf16x2(a[6] * scale, a[7] * scale);
-    } else {
-      float a[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-      for (int q = 0; q < DMPI_MAX_RANKS; ++q)
-        if (q < W) {
-          a[0] += __uint_as_float(in[q].x);
-          a[1] += __uint_as_float(in[q].y);
-          a[2] += __uint_as_float(in[q].z);
-          a[3] += __uint_as_float(in[q].w);
-        }
-      out.x = __float_as_uint(a[0] * scale);
-      out.y = __float_as_uint(a[1] * scale);
-      out.z = __float_as_uint(a[2] * scale);
-      out.w = __float_as_uint(a[3] * scale);
+        for (int q = 0; q < MAXW; ++q)
+          if (q < W) in[u][q] = ld_peer_u4(bufs[q] + i);
+      }
     }
 #pragma unroll
-    for (int q = 0; q < DMPI_MAX_RANKS; ++q)
-      if (q < W) st_peer_u4(bufs[q] + i, out);
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * stride;
+      if (i >= v_end) break;
+      uint4 out;
+      if (kBf16) {
+        float a[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int q = 0; q < MAXW; ++q)
+          if (q < W) {
+            const uint32_t w4[4] = {in[u][q].x, in[u][q].y, in[u][q].z, in[u][q].w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              a[2 * j] += bf16lo(w4[j]);
+              a[2 * j + 1] += bf16hi(w4[j]);
+            }
+          }
+        out.x = pack_bf16x2(a[0] * scale, a[1] * scale);
+        out.y = pack_bf16x2(a[2] * scale, a[3] * scale);
+        out.z = pack_bf16x2(a[4] * scale, a[5] * scale);
+        out.w = pack_bf16x2(a[6] * scale, a[7] * scale);
+      } else {
+        float a[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int q = 0; q < MAXW; ++q)
+          if (q < W) {  // fixed rank order: every rank ends with bit-identical sums
+            a[0] += __uint_as_float(in[u][q].x);
+            a[1] += __uint_as_float(in[u][q].y);
+            a[2] += __uint_as_float(in[u][q].z);
+            a[3] += __uint_as_float(in[u][q].w);
+          }
+        out.x = __float_as_uint(a[0] * scale);
+        out.y = __float_as_uint(a[1] * scale);
+        out.z = __float_as_uint(a[2] * scale);
+        out.w = __float_as_uint(a[3] * scale);
+      }
+#pragma unroll
+      for (int q = 0; q < MAXW; ++q)
+        if (q < W) st_peer_u4(bufs[q] + i, out);
+    }
   }
   __threadfence_system();
   block_barrier(p, rank, blk, e + 2);
@@ -160,7 +180,12 @@ __global__ void __launch_bounds__(kCommThreads) allreduce_oneshot_kernel(const d
   const int blk = blockIdx.x;
   const int W = p.world;
   const uint32_t e = p.epoch[rank][blk];
-  const int parity = e & 1u;
+  // Staging parity comes from a counter of one-shot launches, identical in every block and on every rank (launches
+  // on an arena are stream-ordered), NOT from the per-block epoch: blocks that sat out a smaller earlier call would
+  // otherwise disagree with their neighbours about which half a given element was staged in, and a fast rank's next
+  // push could land in the half a slower peer is still reducing.
+  const uint32_t calls = p.epoch[rank][DMPI_EPOCH_ONESHOT_CALLS];
+  const int parity = calls & 1u;
   float4* mine = reinterpret_cast<float4*>(static_cast<char*>(p.data[rank]) + off_bytes);
   // staging layout per rank: [parity][source rank][slot_bytes]
   const long long slot_off = (static_cast<long long>(parity) * DMPI_MAX_RANKS + rank) * slot_bytes;
@@ -215,7 +240,15 @@ __global__ void __launch_bounds__(kCommThreads) allreduce_oneshot_kernel(const d
       }
     mine[i] = make_float4(a[0] * scale, a[1] * scale, a[2] * scale, a[3] * scale);
   }
-  if (threadIdx.x == 0) p.epoch[rank][blk] = e + 1;
+  if (threadIdx.x == 0) {
+    p.epoch[rank][blk] = e + 1;
+    // the block that finishes last advances the call counter (a block that has not started yet must still read the
+    // old value), and re-arms the ticket for the next launch
+    if (atomicAdd(&p.epoch[rank][DMPI_EPOCH_ONESHOT_DONE], 1u) == gridDim.x - 1) {
+      p.epoch[rank][DMPI_EPOCH_ONESHOT_DONE] = 0u;
+      p.epoch[rank][DMPI_EPOCH_ONESHOT_CALLS] = calls + 1;
+    }
+  }
 }
 
 // NVLS: the reduction happens inside the NVSwitch.  `mc_data` is the multicast mapping of the data region; a
@@ -231,31 +264,53 @@ __global__ void __launch_bounds__(kCommThreads) allreduce_nvls_kernel(const dmpi
   block_barrier(p, rank, blk, e + 1);
   char* mc = static_cast<char*>(p.mc_data) + off_bytes;
   const long long v_begin = nvec * rank / W, v_end = nvec * (rank + 1) / W;
-  for (long long i = v_begin + static_cast<long long>(blk) * blockDim.x + threadIdx.x; i < v_end;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    char* addr = mc + i * 16;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  // kInFlight in-switch reductions per thread are issued before the first result is used (a multimem.ld_reduce is a
+  // round trip through the NVSwitch, ~3 us)
+  for (long long i0 = v_begin + static_cast<long long>(blk) * blockDim.x + threadIdx.x; i0 < v_end;
+       i0 += stride * kInFlight) {
     if (kBf16) {
-      uint32_t a, b, c, d;
-      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
-                   : "=r"(a), "=r"(b), "=r"(c), "=r"(d)
-                   : "l"(addr)
-                   : "memory");
-      a = pack_bf16x2(bf16lo(a) * scale, bf16hi(a) * scale);
-      b = pack_bf16x2(bf16lo(b) * scale, bf16hi(b) * scale);
-      c = pack_bf16x2(bf16lo(c) * scale, bf16hi(c) * scale);
-      d = pack_bf16x2(bf16lo(d) * scale, bf16hi(d) * scale);
-      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(__uint_as_float(a)),
-                   "f"(__uint_as_float(b)), "f"(__uint_as_float(c)), "f"(__uint_as_float(d))
-                   : "memory");
+      uint32_t r[kInFlight][4];
+#pragma unroll
+      for (int u = 0; u < kInFlight; ++u) {
+        const long long i = i0 + u * stride;
+        if (i < v_end)
+          asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+                       : "=r"(r[u][0]), "=r"(r[u][1]), "=r"(r[u][2]), "=r"(r[u][3])
+                       : "l"(mc + i * 16)
+                       : "memory");
+      }
+#pragma unroll
+      for (int u = 0; u < kInFlight; ++u) {
+        const long long i = i0 + u * stride;
+        if (i >= v_end) break;
+        uint32_t o[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) o[j] = pack_bf16x2(bf16lo(r[u][j]) * scale, bf16hi(r[u][j]) * scale);
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc + i * 16),
+                     "f"(__uint_as_float(o[0])), "f"(__uint_as_float(o[1])), "f"(__uint_as_float(o[2])),
+                     "f"(__uint_as_float(o[3]))
+                     : "memory");
+      }
     } else {
-      float a, b, c, d;
-      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
-                   : "=f"(a), "=f"(b), "=f"(c), "=f"(d)
-                   : "l"(addr)
-                   : "memory");
-      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a * scale),
-                   "f"(b * scale), "f"(c * scale), "f"(d * scale)
-                   : "memory");
+      float r[kInFlight][4];
+#pragma unroll
+      for (int u = 0; u < kInFlight; ++u) {
+        const long long i = i0 + u * stride;
+        if (i < v_end)
+          asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                       : "=f"(r[u][0]), "=f"(r[u][1]), "=f"(r[u][2]), "=f"(r[u][3])
+                       : "l"(mc + i * 16)
+                       : "memory");
+      }
+#pragma unroll
+      for (int u = 0; u < kInFlight; ++u) {
+        const long long i = i0 + u * stride;
+        if (i >= v_end) break;
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc + i * 16),
+                     "f"(r[u][0] * scale), "f"(r[u][1] * scale), "f"(r[u][2] * scale), "f"(r[u][3] * scale)
+                     : "memory");
+      }
     }
   }
   __threadfence_system();
@@ -333,6 +388,21 @@ __global__ void __launch_bounds__(kCommThreads) sendrecv_emulated_kernel(const u
 
 using namespace dmpi;
 
+// DMPI_COMM_TIMEOUT_S is applied once, by the first collective launched in this process (outside stream capture:
+// every captured step is preceded by eager warm-up steps).
+static void apply_timeout_env() {
+  static const bool once = [] {
+    if (const char* e = getenv("DMPI_COMM_TIMEOUT_S")) dmpi_comm_set_timeout(atof(e));
+    return true;
+  }();
+  (void)once;
+}
+
+extern "C" int dmpi_comm_set_timeout(double seconds) {
+  const unsigned long long ns = seconds <= 0.0 ? 0ull : static_cast<unsigned long long>(seconds * 1e9);
+  return cudaMemcpyToSymbol(g_comm_timeout_ns, &ns, sizeof(ns)) == cudaSuccess ? 0 : -1;
+}
+
 static int clamp_blocks(int nblocks, long long nvec) {
   if (nblocks < 1) nblocks = 1;
   if (nblocks > DMPI_MAX_COMM_BLOCKS) nblocks = DMPI_MAX_COMM_BLOCKS;
@@ -349,8 +419,17 @@ extern "C" int dmpi_allreduce_twoshot(const dmpi_comm_ptrs* ptrs, long long off_
   const int nb = clamp_blocks(nblocks, (nvec + ptrs->world - 1) / ptrs->world);
   dim3 grid(nb, emulate_ranks > 0 ? emulate_ranks : 1);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  if (dtype == DMPI_BF16) allreduce_twoshot_kernel<true><<<grid, kCommThreads, 0, s>>>(*ptrs, off_bytes, nvec, scale);
-  else allreduce_twoshot_kernel<false><<<grid, kCommThreads, 0, s>>>(*ptrs, off_bytes, nvec, scale);
+  apply_timeout_env();
+  const bool bf = dtype == DMPI_BF16;
+#define DMPI_TWOSHOT(MAXW)                                                                                  \
+  do {                                                                                                      \
+    if (bf) allreduce_twoshot_kernel<true, MAXW><<<grid, kCommThreads, 0, s>>>(*ptrs, off_bytes, nvec, scale); \
+    else allreduce_twoshot_kernel<false, MAXW><<<grid, kCommThreads, 0, s>>>(*ptrs, off_bytes, nvec, scale);   \
+  } while (0)
+  if (ptrs->world <= 2) DMPI_TWOSHOT(2);
+  else if (ptrs->world <= 4) DMPI_TWOSHOT(4);
+  else DMPI_TWOSHOT(8);
+#undef DMPI_TWOSHOT
   return cudaGetLastError() == cudaSuccess ? 0 : -2;
 }
 
@@ -358,6 +437,7 @@ extern "C" int dmpi_allreduce_nvls(const dmpi_comm_ptrs* ptrs, long long off_byt
                                    int nblocks, void* stream) {
   if (nbytes % 16 || off_bytes % 16) return -1;
   if (!ptrs->mc_data) return -4;  // no multicast mapping on this host
+  apply_timeout_env();
   const long long nvec = nbytes / 16;
   const int nb = clamp_blocks(nblocks, (nvec + ptrs->world - 1) / ptrs->world);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -371,6 +451,7 @@ extern "C" int dmpi_allreduce_oneshot(const dmpi_comm_ptrs* ptrs, long long off_
                                       void* stream) {
   if (nbytes % 16 || off_bytes % 16) return -1;
   if (nbytes > slot_bytes) return -3;
+  apply_timeout_env();
   const long long nvec = nbytes / 16;
   const int nb = clamp_blocks(nblocks, nvec);
   dim3 grid(nb, emulate_ranks > 0 ? emulate_ranks : 1);
@@ -384,6 +465,7 @@ extern "C" int dmpi_broadcast(const dmpi_comm_ptrs* ptrs, long long off_bytes, l
                               int emulate_ranks, void* stream) {
   if (nbytes % 16 || off_bytes % 16) return -1;
   const long long nvec = nbytes / 16;
+  apply_timeout_env();
   const int nb = clamp_blocks(nblocks, nvec);
   dim3 grid(nb, emulate_ranks > 0 ? emulate_ranks : 1);
   broadcast_kernel<<<grid, kCommThreads, 0, static_cast<cudaStream_t>(stream)>>>(*ptrs, off_bytes, nvec, root);
@@ -393,6 +475,7 @@ extern "C" int dmpi_broadcast(const dmpi_comm_ptrs* ptrs, long long off_bytes, l
 extern "C" int dmpi_send(const void* src, void* peer_mailbox, long long nbytes, uint32_t* peer_seq,
                          const uint32_t* my_ack, uint32_t seq, void* stream) {
   if (nbytes % 16) return -1;
+  apply_timeout_env();
   send_kernel<<<1, kCommThreads, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const uint4*>(src), static_cast<uint4*>(peer_mailbox), nbytes / 16, peer_seq, my_ack, seq);
   return cudaGetLastError() == cudaSuccess ? 0 : -2;
@@ -401,6 +484,7 @@ extern "C" int dmpi_send(const void* src, void* peer_mailbox, long long nbytes, 
 extern "C" int dmpi_recv(void* dst, const void* my_mailbox, long long nbytes, const uint32_t* my_seq,
                          uint32_t* peer_ack, uint32_t seq, void* stream) {
   if (nbytes % 16) return -1;
+  apply_timeout_env();
   recv_kernel<<<1, kCommThreads, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<uint4*>(dst), static_cast<const uint4*>(my_mailbox), nbytes / 16, my_seq, peer_ack, seq);
   return cudaGetLastError() == cudaSuccess ? 0 : -2;

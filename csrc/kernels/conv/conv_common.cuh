@@ -46,7 +46,7 @@ struct alignas(64) ConvKernelParams {
   // result does not depend on the order in which CTAs retire (fp32 atomics made whole-network gradients differ by
   // ~20 % run to run through ReLU gate flips).  Null: atomics.
   float* stat_scratch;
-  int dbg;  // DMPI_IGEMM_DBG experiment bits (bench only): 1 no TMA store, 2 no statistics, 4 no loads, 8 no MMAs
+  int dbg;  // -DDMPI_ABLATE builds only (otherwise always 0): 1 no TMA store, 2 no statistics, 4 no loads, 8 no MMAs
 };
 
 }  // namespace dmpi
@@ -58,6 +58,7 @@ struct dmpi_conv_plan {
   const void* cached_b;
   const void* cached_o;
   const void* cached_add;
+  long long cached_add_strides[3];  // (sn, sh, sw) the addend map was encoded with: they are per-call arguments
   void* stat_scratch;
   long long stat_scratch_bytes;
   bool maps_valid;

@@ -36,6 +36,15 @@
 #include "../../common/tensormap.h"
 #include "conv_common.cuh"
 
+// Ablation experiments (skip the loads / MMAs / stores / statistics of the kernel to see what paces it) exist only in
+// builds made with -DDMPI_ABLATE (DMPI_NVCC_EXTRA="-DDMPI_ABLATE" python build.py); the shipped kernel has no such
+// switch, so no environment variable can turn it into a no-op.
+#ifdef DMPI_ABLATE
+#define DMPI_DBG(p, bit) (((p).dbg & (bit)) != 0)
+#else
+#define DMPI_DBG(p, bit) false
+#endif
+
 namespace dmpi {
 
 constexpr int kThreads = 512;       // 4 control warps + 8 converter warps + 4 store/statistics warps
@@ -261,7 +270,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
           const int cw = w0 + p.tap_dw[t], ch = h0 + p.tap_dh[t], koff = p.tap_koff[t];
           for (int cb = 0; cb < p.cblocks; ++cb) {
             mbar_wait_spin(&empty[stage], phase ^ 1u);
-            if (p.dbg & 4) {  // experiment: no loads, barriers only (MMA runs on stale shared memory)
+            if (DMPI_DBG(p, 4)) {  // experiment: no loads, barriers only (MMA runs on stale shared memory)
               if (CG == 1 || rank == 0) mbar_arrive(&full[stage]);
               else mbar_arrive_cluster(mapa_u32(smem_u32(&full[stage]), 0));
             } else if (CG == 1) {
@@ -432,7 +441,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
           const uint32_t a_lo = a_lo_ring + static_cast<uint32_t>(stage) * (kABytes >> 4);
           const uint32_t b_lo = b_lo_ring + static_cast<uint32_t>(stage) * (Cfg::kBBytes >> 4);
           if (leader) {
-            if (!(p.dbg & 8)) {  // (experiment bit 8: no MMAs, commits only)
+            if (!DMPI_DBG(p, 8)) {  // (experiment bit 8: no MMAs, commits only)
 #pragma unroll
               for (int k = 0; k < kBlockK / 16; ++k) {
                 if (CG == 2) umma_bf16_pair_lohi(d_tmem, a_lo + 2 * k, hi, b_lo + 2 * k, hi, idesc, k == 0 ? accum : 1u);
@@ -595,7 +604,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
     const int st = threadIdx.x - (4 + kCvtWarps) * 32;
     const int st_c8 = st % kC8;
     const int st_slab = st / kC8;
-    const bool do_stats = p.stat_mod > 0 && !(p.dbg & 2);
+    const bool do_stats = p.stat_mod > 0 && !DMPI_DBG(p, 2);
     float st_sum[kSubs][8], st_sq[kSubs][8];
 #pragma unroll
     for (int s = 0; s < kSubs; ++s)
@@ -659,7 +668,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
           const uint32_t b = u & 1u;
           const uint32_t obuf = obase + b * Cfg::kOutBytes;
           mbar_wait(&ofull[b], (u >> 1) & 1u);
-          if (st == 0 && !(p.dbg & 1)) {
+          if (st == 0 && !DMPI_DBG(p, 1)) {
             const CUtensorMap* omap = &p.o_map[tk.n_blk / p.nblk_per_oview];
             const int ch0 = (tk.n_blk % p.nblk_per_oview) * BN + sub * SN;
 #pragma unroll
@@ -1096,15 +1105,20 @@ extern "C" int dmpi_igemm_run_add(dmpi_conv_plan* plan, const void* a, const voi
     plan->cached_o = out;
     plan->maps_valid = true;
   }
+#ifdef DMPI_ABLATE
   static const int dbg = getenv("DMPI_IGEMM_DBG") ? atoi(getenv("DMPI_IGEMM_DBG")) : 0;
   kp.dbg = dbg;
+#else
+  kp.dbg = 0;
+#endif
   kp.has_add = 0;
   if (addend != nullptr) {
     if (d.out_mode != 0 || d.o_nviews != 1) {
       set_err("igemm: the residual addend needs the bf16 output mode and a single output view");
       return -9;
     }
-    if (plan->cached_add != addend) {
+    if (plan->cached_add != addend || plan->cached_add_strides[0] != add_sn || plan->cached_add_strides[1] != add_sh ||
+        plan->cached_add_strides[2] != add_sw) {
       dmpi_tensor4 av = d.o_view[0];  // same pixel grid and channel count as the output, its own strides
       av.offset = 0;
       av.strides[0] = add_sw;
@@ -1115,6 +1129,9 @@ extern "C" int dmpi_igemm_run_add(dmpi_conv_plan* plan, const void* a, const voi
         return -9;
       }
       plan->cached_add = addend;
+      plan->cached_add_strides[0] = add_sn;
+      plan->cached_add_strides[1] = add_sh;
+      plan->cached_add_strides[2] = add_sw;
     }
     kp.has_add = 1;
   }

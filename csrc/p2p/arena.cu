@@ -9,7 +9,7 @@
 //   [ 2 * MAX_RANKS * stage_slot_bytes ]             one-shot all-reduce staging (double buffered)
 //   [ MAX_RANKS * mailbox_bytes ]                    send/recv mailboxes, one per source rank
 //   [ MAX_COMM_BLOCKS * MAX_RANKS * 4 ]              signal pad
-//   [ MAX_COMM_BLOCKS * 4 ]                          per-block epochs (local use)
+//   [ (MAX_COMM_BLOCKS + 64) * 4 ]                   per-block epochs + launch-wide counters (local use)
 //   [ MAX_RANKS * 4 ] [ MAX_RANKS * 4 ]              send/recv sequence and acknowledge flags
 #include <cuda.h>
 #include <cuda_runtime.h>
@@ -38,7 +38,7 @@ void dmpi_arena_layout(dmpi_arena* a) {
   a->off_mail = a->off_stage + align256(2LL * DMPI_MAX_RANKS * a->stage_slot_bytes);
   a->off_sig = a->off_mail + align256(1LL * DMPI_MAX_RANKS * a->mailbox_bytes);
   a->off_epoch = a->off_sig + align256(4LL * DMPI_MAX_COMM_BLOCKS * DMPI_MAX_RANKS);
-  a->off_seq = a->off_epoch + align256(4LL * DMPI_MAX_COMM_BLOCKS);
+  a->off_seq = a->off_epoch + align256(4LL * (DMPI_MAX_COMM_BLOCKS + 64));  // + launch-wide counters (DMPI_EPOCH_*)
   a->off_ack = a->off_seq + align256(4LL * DMPI_MAX_RANKS);
   a->total = a->off_ack + align256(4LL * DMPI_MAX_RANKS);
 }

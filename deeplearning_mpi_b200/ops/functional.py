@@ -136,6 +136,11 @@ class ConvBnAct(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dout):
         x, y, out, mean, invstd = ctx.saved_tensors
+        if mean is None:
+            # the fused backward implements the batch-statistics formula only (it needs the forward's mean / invstd)
+            raise RuntimeError("backward through an eval-mode BatchNorm is not supported by the fused kernels: call "
+                               "model.train() for training steps (evaluation runs under torch.no_grad() in the "
+                               "reference, ref:pytorch/resnet/main.py:62)")
         weight, bias, gamma, beta = ctx.params
         conv, bn, arena = ctx.conv, ctx.bn, ctx.arena
         R, S = conv.kernel_size

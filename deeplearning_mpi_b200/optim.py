@@ -20,13 +20,17 @@ from .utils.arena import _ARENAS, ParamArena
 
 
 def _find_arena(params: List[torch.nn.Parameter]) -> Optional[ParamArena]:
-    """The arena that owns *all* of ``params`` (and nothing else), if any."""
+    """The arena whose trainable parameters are exactly ``params`` (frozen ones may be passed along, as torch.optim
+    allows: they have no gradient and are skipped), if any."""
     arena = None
     for obj in _ARENAS:
         a = obj()
         if a is None:
             continue
-        if all(id(p) in a.by_param for p in params) and len(params) == len(a.slots):
+        if not all(id(p) in a.by_param for p in params):
+            continue
+        n_train = sum(1 for p in params if p.requires_grad)
+        if n_train == a.n_trainable and len(params) in (a.n_trainable, len(a.slots)):
             arena = a
     return arena
 
@@ -79,7 +83,7 @@ class _FlatOptimizer:
         if self._clip_sumsq is None:
             self._clip_sumsq = torch.zeros((), dtype=torch.float32, device=a.device)
         self._clip_sumsq.zero_()
-        K.sumsq(a.flat_g, a.total, self._clip_sumsq)
+        K.sumsq(a.flat_g, a.total_trainable, self._clip_sumsq)
         self._clip_max_norm = float(max_norm)
         return self._clip_sumsq.sqrt()
 
@@ -118,7 +122,7 @@ class SGD(_FlatOptimizer):
             if mom != 0 and "momentum_buffer" not in self.state:
                 self.state["momentum_buffer"] = torch.zeros_like(a.flat_p)
             ss, mn = self._take_clip()
-            K.sgd_step(a.flat_p, a.flat_g, self.state.get("momentum_buffer"), a.flat_s, a.total, lr, mom, damp, wd,
+            K.sgd_step(a.flat_p, a.flat_g, self.state.get("momentum_buffer"), a.flat_s, a.total_trainable, lr, mom, damp, wd,
                        first, ss, mn)
             a.refresh_derived()
             a.mark_shadows_fresh()
@@ -160,7 +164,7 @@ class Adam(_FlatOptimizer):
                 self.state["step_t"] = torch.full((), float(t - 1), dtype=torch.float32, device=a.device)
             self.state["step_t"] += 1.0
             ss, mn = self._take_clip()
-            K.adam_step_dev(a.flat_p, a.flat_g, self.state["exp_avg"], self.state["exp_avg_sq"], a.flat_s, a.total, lr,
+            K.adam_step_dev(a.flat_p, a.flat_g, self.state["exp_avg"], self.state["exp_avg_sq"], a.flat_s, a.total_trainable, lr,
                             b1, b2, eps, wd, self.state["step_t"], ss, mn)
             a.refresh_derived()
             a.mark_shadows_fresh()
@@ -183,7 +187,7 @@ def clip_grad_norm_(parameters, max_norm: float, norm_type: float = 2.0) -> torc
     a = _find_arena(params)
     if a is not None and a.is_cuda and norm_type == 2.0:
         ss = torch.zeros((), dtype=torch.float32, device=a.device)
-        K.sumsq(a.flat_g, a.total, ss)
-        K.scale_by_clip(a.flat_g, a.total, ss, max_norm)
+        K.sumsq(a.flat_g, a.total_trainable, ss)
+        K.scale_by_clip(a.flat_g, a.total_trainable, ss, max_norm)
         return ss.sqrt()
     return torch.nn.utils.clip_grad_norm_(params, max_norm, norm_type)

@@ -81,26 +81,29 @@ class DistributedDataParallel(nn.Module):
         else:
             self.arena = ensure_arena(module)
         arena = self.arena
-        # ---- bucket plan (arena slots are already in bucket-fill order)
-        sizes = (C.c_int64 * len(arena.slots))(*[_round_up(s.numel) * 4 for s in arena.slots])
-        bucket_of = (C.c_int * len(arena.slots))()
+        # ---- bucket plan over the trainable slots (already in bucket-fill order; frozen parameters sit behind them
+        #      in the arena and take no part in gradient reduction)
+        slots = arena.slots[: arena.n_trainable]
+        self._slots = slots
+        sizes = (C.c_int64 * len(slots))(*[_round_up(s.numel) * 4 for s in slots])
+        bucket_of = (C.c_int * len(slots))()
         host = N.host()
-        self.n_buckets = host.dmpi_plan_buckets(sizes, len(arena.slots), int(first_bucket_mb * _MIB),
+        self.n_buckets = host.dmpi_plan_buckets(sizes, len(slots), int(first_bucket_mb * _MIB),
                                                 int(bucket_cap_mb * _MIB), bucket_of)
         self.bucket_of = list(bucket_of)
         self.bucket_ranges = []  # (element offset, element count) per bucket
         for b in range(self.n_buckets):
             idx = [i for i, bb in enumerate(self.bucket_of) if bb == b]
-            lo = arena.slots[idx[0]].offset
-            hi = arena.slots[idx[-1]].offset + _round_up(arena.slots[idx[-1]].numel)
+            lo = slots[idx[0]].offset
+            hi = slots[idx[-1]].offset + _round_up(slots[idx[-1]].numel)
             self.bucket_ranges.append((lo, hi - lo))
         # ---- verify the layout on every rank (N5), then sync state from rank 0 (N6)
-        logical = (C.c_int64 * len(arena.slots))(*[s.numel for s in arena.slots])
-        self.plan_hash = int(host.dmpi_plan_hash(logical, bucket_of, len(arena.slots)))
+        logical = (C.c_int64 * len(slots))(*[s.numel for s in slots])
+        self.plan_hash = int(host.dmpi_plan_hash(logical, bucket_of, len(slots)))
         self._verify_across_ranks()
         self._sync_module_states()
         # ---- reducer
-        self._reducer = host.dmpi_reducer_create(len(arena.slots), bucket_of, self.n_buckets)
+        self._reducer = host.dmpi_reducer_create(len(slots), bucket_of, self.n_buckets)
         self._cuda_red = None
         if st.kind == "p2p":
             lib = N.cuda()
@@ -114,7 +117,7 @@ class DistributedDataParallel(nn.Module):
         self._pending_work = []
         self._armed = False
         self._finalize_queued = False
-        self._marked = bytearray(len(arena.slots))
+        self._marked = bytearray(len(slots))
         self._install_hooks()
 
     # ------------------------------------------------------------------ construction helpers
@@ -155,12 +158,10 @@ class DistributedDataParallel(nn.Module):
             self._broadcast_buffers_torch()
 
     def _install_hooks(self) -> None:
-        arena = self.arena
-        for i, slot in enumerate(arena.slots):
+        for i, slot in enumerate(self._slots):
             slot.ready_cb = (lambda idx=i: self._mark_ready(idx))
-            if slot.param.requires_grad:
-                # parameters whose gradient comes from stock autograd (not from our fused backward)
-                slot.param.register_post_accumulate_grad_hook(lambda p, idx=i: self._autograd_hook(idx))
+            # parameters whose gradient comes from stock autograd (not from our fused backward)
+            slot.param.register_post_accumulate_grad_hook(lambda p, idx=i: self._autograd_hook(idx))
 
     # ------------------------------------------------------------------ per-iteration machinery
     def _autograd_hook(self, idx: int) -> None:
@@ -280,7 +281,7 @@ class DistributedDataParallel(nn.Module):
         if self._cuda_red is not None:
             N.cuda().dmpi_reducer_cuda_begin(self._cuda_red, N.stream_ptr())
         self._armed = True
-        self._marked = bytearray(len(self.arena.slots))
+        self._marked = bytearray(len(self._slots))
 
     def __del__(self):  # pragma: no cover
         try:

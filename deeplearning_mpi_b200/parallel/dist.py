@@ -235,12 +235,18 @@ class GroupState:
         return c
 
     def scratch_comm(self) -> P2PComm:
+        """Arena behind dist.send / recv / all_reduce / broadcast.  Creating an arena is a collective over the whole
+        world (handle exchange through the store), so it happens inside init_process_group while every rank is known to
+        be present — not lazily at the first call, which only a subset of ranks may ever make (send/recv between ranks
+        0 and 1 of a 4-rank job).  DMPI_LAZY_SCRATCH=1 restores the lazy behaviour (saves 64 MB + the mailboxes per
+        rank when the job only ever uses DistributedDataParallel)."""
         if self.scratch is None:
             self.scratch = self.new_comm(_SCRATCH_BYTES)
         return self.scratch
 
 
 _state: Optional[GroupState] = None
+_init_count = 0  # process groups created by this process so far (every rank creates them in the same order)
 
 
 # ------------------------------------------------------------------------------------------ public API
@@ -286,7 +292,7 @@ def _bootstrap_store(rank: int, world: int, timeout_s: float) -> TCPStore:
 
         agent = tdist.TCPStore(addr, port, world, False, timeout=datetime.timedelta(seconds=timeout_s))
         run_id = os.environ.get("TORCHELASTIC_RUN_ID", "none") + "/" + os.environ.get("TORCHELASTIC_RESTART_COUNT", "0")
-        key = f"dmpi/store_port/{run_id}"
+        key = f"dmpi/store_port/{run_id}/{_init_count}"  # a re-created group must not read the previous store's port
         if rank == 0:
             store = TCPStore(addr, 0, True, timeout_s)
             agent.set(key, str(store.port))
@@ -301,9 +307,10 @@ def init_process_group(backend: str = "nccl", init_method: Optional[str] = None,
     """Same call shapes as the reference: ``init_process_group(backend)`` and
     ``init_process_group(backend, rank=WORLD_RANK, world_size=WORLD_SIZE)``.  ``timeout`` (a ``datetime.timedelta``, as
     in torch.distributed) or ``timeout_s`` bounds the rendezvous and, on the gloo path, every collective."""
-    global _state
+    global _state, _init_count
     if _state is not None:
         raise RuntimeError("trying to initialize the default process group twice!")
+    _init_count += 1
     if timeout is not None:
         timeout_s = timeout.total_seconds() if hasattr(timeout, "total_seconds") else float(timeout)
     backend = (backend or "nccl").lower()
@@ -356,6 +363,8 @@ def init_process_group(backend: str = "nccl", init_method: Optional[str] = None,
         if rank == 0:
             store.set("__run_uid__", os.urandom(6).hex().encode())  # namespaces the abstract unix sockets of this job
         store.barrier("init", rank, world)
+        if os.environ.get("DMPI_LAZY_SCRATCH", "0") != "1":
+            _state.scratch_comm()
 
 
 def destroy_process_group() -> None:
@@ -412,7 +421,7 @@ def send(tensor: torch.Tensor, dst: int, **_ignored) -> None:
 
         tdist.send(tensor=tensor, dst=dst)
         return
-    comm = st.scratch_comm_pairwise() if hasattr(st, "scratch_comm_pairwise") else st.scratch_comm()
+    comm = st.scratch_comm()
     src = tensor.to(st.device)
     raw = _as_bytes_view(src)
     chunk = comm.mailbox_bytes

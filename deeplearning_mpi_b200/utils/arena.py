@@ -113,15 +113,26 @@ class ParamArena:
                 elif p.dim() == 1:
                     kinds.setdefault(id(p), "vector")
         named = [(n, p) for n, p in module.named_parameters()]
+        # Trainable parameters first (bucket-fill order), frozen ones (requires_grad=False) behind them: the reducer,
+        # the fused optimizers and clipping work on the prefix [0, total_trainable) only, so a frozen parameter is
+        # never bucketed, waited for, decayed or updated (torch DDP / torch.optim semantics).
+        ordered = [np_ for np_ in reversed(named) if np_[1].requires_grad] + \
+                  [np_ for np_ in reversed(named) if not np_[1].requires_grad]
         self.slots: List[ParamSlot] = []
         self.by_param: Dict[int, ParamSlot] = {}
         off = 0
-        for idx, (name, p) in enumerate(reversed(named)):
+        self.n_trainable = 0
+        self.total_trainable = 0
+        for idx, (name, p) in enumerate(ordered):
             slot = ParamSlot(name, p, kinds.get(id(p), "other"), tuple(p.shape), p.numel(), off, idx)
             off += _round_up(p.numel())
             self.slots.append(slot)
             self.by_param[id(p)] = slot
+            if p.requires_grad:
+                self.n_trainable = idx + 1
+                self.total_trainable = off
         self.total = max(off, PAD)
+        self.total_trainable = max(self.total_trainable, PAD) if self.n_trainable else 0
 
         self.flat_p = alloc("params", self.total * 4).view(torch.float32)
         self.flat_g = alloc("grads", self.total * 4).view(torch.float32)
@@ -133,7 +144,7 @@ class ParamArena:
                 dst = self.flat_p[s.offset: s.offset + s.numel]
                 dst.copy_(_physical(s.param.data, s.kind).reshape(-1))
                 s.param.data = _logical_view(self.flat_p, s)
-                s.param.grad = _logical_view(self.flat_g, s)
+                s.param.grad = _logical_view(self.flat_g, s) if s.param.requires_grad else None
 
         # ---- buffers (BatchNorm running statistics): one byte range, fp32 first then int64
         bufs = [(n, b) for n, b in module.named_buffers() if b is not None]
@@ -331,6 +342,8 @@ class ParamArena:
         return v.view(s.shape)
 
     def _ensure_grad(self, s: ParamSlot) -> None:
+        if not s.param.requires_grad:
+            return  # frozen: the fused kernels still get a (tail-of-arena) slot to write into; nothing reads it
         g = s.param.grad
         if g is None or g.data_ptr() != self.flat_g.data_ptr() + s.offset * 4:
             # e.g. torch.optim's zero_grad(set_to_none=True): start again from a clean slot
@@ -345,7 +358,7 @@ class ParamArena:
 
     def zero_grad(self) -> None:
         self.flat_g.zero_()
-        for s in self.slots:
+        for s in self.slots[: self.n_trainable]:
             if s.param.grad is None or s.param.grad.data_ptr() != self.flat_g.data_ptr() + s.offset * 4:
                 s.param.grad = _logical_view(self.flat_g, s)
 

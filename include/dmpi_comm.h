@@ -15,6 +15,9 @@ extern "C" {
 
 #define DMPI_MAX_RANKS 8
 #define DMPI_MAX_COMM_BLOCKS 64
+/* slots of the epoch array past the per-block epochs (a rank only touches its own) */
+#define DMPI_EPOCH_ONESHOT_CALLS DMPI_MAX_COMM_BLOCKS      /* one-shot all-reduce launches so far: staging parity */
+#define DMPI_EPOCH_ONESHOT_DONE (DMPI_MAX_COMM_BLOCKS + 1) /* blocks of the running one-shot launch that have finished */
 #define DMPI_F32 0
 #define DMPI_BF16 1
 #define DMPI_IPC_HANDLE_BYTES 64
@@ -24,7 +27,7 @@ typedef struct {
   void* data[DMPI_MAX_RANKS];      /* symmetric data region (gradient buckets, params, buffers) */
   uint32_t* sig[DMPI_MAX_RANKS];   /* signal pad: [DMPI_MAX_COMM_BLOCKS][DMPI_MAX_RANKS] epochs */
   void* stage[DMPI_MAX_RANKS];     /* one-shot staging: [2 parities][DMPI_MAX_RANKS][slot_bytes] */
-  uint32_t* epoch[DMPI_MAX_RANKS]; /* per-block epoch counters (a rank only touches its own) */
+  uint32_t* epoch[DMPI_MAX_RANKS]; /* per-block epoch counters, then the DMPI_EPOCH_* launch-wide counters */
   int world;
   int rank_base;                   /* this process' rank (0 in single-GPU emulation) */
   void* mc_data;                   /* NVLS: multicast address of the data region (NULL when the host exposes none) */
@@ -82,7 +85,9 @@ const char* dmpi_arena_last_error(void);
  * dtype: DMPI_F32 or DMPI_BF16 (fp32 accumulation).  emulate_ranks > 0: single-launch emulation of that many ranks. */
 int dmpi_allreduce_twoshot(const dmpi_comm_ptrs* ptrs, long long off_bytes, long long nbytes, int dtype, float scale,
                            int nblocks, int emulate_ranks, void* stream);
-/* Latency path for small fp32 messages (nbytes <= slot_bytes); wire_bf16 halves the NVLink traffic. */
+/* Latency path for small fp32 messages (nbytes <= slot_bytes); wire_bf16 halves the NVLink traffic.  Staging is
+ * double buffered by the parity of a launch-wide call counter, so consecutive calls may differ in size and nblocks;
+ * calls on one arena must be stream-ordered on every rank (as for every collective here). */
 int dmpi_allreduce_oneshot(const dmpi_comm_ptrs* ptrs, long long off_bytes, long long nbytes, int wire_bf16,
                            float scale, long long slot_bytes, int nblocks, int emulate_ranks, void* stream);
 /* Copies [off_bytes, +nbytes) of root's data region into the same range of every rank. */
@@ -95,6 +100,13 @@ int dmpi_recv(void* dst, const void* my_mailbox, long long nbytes, const uint32_
               uint32_t seq, void* stream);
 int dmpi_sendrecv_emulated(const void* src, void* mailbox, void* dst, long long nbytes, uint32_t* seq_flag,
                            uint32_t* ack_flag, uint32_t seq, void* stream);
+
+/* Upper bound, in seconds, of every device-side wait on a peer's flag (barriers, send/recv); a wait that exceeds it
+ * traps, which surfaces on the host as a launch failure instead of a hung GPU.  Default 600 (the order of NCCL's
+ * watchdog: rank 0 may legitimately spend minutes in a rank-0-only evaluation + checkpoint while its peers already
+ * wait in the next step's first collective); 0 disables the bound.  Also read once from DMPI_COMM_TIMEOUT_S.
+ * Synchronous (cudaMemcpyToSymbol): call it outside stream capture. */
+int dmpi_comm_set_timeout(double seconds);
 
 #ifdef __cplusplus
 }
