@@ -1,11 +1,15 @@
-"""Per-layer timing of the tcgen05 conv kernels vs cuDNN (bf16, channels_last) on ResNet-50 shapes.
-Writes gpurun_out/conv_bench.txt.  CUDA-event timed, L2 flushed between iterations."""
+"""Per-layer timing of the tcgen05 conv kernels vs cuDNN (bf16, channels_last, cudnn.benchmark = True as the reference
+sets it, ref:pytorch/resnet/main.py:29) on every distinct ResNet-50 (MODEL=resnet50, batch 256) or UNet (MODEL=unet,
+batch 16, 512x512) convolution shape.  Writes gpurun_out/conv_bench_<model>.txt.  CUDA-event timed, best of 5, L2
+flushed between iterations."""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch, torch.nn.functional as F
 from deeplearning_mpi_b200.ops import conv as C
 
+torch.backends.cudnn.benchmark = True
 dev = torch.device("cuda:0")
+MODEL = os.environ.get("MODEL", "resnet50")
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
 def timeit(fn, iters=5):
@@ -18,7 +22,7 @@ def timeit(fn, iters=5):
         ts.append(a.elapsed_time(b))
     return min(ts)
 
-N = int(os.environ.get("BS", "256"))
+N = int(os.environ.get("BS", "256" if MODEL == "resnet50" else "16"))
 shapes = [  # h, c, k, R, stride, pad
     (56, 64, 64, 1, 1, 0), (56, 64, 64, 3, 1, 1), (56, 64, 256, 1, 1, 0), (56, 256, 64, 1, 1, 0),
     (56, 256, 128, 1, 1, 0), (56, 128, 128, 3, 2, 1), (28, 128, 512, 1, 1, 0), (28, 512, 128, 1, 1, 0),
@@ -26,6 +30,11 @@ shapes = [  # h, c, k, R, stride, pad
     (14, 1024, 256, 1, 1, 0), (14, 256, 256, 3, 1, 1), (14, 512, 512, 3, 2, 1), (7, 512, 2048, 1, 1, 0),
     (7, 2048, 512, 1, 1, 0), (7, 512, 512, 3, 1, 1),
 ]
+if MODEL == "unet":  # ref:pytorch/unet/model.py:51-68 at 512x512: every 3x3 DoubleConv shape of encoder and decoder
+    shapes = [(512, 64, 64, 3, 1, 1), (256, 64, 128, 3, 1, 1), (256, 128, 128, 3, 1, 1), (128, 128, 256, 3, 1, 1),
+              (128, 256, 256, 3, 1, 1), (64, 256, 512, 3, 1, 1), (64, 512, 512, 3, 1, 1), (32, 512, 1024, 3, 1, 1),
+              (32, 1024, 1024, 3, 1, 1), (64, 1024, 512, 3, 1, 1), (128, 512, 256, 3, 1, 1), (256, 256, 128, 3, 1, 1),
+              (512, 128, 64, 3, 1, 1)]
 if os.environ.get("SHAPES"):
     shapes = [shapes[int(i)] for i in os.environ["SHAPES"].split(",")]
 skip_ref = os.environ.get("SKIP_CUDNN") == "1"
@@ -55,4 +64,4 @@ for (h, c, k, R, st, pad) in shapes:
     line = f"h{h} c{c} k{k} R{R} s{st}: " + " ".join(f"{n}={v*1e3:.0f}us({flops/v/1e9:.0f}TF)" for n, v in res.items())
     print(line, flush=True); lines.append(line)
 os.makedirs("gpurun_out", exist_ok=True)
-open("gpurun_out/conv_bench.txt", "w").write("\n".join(lines) + "\n")
+open(f"gpurun_out/conv_bench_{MODEL}.txt", "w").write("\n".join(lines) + "\n")

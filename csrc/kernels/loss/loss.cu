@@ -233,6 +233,76 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(const float* __restrict__
 
 using namespace dmpi;
 
+namespace dmpi {
+
+// dst[i] = src[i] * (*scale): the incoming gradient of a scalar loss (a device scalar, usually 1) applied to the
+// gradient the fused forward pass already produced, without a host round trip.
+__global__ void __launch_bounds__(256) scale_dev_kernel(const float4* __restrict__ src, float4* __restrict__ dst,
+                                                        long long nvec, const float* __restrict__ src_tail,
+                                                        float* __restrict__ dst_tail, int ntail,
+                                                        const float* __restrict__ scale) {
+  const float s = __ldg(scale);
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < nvec; i += stride) {
+    float4 v = src[i];
+    v.x *= s; v.y *= s; v.z *= s; v.w *= s;
+    dst[i] = v;
+  }
+  if (blockIdx.x == 0 && static_cast<int>(threadIdx.x) < ntail) dst_tail[threadIdx.x] = src_tail[threadIdx.x] * s;
+}
+
+// Backward-pass preparation of the fully connected layer (nn.Linear of ref:pytorch/resnet/main.py:41): one pass over
+// the fp32 logit gradient dy [M, N] that (a) writes the bf16 copy zero-padded to Npad columns which the tcgen05
+// weight-/data-gradient GEMMs consume and (b) adds the column sums (= bias gradient) into dbias.  One block owns 32
+// columns, so every dbias element has a single writer and a fixed summation order.
+__global__ void __launch_bounds__(256) linear_bwd_prep_kernel(const float* __restrict__ dy, long long ld, int M, int N,
+                                                              __nv_bfloat16* __restrict__ out, int Npad,
+                                                              float* __restrict__ dbias) {
+  const int col = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int rg = threadIdx.x >> 5;  // 8 row groups
+  float acc = 0.f;
+  if (col < Npad) {
+    for (int r = rg; r < M; r += 8) {
+      const float v = col < N ? dy[static_cast<long long>(r) * ld + col] : 0.f;
+      out[static_cast<long long>(r) * Npad + col] = __float2bfloat16(v);
+      acc += v;
+    }
+  }
+  __shared__ float red[8][32];
+  red[rg][threadIdx.x & 31] = acc;
+  __syncthreads();
+  if (rg == 0 && col < N && dbias != nullptr) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += red[i][threadIdx.x];
+    dbias[col] += t;
+  }
+}
+
+}  // namespace dmpi
+
+extern "C" int dmpi_scale_dev(const float* src, float* dst, long long n, const float* scale_dev, void* stream) {
+  if (n <= 0) return 0;
+  if ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) return -1;
+  const long long nvec = n / 4;
+  const int ntail = static_cast<int>(n - nvec * 4);
+  long long blocks = (nvec + 256 * 4 - 1) / (256 * 4);
+  if (blocks < 1) blocks = 1;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  dmpi::scale_dev_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const float4*>(src), reinterpret_cast<float4*>(dst), nvec, src + nvec * 4, dst + nvec * 4, ntail,
+      scale_dev);
+  return cudaGetLastError() == cudaSuccess ? 0 : -2;
+}
+
+extern "C" int dmpi_linear_bwd_prep(const float* dy, long long ld, int M, int N, void* dy_bf16, int Npad, float* dbias,
+                                    void* stream) {
+  if (M <= 0 || N <= 0 || Npad < N) return -1;
+  dmpi::linear_bwd_prep_kernel<<<(Npad + 31) / 32, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      dy, ld, M, N, static_cast<__nv_bfloat16*>(dy_bf16), Npad, dbias);
+  return cudaGetLastError() == cudaSuccess ? 0 : -2;
+}
+
 extern "C" int dmpi_softmax_xent(const float* logits, const long long* labels, void* dlogits, float* loss_sum, int M,
                                  int N, long long ld, long long ldd, int ldd_cols, float grad_scale, void* stream) {
   const int warps_per_block = 8;

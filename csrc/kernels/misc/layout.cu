@@ -135,6 +135,13 @@ static int lgrid(long long items) {
   return b < 1 ? 1 : static_cast<int>(b);
 }
 
+// Clears a byte range with the copy engine's memset (no SM time, graph-capturable): gradient arena, BatchNorm
+// accumulators, loss accumulators — everything the step has to start from zero.
+extern "C" int dmpi_memset_async(void* p, int value, long long bytes, void* stream) {
+  if (bytes <= 0) return 0;
+  return cudaMemsetAsync(p, value, static_cast<size_t>(bytes), static_cast<cudaStream_t>(stream)) == cudaSuccess ? 0 : -2;
+}
+
 extern "C" int dmpi_nchw_to_nhwc8_padded(const float* x, void* out, int N, int C, int H, int W, int pad, int Hp, int Wp,
                                          void* stream) {
   if (C > 8) return -1;

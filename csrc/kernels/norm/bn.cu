@@ -446,7 +446,7 @@ __global__ void __launch_bounds__(kBnThreads) bn_stats_kernel(const __nv_bfloat1
       t2 += r2[(r * vecC + ctx) * 8 + cj];
     }
     atomicAdd(sum + c, t1);
-    atomicAdd(sqsum + c, t2);
+    if (sqsum != nullptr) atomicAdd(sqsum + c, t2);
   }
 }
 

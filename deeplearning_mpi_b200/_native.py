@@ -161,6 +161,8 @@ def _bind_cuda(lib) -> None:
     # loss / head
     _sig(lib, "dmpi_softmax_xent", I, [VP, VP, VP, VP, I, I, I64, I64, I, F, VP])
     _sig(lib, "dmpi_bce_logits", I, [VP, VP, VP, VP, I64, F, VP])
+    _sig(lib, "dmpi_scale_dev", I, [VP, VP, I64, VP, VP])
+    _sig(lib, "dmpi_linear_bwd_prep", I, [VP, I64, I, I, VP, I, VP, VP])
     _sig(lib, "dmpi_head_forward", I, [VP, VP, VP, VP, I64, I, I, I64, VP])
     _sig(lib, "dmpi_head_backward", I, [VP, VP, VP, VP, VP, VP, I64, I, I, I64, I64, VP])
     # optim
@@ -171,6 +173,7 @@ def _bind_cuda(lib) -> None:
     _sig(lib, "dmpi_scale_by_clip", I, [VP, I64, VP, F, VP])
     _sig(lib, "dmpi_cast_bf16", I, [VP, VP, I64, VP])
     # layout
+    _sig(lib, "dmpi_memset_async", I, [VP, I, I64, VP])
     _sig(lib, "dmpi_nchw_to_nhwc8_padded", I, [VP, VP, I, I, I, I, I, I, I, VP])
     _sig(lib, "dmpi_nchw_to_nhwc", I, [VP, VP, I, I, I, VP])
     _sig(lib, "dmpi_nhwc_to_nchw", I, [VP, VP, I, I, I, I64, VP])
@@ -207,6 +210,7 @@ def _bind_cuda(lib) -> None:
     _sig(lib, "dmpi_allreduce_twoshot", I, [VP, I64, I64, I, F, I, I, VP])
     _sig(lib, "dmpi_allreduce_oneshot", I, [VP, I64, I64, I, F, I64, I, I, VP])
     _sig(lib, "dmpi_broadcast", I, [VP, I64, I64, I, I, I, VP])
+    _sig(lib, "dmpi_comm_set_timeout", I, [C.c_double])
     _sig(lib, "dmpi_send", I, [VP, VP, I64, VP, VP, C.c_uint32, VP])
     _sig(lib, "dmpi_recv", I, [VP, VP, I64, VP, VP, C.c_uint32, VP])
     _sig(lib, "dmpi_sendrecv_emulated", I, [VP, VP, VP, I64, VP, VP, C.c_uint32, VP])

@@ -165,7 +165,7 @@ class ConvBnAct(torch.autograd.Function):
         if ctx.is_stem:
             _flush_pending_wgrads()
             dwin = arena.stem_dw[id(weight)]
-            dwin.zero_()
+            K.zero_(dwin)
             CV.smallc_wgrad(dy, x, dwin, R, stride)
             k, c = weight.shape[0], weight.shape[1]
             K.stem_unpack_grad(dwin, arena.grad_physical(weight), k, R, S, c)
@@ -238,10 +238,8 @@ class ConvTranspose2x2(torch.autograd.Function):
         CV.convt2x2_wgrad(dout, x, arena.grad_physical(weight))
         arena.grad_ready(weight)
         if bias is not None:
-            k = ctx.k
-            scratch = torch.zeros(2 * k, dtype=torch.float32, device=dout.device)
-            K.channel_stats(dout, scratch[:k], scratch[k:])
-            arena.grad_physical(bias).add_(scratch[:k])
+            # every output pixel sees the bias once: its gradient is the per-channel sum of dout, added into the slot
+            K.channel_stats(dout, arena.grad_physical(bias), None)
             arena.grad_ready(bias)
         dx = CV.convt2x2_dgrad(dout, arena.w_natural(weight)) if ctx.needs_input_grad[0] else None
         return dx, None, None, None, None
@@ -318,12 +316,13 @@ class LinearFn(torch.autograd.Function):
         n_out, kk = weight.shape
         wt = arena.w_transposed(weight)  # [K, N_pad]
         npad = wt.shape[1]
-        dyp = torch.zeros((dy.shape[0], npad), dtype=torch.bfloat16, device=dy.device)
-        dyp[:, :n_out].copy_(dy)
+        if dy.dtype != torch.float32 or dy.stride(1) != 1:
+            dy = dy.float().contiguous()
+        # one pass: bf16 zero-padded copy for the GEMMs + the bias gradient (column sums) into its arena slot
+        dyp = K.linear_bwd_prep(dy, npad, arena.grad_physical(bias) if bias is not None else None)
         CV.linear_wgrad(dyp, x.contiguous(), arena.grad_physical(weight))
         arena.grad_ready(weight)
         if bias is not None:
-            arena.grad_physical(bias).add_(dy.sum(0))
             arena.grad_ready(bias)
         dx = CV.linear_dgrad(dyp, wt) if ctx.needs_input_grad[0] else None
         return dx, None, None, None
@@ -381,7 +380,7 @@ class SoftmaxCrossEntropy(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g):
         (d,) = ctx.saved_tensors
-        return d * g, None
+        return K.scale_dev(d, g), None
 
 
 class BCEWithLogits(torch.autograd.Function):
@@ -396,4 +395,4 @@ class BCEWithLogits(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g):
         (d,) = ctx.saved_tensors
-        return (d * g).view(ctx.shape), None
+        return K.scale_dev(d, g).view(ctx.shape), None

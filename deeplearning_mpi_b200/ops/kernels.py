@@ -34,6 +34,16 @@ def _rows_ld(x: torch.Tensor) -> Tuple[int, int]:
     return rows, sw
 
 
+def zero_(t: torch.Tensor) -> torch.Tensor:
+    """In-place clear of a dense tensor with cudaMemsetAsync on the current stream (CPU tensors: Tensor.zero_)."""
+    if not t.is_cuda:
+        return t.zero_()
+    assert t.is_contiguous()
+    rc = N.cuda().dmpi_memset_async(_p(t), 0, t.numel() * t.element_size(), N.stream_ptr())
+    _chk(rc, "dmpi_memset_async")
+    return t
+
+
 # ------------------------------------------------------------------------------------------ BatchNorm
 _DETERMINISTIC = os.environ.get("DMPI_DETERMINISTIC_BN", "0" if os.environ.get("DMPI_DETERMINISTIC", "1") == "0" else "1") == "1"
 _BN_DET_BYTES = 1 << 20
@@ -150,7 +160,7 @@ def softmax_xent(logits: torch.Tensor, labels: torch.Tensor, grad_scale: float =
     """Returns (loss scalar fp32 tensor, dlogits fp32 [M, N]) for mean-reduced cross-entropy."""
     m, n = logits.shape
     assert logits.dtype == torch.float32 and logits.stride(1) == 1 and labels.dtype == torch.int64
-    loss = torch.zeros((), dtype=torch.float32, device=logits.device)
+    loss = zero_(torch.empty((), dtype=torch.float32, device=logits.device))
     d = torch.empty((m, n), dtype=torch.float32, device=logits.device)
     rc = N.cuda().dmpi_softmax_xent(_p(logits), _p(labels), _p(d), _p(loss), m, n, logits.stride(0), n, n,
                                     float(grad_scale), N.stream_ptr())
@@ -161,12 +171,35 @@ def softmax_xent(logits: torch.Tensor, labels: torch.Tensor, grad_scale: float =
 
 def bce_logits(x: torch.Tensor, t: torch.Tensor, grad_scale: float = 1.0):
     assert x.dtype == torch.float32 and t.dtype == torch.float32 and x.is_contiguous() and t.is_contiguous()
-    loss = torch.zeros((), dtype=torch.float32, device=x.device)
+    loss = zero_(torch.empty((), dtype=torch.float32, device=x.device))
     d = torch.empty_like(x)
     rc = N.cuda().dmpi_bce_logits(_p(x), _p(t), _p(d), _p(loss), x.numel(), float(grad_scale), N.stream_ptr())
     N.count_launch()
     _chk(rc, "dmpi_bce_logits")
     return loss, d
+
+
+def scale_dev(src: torch.Tensor, scale: torch.Tensor) -> torch.Tensor:
+    """src * scale for a 0-dim fp32 device tensor ``scale`` (the gradient flowing into a scalar loss), out of place."""
+    assert src.dtype == torch.float32 and src.is_contiguous()
+    if scale.dtype != torch.float32 or not scale.is_cuda:
+        scale = scale.to(device=src.device, dtype=torch.float32)
+    dst = torch.empty_like(src)
+    rc = N.cuda().dmpi_scale_dev(_p(src), _p(dst), src.numel(), _p(scale), N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_scale_dev")
+    return dst
+
+
+def linear_bwd_prep(dy: torch.Tensor, npad: int, dbias: Optional[torch.Tensor]) -> torch.Tensor:
+    """fp32 logit gradient [M, N] -> bf16 [M, npad] (zero padded) for the tcgen05 GEMMs; dbias += column sums."""
+    assert dy.dtype == torch.float32 and dy.dim() == 2 and dy.stride(1) == 1
+    m, n = dy.shape
+    out = torch.empty((m, npad), dtype=torch.bfloat16, device=dy.device)
+    rc = N.cuda().dmpi_linear_bwd_prep(_p(dy), dy.stride(0), m, n, _p(out), npad, _p(dbias), N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_linear_bwd_prep")
+    return out
 
 
 def head_forward(x, w, b):

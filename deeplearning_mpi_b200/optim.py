@@ -82,7 +82,7 @@ class _FlatOptimizer:
         assert a is not None, "fused clipping needs arena-resident CUDA parameters"
         if self._clip_sumsq is None:
             self._clip_sumsq = torch.zeros((), dtype=torch.float32, device=a.device)
-        self._clip_sumsq.zero_()
+        K.zero_(self._clip_sumsq)
         K.sumsq(a.flat_g, a.total_trainable, self._clip_sumsq)
         self._clip_max_norm = float(max_norm)
         return self._clip_sumsq.sqrt()
@@ -186,7 +186,7 @@ def clip_grad_norm_(parameters, max_norm: float, norm_type: float = 2.0) -> torc
     params = [p for p in parameters]
     a = _find_arena(params)
     if a is not None and a.is_cuda and norm_type == 2.0:
-        ss = torch.zeros((), dtype=torch.float32, device=a.device)
+        ss = K.zero_(torch.empty((), dtype=torch.float32, device=a.device))
         K.sumsq(a.flat_g, a.total_trainable, ss)
         K.scale_by_clip(a.flat_g, a.total_trainable, ss, max_norm)
         return ss.sqrt()

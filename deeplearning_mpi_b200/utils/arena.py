@@ -263,7 +263,7 @@ class ParamArena:
         """Zeroed scratch for the BatchNorm backward reductions."""
         acc = self._bn_slices[id(bn)][2]
         if self._bn_dirty[id(bn)]:
-            acc.zero_()
+            self._zero(acc)
         self._bn_dirty[id(bn)] = True
         return acc
 
@@ -272,7 +272,7 @@ class ParamArena:
         shadows reflect the current master weights."""
         if not self.is_cuda:
             return
-        self.bn_scratch.zero_()
+        self._zero(self.bn_scratch)
         for k in self._bn_dirty:
             self._bn_dirty[k] = False
         self.refresh_shadows()
@@ -347,7 +347,7 @@ class ParamArena:
         g = s.param.grad
         if g is None or g.data_ptr() != self.flat_g.data_ptr() + s.offset * 4:
             # e.g. torch.optim's zero_grad(set_to_none=True): start again from a clean slot
-            self.flat_g[s.offset: s.offset + _round_up(s.numel)].zero_()
+            self._zero(self.flat_g[s.offset: s.offset + _round_up(s.numel)])
             s.param.grad = _logical_view(self.flat_g, s)
 
     def grad_ready(self, p: nn.Parameter) -> None:
@@ -356,8 +356,14 @@ class ParamArena:
         if s.ready_cb is not None:
             s.ready_cb()
 
+    @staticmethod
+    def _zero(t: torch.Tensor) -> None:
+        from ..ops import kernels as K
+
+        K.zero_(t)
+
     def zero_grad(self) -> None:
-        self.flat_g.zero_()
+        self._zero(self.flat_g)
         for s in self.slots[: self.n_trainable]:
             if s.param.grad is None or s.param.grad.data_ptr() != self.flat_g.data_ptr() + s.offset * 4:
                 s.param.grad = _logical_view(self.flat_g, s)

@@ -67,7 +67,7 @@ int dmpi_bn_backward_noalloc(const void* dout, const void* y, const void* act, v
                              long long ld_dout, long long ldy, long long ld_act, long long ld_dy, long long ld_dres,
                              const float* mean, const float* invstd, const float* gamma, float* dgamma, float* dbeta,
                              void* stream);
-/* sum[c] += sum_rows y, sqsum[c] += sum_rows y*y */
+/* sum[c] += sum_rows y, sqsum[c] += sum_rows y*y (sqsum may be NULL: channel sums only, e.g. a bias gradient) */
 int dmpi_bn_stats(const void* y, long long M, int C, long long ld, float* sum, float* sqsum, void* stream);
 
 /* ---- pooling (ref:pytorch/unet/model.py:25; torchvision resnet maxpool/avgpool) */
@@ -91,6 +91,12 @@ int dmpi_softmax_xent(const float* logits, const long long* labels, void* dlogit
                       long long ld, long long ldd, int ldd_cols, float grad_scale, void* stream);
 int dmpi_bce_logits(const float* x, const float* t, float* dx, float* loss_sum, long long M, float grad_scale,
                     void* stream);
+/* dst = src * (*scale_dev): applies the incoming gradient of the scalar loss (a device scalar) to the stored dlogits. */
+int dmpi_scale_dev(const float* src, float* dst, long long n, const float* scale_dev, void* stream);
+/* Backward-pass preparation of nn.Linear (ref:pytorch/resnet/main.py:41): dy fp32 [M, N] (row stride ld) -> bf16 copy
+ * zero-padded to Npad columns (operand of the tcgen05 wgrad / dgrad GEMMs) and dbias[c] += sum_rows dy (NULL: skip). */
+int dmpi_linear_bwd_prep(const float* dy, long long ld, int M, int N, void* dy_bf16, int Npad, float* dbias,
+                         void* stream);
 /* narrow 1x1 conv head, K <= 8 output classes (ref:pytorch/unet/model.py:68) */
 int dmpi_head_forward(const void* x, const float* w, const float* b, float* y, long long M, int C, int K, long long ldx,
                       void* stream);
@@ -112,6 +118,7 @@ int dmpi_scale_by_clip(float* g, long long n, const float* sumsq, float max_norm
 int dmpi_cast_bf16(const float* src, void* dst, long long n, void* stream);
 
 /* ---- layout / staging (ref:pytorch/resnet/main.py:126 input .to(device)) */
+int dmpi_memset_async(void* p, int value, long long bytes, void* stream); /* cudaMemsetAsync on `stream` */
 int dmpi_nchw_to_nhwc8_padded(const float* x, void* out, int N, int C, int H, int W, int pad, int Hp, int Wp,
                               void* stream);
 int dmpi_nchw_to_nhwc(const float* x, void* out, int N, int C, int HW, void* stream);
