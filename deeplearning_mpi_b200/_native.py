@@ -158,6 +158,8 @@ def _bind_cuda(lib) -> None:
                                                I64, I64, I64, VP])
     _sig(lib, "dmpi_avgpool_forward", I, [VP, VP, I, I, I, VP])
     _sig(lib, "dmpi_avgpool_backward", I, [VP, VP, I, I, I, VP])
+    _sig(lib, "dmpi_upsample2x_bilinear_forward", I, [VP, VP, I, I, I, I, I64, I64, I64, I64, I64, I64, VP])
+    _sig(lib, "dmpi_upsample2x_bilinear_backward", I, [VP, VP, I, I, I, I, I64, I64, I64, I64, I64, I64, VP])
     # loss / head
     _sig(lib, "dmpi_softmax_xent", I, [VP, VP, VP, VP, I, I, I64, I64, I, F, VP])
     _sig(lib, "dmpi_bce_logits", I, [VP, VP, VP, VP, I64, F, VP])

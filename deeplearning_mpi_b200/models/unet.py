@@ -10,14 +10,17 @@ CUDA forward (sm_100a kernels, NHWC bf16):
     pre-allocated buffer and the decoder's ConvTranspose2d (a GEMM with a pixel-shuffle scatter epilogue)
     writes the lower slice (the reference materialises ``torch.cat`` — model.py:47);
   * the 1-channel head is a bandwidth-bound dot-product kernel.
-``up_sample_mode='bilinear'`` keeps the reference semantics (nn.Upsample, align_corners=True) through a
-PyTorch op on the NHWC tensor; ``conv_transpose`` is the benchmarked mode.
+``up_sample_mode='bilinear'`` (nn.Upsample, align_corners=True, ref:pytorch/unet/model.py:39-40) runs a native gather
+kernel pair (csrc/kernels/misc/upsample.cu) that also writes straight into the concat buffer; ``conv_transpose`` is the
+benchmarked mode.
+
+``python -m deeplearning_mpi_b200.models.unet`` prints the module tree and the output shape for a 512x512 input, the
+smoke block of ref:pytorch/unet/model.py:84-89.
 """
 from __future__ import annotations
 
 import torch
 import torch.nn as nn
-import torch.nn.functional as F
 
 from ..ops import functional as FN
 from ..utils.arena import ensure_arena
@@ -85,9 +88,7 @@ class UpBlock(nn.Module):
         if isinstance(self.up_sample, nn.ConvTranspose2d):
             up = FN.ConvTranspose2x2.apply(down, self.up_sample.weight, self.up_sample.bias, [cat_buf[..., :c_up]], arena)
         else:
-            up_nchw = F.interpolate(down.permute(0, 3, 1, 2).float(), scale_factor=2, mode="bilinear", align_corners=True)
-            up = up_nchw.permute(0, 2, 3, 1).to(torch.bfloat16)
-            cat_buf[..., :c_up].copy_(up.detach())
+            up = FN.UpsampleBilinear2x.apply(down, [cat_buf[..., :c_up]])
         x = FN.ConcatView.apply(up, skip, [cat_buf], link)
         return self.double_conv.forward_sm100(x, arena)
 
@@ -146,3 +147,23 @@ class UNet(nn.Module):
         a = self.up_conv2.forward_sm100(a, s2, cat2, arena, l2)
         a = self.up_conv1.forward_sm100(a, s1, cat1, arena, l1)
         return FN.Head1x1.apply(a, self.conv_last.weight, self.conv_last.bias, arena)
+
+
+def _smoke(size: int = 512) -> None:
+    """Module tree + output shape for one ``size`` x ``size`` RGB image (on the GPU through the sm_100a kernels when
+    one is present, else the CPU oracle path)."""
+    model = UNet(out_classes=1)
+    print(model)
+    dev = torch.device("cuda" if torch.cuda.is_available() else "cpu")
+    model = model.to(dev).eval()
+    with torch.no_grad():
+        out = model(torch.randn(1, 3, size, size, device=dev))
+    n_params = sum(p.numel() for p in model.parameters())
+    print(f"input (1, 3, {size}, {size}) -> output {tuple(out.shape)} on {dev.type}; {n_params:,} parameters, "
+          f"{len(model.state_dict())} state_dict keys")
+
+
+if __name__ == "__main__":
+    import sys
+
+    _smoke(int(sys.argv[1]) if len(sys.argv) > 1 else 512)

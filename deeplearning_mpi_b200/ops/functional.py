@@ -245,6 +245,21 @@ class ConvTranspose2x2(torch.autograd.Function):
         return dx, None, None, None, None
 
 
+class UpsampleBilinear2x(torch.autograd.Function):
+    """nn.Upsample(scale_factor=2, mode="bilinear", align_corners=True) on NHWC bf16, writing into a channel slice of
+    the decoder's concat buffer (ref:pytorch/unet/model.py:39-40,46-47)."""
+
+    @staticmethod
+    def forward(ctx, x, out_holder):
+        return K.upsample2x_bilinear_forward(x, out_holder[0] if out_holder else None)
+
+    @staticmethod
+    def backward(ctx, dout):
+        if dout.dtype != torch.bfloat16:
+            dout = dout.to(torch.bfloat16)
+        return K.upsample2x_bilinear_backward(dout), None
+
+
 class ConcatView(torch.autograd.Function):
     """Zero-copy torch.cat([up, skip], dim=channels): both producers already wrote their channel slice of ``buf``;
     this node only ties them into the autograd graph and splits the incoming gradient into two slice views."""

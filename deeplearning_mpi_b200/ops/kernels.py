@@ -155,6 +155,32 @@ def avgpool_backward(dy, in_shape):
     return dx
 
 
+def upsample2x_bilinear_forward(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """NHWC bf16 [n, h, w, c] -> [n, 2h, 2w, c] (align_corners=True); ``out`` may be a channel slice of a wider buffer."""
+    n, h, w, c = x.shape
+    assert x.dtype == torch.bfloat16 and x.stride(3) == 1
+    if out is None:
+        out = torch.empty((n, 2 * h, 2 * w, c), dtype=torch.bfloat16, device=x.device)
+    assert tuple(out.shape) == (n, 2 * h, 2 * w, c) and out.stride(3) == 1
+    rc = N.cuda().dmpi_upsample2x_bilinear_forward(_p(x), _p(out), n, h, w, c, x.stride(0), x.stride(1), x.stride(2),
+                                                   out.stride(0), out.stride(1), out.stride(2), N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_upsample2x_bilinear_forward")
+    return out
+
+
+def upsample2x_bilinear_backward(dy: torch.Tensor) -> torch.Tensor:
+    n, oh, ow, c = dy.shape
+    assert dy.dtype == torch.bfloat16 and dy.stride(3) == 1 and oh % 2 == 0 and ow % 2 == 0
+    dx = torch.empty((n, oh // 2, ow // 2, c), dtype=torch.bfloat16, device=dy.device)
+    rc = N.cuda().dmpi_upsample2x_bilinear_backward(_p(dy), _p(dx), n, oh // 2, ow // 2, c, dy.stride(0), dy.stride(1),
+                                                    dy.stride(2), dx.stride(0), dx.stride(1), dx.stride(2),
+                                                    N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_upsample2x_bilinear_backward")
+    return dx
+
+
 # ------------------------------------------------------------------------------------------ losses / head
 def softmax_xent(logits: torch.Tensor, labels: torch.Tensor, grad_scale: float = 1.0):
     """Returns (loss scalar fp32 tensor, dlogits fp32 [M, N]) for mean-reduced cross-entropy."""

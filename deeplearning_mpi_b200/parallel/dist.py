@@ -508,3 +508,25 @@ def broadcast(tensor: torch.Tensor, src: int) -> None:
             raw[o: o + n].copy_(stage[:n])
     if raw.data_ptr() != tensor.data_ptr():
         tensor.copy_(raw.view(tensor.dtype).view(tensor.shape))
+
+
+def broadcast_object(obj, src: int = 0):
+    """Returns rank ``src``'s picklable ``obj`` on every rank (small control-plane data: a palette, a config dict).
+    P2P groups move it through the rendezvous store, the others through torch.distributed."""
+    st = _require()
+    if st.world == 1:
+        return obj
+    if st.kind != "p2p":
+        import torch.distributed as tdist
+
+        box = [obj if st.rank == src else None]
+        tdist.broadcast_object_list(box, src=src)
+        return box[0]
+    import pickle
+
+    st.barrier_count += 1
+    key = f"bcast_obj{st.barrier_count}"
+    if st.rank == src:
+        st.store.set(key, pickle.dumps(obj))
+        return obj
+    return pickle.loads(st.store.get(key))

@@ -86,6 +86,15 @@ int dmpi_maxpool_backward_add(const void* dy, const void* idx, void* dx, int N, 
 int dmpi_avgpool_forward(const void* x, void* y, int N, int HW, int C, void* stream);
 int dmpi_avgpool_backward(const void* dy, void* dx, int N, int HW, int C, void* stream);
 
+/* ---- bilinear 2x up-sampling, align_corners = True (nn.Upsample in ref:pytorch/unet/model.py:39-40).
+ * x / dx: NHWC bf16 [N, H, W, C]; y / dy: [N, 2H, 2W, C]; element strides of n / h / w (channel stride 1, C % 8 == 0,
+ * strides multiples of 8), so y may be a channel slice of the decoder's concat buffer.  Backward is a gather (no
+ * atomics, deterministic). */
+int dmpi_upsample2x_bilinear_forward(const void* x, void* y, int N, int H, int W, int C, long long xsn, long long xsh,
+                                     long long xsw, long long ysn, long long ysh, long long ysw, void* stream);
+int dmpi_upsample2x_bilinear_backward(const void* dy, void* dx, int N, int H, int W, int C, long long dsn, long long dsh,
+                                      long long dsw, long long xsn, long long xsh, long long xsw, void* stream);
+
 /* ---- losses, forward value + input gradient in one pass (ref:pytorch/resnet/main.py:113; ref:pytorch/unet/train.py:162) */
 int dmpi_softmax_xent(const float* logits, const long long* labels, void* dlogits_f32, float* loss_sum, int M, int N,
                       long long ld, long long ldd, int ldd_cols, float grad_scale, void* stream);

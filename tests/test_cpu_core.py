@@ -214,6 +214,31 @@ def test_choose_box_and_dice_and_dataset(tmp_path):
     item = ds[0]
     assert item["image"].shape == (3, 10, 15) and item["mask"].shape == (10, 15)
     assert item["image"].max() <= 1.0 and set(item["mask"].unique().tolist()) <= {0.0, 1.0}
+    assert ds.mask_values == [0, 255] and len(ds) == 3
+    # colour masks (one packed value per colour), a suffix, the parallel palette scan and a ready-made palette
+    from deeplearning_mpi_b200.utils.data import SegmentationFolder, scan_palette
+
+    (tmp_path / "rgb_i").mkdir()
+    (tmp_path / "rgb_m").mkdir()
+    colours = np.array([[0, 0, 0], [255, 0, 0], [0, 0, 255]], dtype=np.uint8)
+    want = {}
+    for i in range(9):
+        lab = rng.integers(0, 3, (8, 12))
+        want[f"s{i}"] = lab
+        Image.fromarray(rng.integers(0, 255, (8, 12), dtype=np.uint8)).save(tmp_path / "rgb_i" / f"s{i}.png")
+        Image.fromarray(colours[lab]).save(tmp_path / "rgb_m" / f"s{i}_mask.png")
+    pal = scan_palette(sorted((tmp_path / "rgb_m").glob("*.png")), workers=2)
+    assert pal.tolist() == [0, 255, 255 << 16]
+    ds2 = SegmentationFolder(str(tmp_path / "rgb_i"), str(tmp_path / "rgb_m"), 1.0, "_mask", palette=pal)
+    it = ds2[4]
+    assert it["image"].shape == (1, 8, 12) and it["image"].max() <= 1.0
+    # packed order: black 0 < blue 255 < red 255 << 16  ->  class indices 0, 1, 2
+    remap = np.array([0, 2, 1])
+    assert np.array_equal(ds2.class_index_mask(colours[want["s4"]]), remap[want["s4"]])
+    assert np.array_equal(it["mask"].numpy(), (want["s4"] > 0).astype(np.float32))
+    with pytest.raises(FileNotFoundError):
+        SegmentationFolder(str(tmp_path / "rgb_i"), str(tmp_path / "rgb_m"), 1.0, "")  # suffix missing: no masks match
+    assert SegmentationFolder.shared(str(tmp_path / "images"), str(tmp_path / "masks"), 0.5).mask_values == [0, 255]
 
 
 def test_conv_planner_invariants():

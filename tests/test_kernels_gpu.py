@@ -374,3 +374,100 @@ def test_sendrecv_emulated():
         assert rc == 0
         torch.cuda.synchronize()
         assert torch.equal(dst, src)
+
+
+@pytest.mark.parametrize("shape", [(2, 8, 8, 64), (1, 5, 7, 128), (3, 16, 12, 8), (2, 1, 9, 64)])
+def test_upsample_bilinear2x(shape):
+    """Native bilinear x2 (align_corners=True) forward into a channel slice + gather backward vs F.interpolate fp32."""
+    from deeplearning_mpi_b200.ops import kernels as K
+
+    torch.manual_seed(3)
+    n, h, w, c = shape
+    x = torch.randn(shape, device=DEV).bfloat16()
+    buf = torch.zeros((n, 2 * h, 2 * w, c + 64), dtype=torch.bfloat16, device=DEV)
+    out = K.upsample2x_bilinear_forward(x, buf[..., :c])
+    xr = x.float().permute(0, 3, 1, 2).requires_grad_(True)
+    ref = F.interpolate(xr, scale_factor=2, mode="bilinear", align_corners=True)
+    _close(out.float(), ref.permute(0, 2, 3, 1), 1e-2, "upsample fwd")
+    assert torch.all(buf[..., c:] == 0), "forward wrote outside its channel slice"
+    g = torch.randn((n, 2 * h, 2 * w, c), device=DEV).bfloat16()
+    dx = K.upsample2x_bilinear_backward(g)
+    ref.backward(g.float().permute(0, 3, 1, 2))
+    _close(dx.float(), xr.grad.permute(0, 2, 3, 1), 1e-2, "upsample bwd")
+
+
+def test_unet_bilinear_mode_runs_native():
+    """UNet(up_sample_mode='bilinear') trains through the native up-sampling kernels (no ATen interpolate)."""
+    import deeplearning_mpi_b200.nn as dnn
+    from deeplearning_mpi_b200 import _native
+    from deeplearning_mpi_b200.models import UNet
+
+    torch.manual_seed(0)
+    m = UNet(out_classes=1, up_sample_mode="bilinear").to(DEV)
+    ref = UNet(out_classes=1, up_sample_mode="bilinear")
+    ref.load_state_dict(m.state_dict())
+    x = torch.randn(2, 3, 32, 32)
+    t = (torch.rand(2, 32, 32) > 0.5).float()
+    before = _native.launches()
+    loss = dnn.binary_cross_entropy_with_logits(m(x.to(DEV)).squeeze(1), t.to(DEV))
+    loss.backward()
+    torch.cuda.synchronize()
+    assert _native.launches() - before > 100
+    loss_ref = F.binary_cross_entropy_with_logits(ref(x).squeeze(1), t)
+    assert abs(loss.item() - loss_ref.item()) < 0.05 * abs(loss_ref.item()) + 1e-3
+    assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in m.parameters())
+
+
+def test_linear_bwd_prep_and_scale():
+    from deeplearning_mpi_b200.ops import kernels as K
+
+    torch.manual_seed(1)
+    for m, n, npad in [(256, 1000, 1024), (37, 10, 64), (8, 64, 64)]:
+        dy = torch.randn(m + 3, n + 5, device=DEV)[:m, :n]  # row stride != n
+        db = torch.randn(n, device=DEV)
+        db0 = db.clone()
+        out = K.linear_bwd_prep(dy, npad, db)
+        _close(out[:, :n].float(), dy, 1e-2, "prep cast")
+        assert torch.all(out[:, n:] == 0)
+        _close(db - db0, dy.sum(0), 1e-5, "prep bias grad", atol=1e-5)
+    for numel in (1, 7, 4096, 100003):
+        src = torch.randn(numel, device=DEV)
+        g = torch.tensor(0.37, device=DEV)
+        _close(K.scale_dev(src, g), src * 0.37, 1e-6, "scale_dev")
+    z = torch.randn(1000, device=DEV)
+    K.zero_(z)
+    assert torch.all(z == 0)
+
+
+def test_oneshot_alternating_sizes_and_blocks():
+    """Staging parity comes from a launch-wide call counter: consecutive one-shot calls may differ in size and block
+    count (blocks that sat out a small call must agree with their neighbours on the next large one)."""
+    from deeplearning_mpi_b200 import _native as N
+
+    lib = N.cuda()
+    world, slot = 4, 1 << 20
+    arena = lib.dmpi_arena_create_emulated(world, slot + 4096, slot, 1 << 16)
+    assert arena
+    ptrs, s = lib.dmpi_arena_ptrs(arena), N.stream_ptr()
+
+    def view(rank, n):
+        base = lib.dmpi_arena_data(arena, rank)
+
+        class _W:
+            __cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (base, False), "version": 2}
+        return torch.as_tensor(_W(), device=DEV)
+
+    try:
+        torch.manual_seed(9)
+        for n, nb in [(1024, 8), (1 << 16, 32), (2048, 1), (1 << 16, 16), (4096, 64), (1 << 18, 3), (1 << 18, 64)]:
+            bufs = [view(r, n) for r in range(world)]
+            src = [torch.randn(n, device=DEV) for _ in range(world)]
+            for r in range(world):
+                bufs[r].copy_(src[r])
+            ref = torch.stack(src).sum(0) / world
+            assert lib.dmpi_allreduce_oneshot(ptrs, 0, n * 4, 0, 1.0 / world, slot, nb, world, s) == 0
+            torch.cuda.synchronize()
+            for r in range(world):
+                _close(bufs[r], ref, 1e-6, f"oneshot n={n} nb={nb} rank{r}", atol=1e-6)
+    finally:
+        lib.dmpi_arena_destroy(arena)
