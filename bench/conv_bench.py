@@ -55,6 +55,8 @@ for (h, c, k, R, st, pad) in shapes:
     xc = x.permute(0, 3, 1, 2); wc = w.contiguous(memory_format=torch.channels_last); dyc = dy.permute(0, 3, 1, 2)
     res = {}
     res["fprop"] = timeit(lambda: C.conv2d_fprop(x, w2d, R, R, st, pad, stats=(ssum, ssq)))
+    if os.environ.get("FPROP_NOSTATS") == "1":  # the same GEMM without the BatchNorm statistics in the epilogue
+        res["fprop_nostat"] = timeit(lambda: C.conv2d_fprop(x, w2d, R, R, st, pad))
     res["dgrad"] = timeit(lambda: C.conv2d_dgrad(dy, wt2d, R, R, st, pad, (h, h)))
     res["wgrad"] = timeit(lambda: C.conv2d_wgrad(dy, x, dw, R, R, st, pad))
     if st == 1:

@@ -55,7 +55,8 @@ constexpr int kStatWarps = 4;
 constexpr int kTileM = 128;
 constexpr int kBlockK = 64;  // bf16 elements = one 128-byte swizzle row
 constexpr int kABytes = kTileM * kBlockK * 2;
-constexpr int kDetInFlight = 8;  // partial-sum rows a thread of the last-CTA reduction keeps in flight
+constexpr int kDetInFlight = 4;  // partial-sum rows a thread of the tail reduction keeps in flight
+constexpr int kTailCtas = 8;     // CTAs that share the deterministic statistics tail
 constexpr int kStatHdr = 64;  // floats reserved at the head of the statistics scratch (ticket counter)
 
 // CG = 1: one CTA per tile.  CG = 2: a CTA pair (cluster of two SMs of one TPC) works on a 256-row tile with
@@ -743,12 +744,13 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
           // release: the barrier orders every thread's partial stores before thread 0's fence + ticket (one fence per
           // CTA instead of 128); acquire on the other side: fence after drawing the last ticket, then the CTA barrier
           named_bar_sync(2, kStatThreads);
-          if (st == 0) {
+          if (st == 0 && !DMPI_DBG(p, 32)) {
             __threadfence();
             uint32_t* ticket = reinterpret_cast<uint32_t*>(p.stat_scratch);  // fixed place: launches of every shape share it
-            const bool last = atomicAdd(ticket, 1u) == gridDim.x - 1;
-            if (last) __threadfence();
-            *last_flag = last ? 1u : 0u;
+            const uint32_t t = atomicAdd(ticket, 1u);
+            const uint32_t tail = gridDim.x < static_cast<uint32_t>(kTailCtas) ? gridDim.x : static_cast<uint32_t>(kTailCtas);
+            // the last `tail` CTAs to finish share the final summation (role = order of arrival among them)
+            *last_flag = t >= gridDim.x - tail ? t - (gridDim.x - tail) + 1u : 0u;
           }
         }
       }
@@ -765,62 +767,78 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
     if (warp == 2) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
   }
 
-  // Deterministic BatchNorm statistics: the CTA that drew the last ticket adds the partial sums of all CTAs in CTA
-  // order.  8 lanes share a channel (each takes every 8th CTA of that channel's list, ascending) and combine with a
-  // fixed shuffle tree, so the summation order is a function of the launch geometry only.
-  if (p.stat_scratch != nullptr && *last_flag != 0u) {
+  // Deterministic BatchNorm statistics: the last kTailCtas CTAs to finish add the partial sums of all CTAs in CTA
+  // order, each for its own slice of the channels (role r takes quads [nq*r/R, nq*(r+1)/R)).  L lanes share a quad of
+  // 4 channels (each takes every L-th CTA of that N tile's list, ascending) and combine with a fixed shuffle tree, so
+  // the summation order is a function of the launch geometry only — not of which CTA ends up in which role.
+  // The tail CTAs wait (bounded spin) until every CTA of the grid has published its partials; at most kTailCtas SMs
+  // are held while waiting, so CTAs that have not been scheduled yet always find room.
+  // This code runs once per launch from a cold instruction cache (a single CTA walking an unrolled 7 KB version of it
+  // cost 10-12 us per launch): it is kept small, rolled and parallel on purpose.
+  if (p.stat_scratch != nullptr && *last_flag != 0u && !DMPI_DBG(p, 16)) {
+    const int role = static_cast<int>(*last_flag) - 1;
     const int grid = static_cast<int>(gridDim.x);
+    const int R = grid < kTailCtas ? grid : kTailCtas;
+    uint32_t* ctr = reinterpret_cast<uint32_t*>(p.stat_scratch);  // [0] finished CTAs, [1] finished tail roles
+    if (threadIdx.x == 0) {
+      uint64_t t0 = 0;
+      uint32_t spins = 0, seen;
+      do {
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(ctr) : "memory");
+        if ((++spins & 0xFFFu) == 0) {
+          const uint64_t now = globaltimer_ns();
+          if (t0 == 0) t0 = now;
+          else if (DMPI_MBAR_TIMEOUT_NS != 0ull && now - t0 > DMPI_MBAR_TIMEOUT_NS) __trap();
+        }
+      } while (seen < static_cast<uint32_t>(grid));
+    }
+    __syncthreads();
     const int nnt = p.num_n_tiles;
-    // L lanes share a quad of 4 channels (16-byte loads); each lane takes every L-th CTA of the tile's list, ascending
     const int cpt = ((grid / CG + nnt - 1) / nnt) * CG;  // CTAs per N tile (upper bound)
-    // L lanes per quad: as many as keep the whole channel range in ONE pass (each pass is a chain of L2 round trips)
-    const int nq_all = p.stat_mod >> 2;
-    int L = 32;
-    while (L > 1 && (kThreads / L < nq_all || L > cpt)) L >>= 1;
+    const int nq = p.stat_mod >> 2;
+    const int q_lo = static_cast<int>(static_cast<long long>(nq) * role / R);
+    const int q_hi = static_cast<int>(static_cast<long long>(nq) * (role + 1) / R);
+    int L = 32;  // lanes per quad: as many as still cover this role's quads in one pass
+    while (L > 1 && (kThreads / L < q_hi - q_lo || L > cpt)) L >>= 1;
     const int l = threadIdx.x & (L - 1);
-    const int quads_per_pass = kThreads / L;
-    const int nquads = p.stat_mod >> 2;
-    for (int q0 = 0; q0 < nquads; q0 += quads_per_pass) {
-      const int quad = q0 + threadIdx.x / L;
+    const int per_pass = kThreads / L;
+    for (int q0 = q_lo; q0 < q_hi; q0 += per_pass) {
+      const int quad = q0 + static_cast<int>(threadIdx.x) / L;
       float4 t1 = make_float4(0.f, 0.f, 0.f, 0.f), t2 = t1;
-      if (quad < nquads) {
+      if (quad < q_hi) {
         for (int gcol = quad * 4; gcol < p.n_out; gcol += p.stat_mod) {  // column groups that share the channels (convT)
           const int n_blk = gcol / BN, cc = gcol - n_blk * BN;
           const float* base = p.stat_scratch + kStatHdr + cc;
           // list entry idx of this tile: CTA blockIdx = CG * (n_blk + (idx / CG) * nnt) + idx % CG
-          int idx = l;
-          while (true) {
+#pragma unroll 1
+          for (int idx = l; idx < cpt; idx += kDetInFlight * L) {
             float4 a1[kDetInFlight], a2[kDetInFlight];
-            int nv = 0;
 #pragma unroll
-            for (int k = 0; k < kDetInFlight; ++k) {  // independent CTAs in flight, added in list order below
+            for (int k = 0; k < kDetInFlight; ++k) {  // independent loads in flight; entries past the list add zeros
               const int id = idx + k * L;
               const int b = CG * (n_blk + (id / CG) * nnt) + (id % CG);
-              if (b < grid) {
+              a1[k] = a2[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (id < cpt && b < grid) {
                 a1[k] = __ldcg(reinterpret_cast<const float4*>(base + static_cast<size_t>(b * 2 + 0) * BN));
                 a2[k] = __ldcg(reinterpret_cast<const float4*>(base + static_cast<size_t>(b * 2 + 1) * BN));
-                nv = k + 1;
               }
             }
 #pragma unroll
             for (int k = 0; k < kDetInFlight; ++k) {
-              if (k < nv) {
-                t1.x += a1[k].x; t1.y += a1[k].y; t1.z += a1[k].z; t1.w += a1[k].w;
-                t2.x += a2[k].x; t2.y += a2[k].y; t2.z += a2[k].z; t2.w += a2[k].w;
-              }
+              t1.x += a1[k].x; t1.y += a1[k].y; t1.z += a1[k].z; t1.w += a1[k].w;
+              t2.x += a2[k].x; t2.y += a2[k].y; t2.z += a2[k].z; t2.w += a2[k].w;
             }
-            if (nv < kDetInFlight) break;
-            idx += kDetInFlight * L;
           }
         }
       }
+#pragma unroll 1
       for (int o = 1; o < L; o <<= 1) {
         t1.x += __shfl_xor_sync(0xffffffffu, t1.x, o); t1.y += __shfl_xor_sync(0xffffffffu, t1.y, o);
         t1.z += __shfl_xor_sync(0xffffffffu, t1.z, o); t1.w += __shfl_xor_sync(0xffffffffu, t1.w, o);
         t2.x += __shfl_xor_sync(0xffffffffu, t2.x, o); t2.y += __shfl_xor_sync(0xffffffffu, t2.y, o);
         t2.z += __shfl_xor_sync(0xffffffffu, t2.z, o); t2.w += __shfl_xor_sync(0xffffffffu, t2.w, o);
       }
-      if (l == 0 && quad < nquads) {
+      if (l == 0 && quad < q_hi) {
         float4* s1 = reinterpret_cast<float4*>(p.stat_sum + quad * 4);
         float4* s2 = reinterpret_cast<float4*>(p.stat_sq + quad * 4);
         float4 v1 = *s1, v2 = *s2;
@@ -830,7 +848,11 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
         *s2 = v2;
       }
     }
-    if (threadIdx.x == 0) *reinterpret_cast<uint32_t*>(p.stat_scratch) = 0u;  // ready for the next launch
+    __syncthreads();
+    if (threadIdx.x == 0 && atomicAdd(&ctr[1], 1u) == static_cast<uint32_t>(R - 1)) {
+      ctr[1] = 0u;  // the last role re-arms both counters for the next launch (stream order makes this visible)
+      ctr[0] = 0u;
+    }
   }
 }
 

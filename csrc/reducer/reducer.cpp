@@ -6,13 +6,18 @@
 //   * gradients ARE views into the flat bucket arena, so there is no copy-in / copy-out;
 //   * buckets are planned once, in reverse registration order (~ gradient-ready order), with the same
 //     size rule as torch (first bucket 1 MiB, then 25 MiB; a tensor is added before the cap is checked);
-//   * a bucket is launched only when it AND every earlier bucket is complete, so every rank issues the
-//     collectives in the same order (required by the peer-to-peer flag protocol);
+//   * buckets are launched in a fixed LAUNCH ORDER (a bucket goes out once it and every bucket before it in that
+//     order is complete), so every rank issues the collectives in the same sequence (required by the peer-to-peer
+//     flag protocol).  The order starts as 0, 1, 2, ... and is re-derived once from the gradient-ready order
+//     observed in the first backward pass (dmpi_reducer_rebuild, the counterpart of c10d's bucket rebuild): buckets
+//     are contiguous ranges of the gradient arena and stay where they are, but a bucket that holds a late gradient
+//     (a parked downsample dgrad, a UNet skip branch) no longer holds back the buckets behind it;
 //   * the launch itself is a C callback (CUDA glue in reducer_cuda.cu) — Python only forwards the
 //     autograd hook.  On the CPU/gloo path no callback is installed and the ready buckets are returned.
 #include <stdint.h>
 #include <string.h>
 
+#include <algorithm>
 #include <mutex>
 #include <vector>
 
@@ -47,7 +52,8 @@ struct Reducer {
   std::vector<int> pending;         // per bucket, this iteration
   std::vector<uint8_t> ready;       // per param, this iteration
   std::vector<int> ready_order;     // params in the order their gradients arrived (for plan rebuild)
-  int next_bucket = 0;              // first bucket not yet launched
+  std::vector<int> launch_order;    // buckets in the order they are launched
+  int next_bucket = 0;              // position in launch_order of the first bucket not yet launched
   long long double_marks = 0;
   dmpi_launch_cb cb = nullptr;
   void* cb_ctx = nullptr;
@@ -63,6 +69,8 @@ void* dmpi_reducer_create(int n_params, const int* bucket_of, int n_buckets) {
   r->pending = r->bucket_size;
   r->ready.assign(n_params, 0);
   r->ready_order.reserve(n_params);
+  r->launch_order.resize(n_buckets);
+  for (int b = 0; b < n_buckets; ++b) r->launch_order[b] = b;
   return r;
 }
 
@@ -99,8 +107,8 @@ int dmpi_reducer_mark_ready(void* h, int param, int* out_buckets, int max_out) {
   r->ready_order.push_back(param);
   r->pending[r->bucket_of[param]]--;
   int n = 0;
-  while (r->next_bucket < r->n_buckets && r->pending[r->next_bucket] == 0) {
-    const int b = r->next_bucket++;
+  while (r->next_bucket < r->n_buckets && r->pending[r->launch_order[r->next_bucket]] == 0) {
+    const int b = r->launch_order[r->next_bucket++];
     if (r->cb) r->cb(r->cb_ctx, b);
     if (n < max_out) out_buckets[n] = b;
     ++n;
@@ -123,6 +131,45 @@ int dmpi_reducer_ready_order(void* h, int* out, int max_out) {
   const int n = static_cast<int>(r->ready_order.size());
   for (int i = 0; i < n && i < max_out; ++i) out[i] = r->ready_order[i];
   return n;
+}
+
+// Re-derives the launch order from the gradient-ready order of the iteration that just finished (call it only after a
+// complete backward pass): buckets sorted by the arrival position of their LAST gradient, ties by index.  Returns the
+// number of buckets whose position changed, or -1 if the iteration was incomplete (order left as it was).
+int dmpi_reducer_rebuild(void* h) {
+  Reducer* r = static_cast<Reducer*>(h);
+  std::lock_guard<std::mutex> lk(r->mu);
+  if (static_cast<int>(r->ready_order.size()) != r->n_params) return -1;
+  std::vector<int> last(r->n_buckets, -1);
+  for (int pos = 0; pos < r->n_params; ++pos) last[r->bucket_of[r->ready_order[pos]]] = pos;
+  std::vector<int> order(r->n_buckets);
+  for (int b = 0; b < r->n_buckets; ++b) order[b] = b;
+  std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return last[a] < last[b]; });
+  int moved = 0;
+  for (int i = 0; i < r->n_buckets; ++i) moved += order[i] != r->launch_order[i];
+  r->launch_order = order;
+  return moved;
+}
+
+// Installs a launch order (a permutation of 0..n_buckets-1; e.g. back to the identity when ranks disagree).
+int dmpi_reducer_set_launch_order(void* h, const int* order, int n) {
+  Reducer* r = static_cast<Reducer*>(h);
+  std::lock_guard<std::mutex> lk(r->mu);
+  if (n != r->n_buckets) return -1;
+  std::vector<uint8_t> seen(n, 0);
+  for (int i = 0; i < n; ++i) {
+    if (order[i] < 0 || order[i] >= n || seen[order[i]]) return -2;
+    seen[order[i]] = 1;
+  }
+  r->launch_order.assign(order, order + n);
+  return 0;
+}
+
+int dmpi_reducer_launch_order(void* h, int* out, int max_out) {
+  Reducer* r = static_cast<Reducer*>(h);
+  std::lock_guard<std::mutex> lk(r->mu);
+  for (int i = 0; i < r->n_buckets && i < max_out; ++i) out[i] = r->launch_order[i];
+  return r->n_buckets;
 }
 
 // FNV-1a over the bucket layout, exchanged through the store so ranks can assert identical plans

@@ -23,6 +23,8 @@ struct ReducerCuda {
   std::vector<long long> off, bytes;
   std::vector<cudaEvent_t> ready;
   cudaEvent_t done = nullptr;
+  cudaEvent_t fwd_done = nullptr, bcast_done = nullptr;  // buffer broadcast on the comm stream (see side_broadcast)
+  bool bcast_pending = false;
   cudaStream_t compute = nullptr, comm = nullptr;
   bool own_comm = false;
   long long oneshot_max_bytes = 0, slot_bytes = 0;
@@ -46,6 +48,8 @@ extern "C" void* dmpi_reducer_cuda_create(const dmpi_comm_ptrs* ptrs, int n_buck
   r->ready.resize(n_buckets);
   for (auto& e : r->ready) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
   cudaEventCreateWithFlags(&r->done, cudaEventDisableTiming);
+  cudaEventCreateWithFlags(&r->fwd_done, cudaEventDisableTiming);
+  cudaEventCreateWithFlags(&r->bcast_done, cudaEventDisableTiming);
   int lo = 0, hi = 0;
   cudaDeviceGetStreamPriorityRange(&lo, &hi);
   cudaStreamCreateWithPriority(&r->comm, cudaStreamNonBlocking, hi);  // highest priority: comm blocks get SMs first
@@ -54,6 +58,7 @@ extern "C" void* dmpi_reducer_cuda_create(const dmpi_comm_ptrs* ptrs, int n_buck
   r->oneshot_max_bytes = oneshot_max_bytes;
   r->slot_bytes = slot_bytes;
   r->nblocks = nblocks;
+  if (const char* e = getenv("DMPI_COMM_BLOCKS")) r->nblocks = atoi(e) > 0 ? atoi(e) : nblocks;
   r->wire_bf16 = wire_bf16;
   // profiles/allreduce_sweep_w8.json: NVLS beats two-shot at every size above the one-shot range at W=8, loses at W=2
   r->use_nvls = ptrs->mc_data != nullptr && ptrs->world > 2;
@@ -66,6 +71,8 @@ extern "C" void dmpi_reducer_cuda_destroy(void* h) {
   if (!r) return;
   for (auto& e : r->ready) cudaEventDestroy(e);
   cudaEventDestroy(r->done);
+  cudaEventDestroy(r->fwd_done);
+  cudaEventDestroy(r->bcast_done);
   if (r->own_comm) cudaStreamDestroy(r->comm);
   delete r;
 }
@@ -106,6 +113,33 @@ extern "C" int dmpi_reducer_cuda_finalize(void* h) {
   const int e = r->last_error;
   r->last_error = 0;
   return e;
+}
+
+// Per-iteration buffer broadcast (BatchNorm running statistics, rank 0 -> all) OFF the forward's critical
+// path: torch DDP broadcasts at the head of forward i+1 what rank 0 holds after forward i; nothing reads or writes the
+// buffers between the end of forward i and the BatchNorm kernels of forward i+1, so the same bytes can travel any time
+// in between.  Called right after the forward pass was enqueued: the comm stream waits for the forward, runs the
+// broadcast kernel (its two cross-GPU barriers overlap the loss and the first backward kernels) and the bucket
+// all-reduces queue up behind it.  The compute stream picks the result up in dmpi_reducer_cuda_join_broadcast (head of
+// the next forward) or, earlier, through the `done` event of finalize (same stream, later).
+extern "C" int dmpi_reducer_cuda_side_broadcast(void* h, long long off_bytes, long long nbytes, int root, int nblocks,
+                                                void* compute_stream) {
+  ReducerCuda* r = static_cast<ReducerCuda*>(h);
+  if (r->world <= 1 || nbytes <= 0) return 0;
+  cudaStream_t cs = static_cast<cudaStream_t>(compute_stream);
+  cudaEventRecord(r->fwd_done, cs);
+  cudaStreamWaitEvent(r->comm, r->fwd_done, 0);
+  const int rc = dmpi_broadcast(&r->ptrs, off_bytes, nbytes, root, nblocks, 0, r->comm);
+  cudaEventRecord(r->bcast_done, r->comm);
+  r->bcast_pending = true;
+  return rc;
+}
+
+extern "C" void dmpi_reducer_cuda_join_broadcast(void* h, void* stream) {
+  ReducerCuda* r = static_cast<ReducerCuda*>(h);
+  if (!r->bcast_pending) return;
+  cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), r->bcast_done, 0);
+  r->bcast_pending = false;
 }
 
 extern "C" void* dmpi_reducer_cuda_comm_stream(void* h) { return static_cast<ReducerCuda*>(h)->comm; }

@@ -130,6 +130,9 @@ def _bind_host(lib) -> None:
     _sig(lib, "dmpi_reducer_pending", I, [VP])
     _sig(lib, "dmpi_reducer_ready_order", I, [VP, C.POINTER(I), I])
     _sig(lib, "dmpi_reducer_set_launch_cb", None, [VP, VP, VP])
+    _sig(lib, "dmpi_reducer_rebuild", I, [VP])
+    _sig(lib, "dmpi_reducer_set_launch_order", I, [VP, C.POINTER(I), I])
+    _sig(lib, "dmpi_reducer_launch_order", I, [VP, C.POINTER(I), I])
     _sig(lib, "dmpi_plan_hash", C.c_uint64, [C.POINTER(I64), C.POINTER(I), I])
 
 
@@ -222,6 +225,8 @@ def _bind_cuda(lib) -> None:
     _sig(lib, "dmpi_reducer_cuda_begin", None, [VP, VP])
     _sig(lib, "dmpi_reducer_cuda_launch", None, [VP, I])
     _sig(lib, "dmpi_reducer_cuda_finalize", I, [VP])
+    _sig(lib, "dmpi_reducer_cuda_side_broadcast", I, [VP, I64, I64, I, I, VP])
+    _sig(lib, "dmpi_reducer_cuda_join_broadcast", None, [VP, VP])
     _sig(lib, "dmpi_reducer_cuda_comm_stream", VP, [VP])
     _sig(lib, "dmpi_reducer_cuda_launched", I, [VP])
     _sig(lib, "dmpi_reducer_cuda_launch_fn", VP, [])

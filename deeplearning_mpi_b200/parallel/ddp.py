@@ -15,16 +15,21 @@ What happens underneath is different from c10d:
   C++ reducer counts readiness and launches the fused (sum * 1/world) all-reduce kernel for bucket b on a
   high-priority comm stream as soon as buckets 0..b are complete — overlapping the rest of backward.
 * every training forward re-broadcasts rank 0's buffers (BatchNorm running statistics) like
-  ``broadcast_buffers=True`` does — with ONE kernel over the contiguous buffer range.  Forwards under
+  ``broadcast_buffers=True`` does — with ONE kernel over the contiguous buffer range, issued on the comm stream right
+  after the forward pass was enqueued (the bytes torch would send at the head of the next forward), so its two
+  cross-GPU barriers overlap the backward pass instead of delaying the next forward.  Forwards under
   ``torch.no_grad()`` never communicate, so a rank-0-only evaluation between epochs
   (ref:pytorch/resnet/main.py:136-139) cannot dead-lock the other ranks.
 * ``no_sync()`` accumulates locally.  On gloo / NCCL-fallback groups the same reducer drives
   ``torch.distributed.all_reduce`` on the flat bucket views.
+* after the first complete backward pass the bucket LAUNCH ORDER is re-derived from the observed gradient-ready order
+  (c10d rebuilds its buckets at the same point) and cross-checked between the ranks.
 """
 from __future__ import annotations
 
 import contextlib
 import ctypes as C
+import os
 from typing import List, Optional
 
 import torch
@@ -118,6 +123,10 @@ class DistributedDataParallel(nn.Module):
         self._armed = False
         self._finalize_queued = False
         self._marked = bytearray(len(slots))
+        self._uid = f"{st.n_comms}_{self.plan_hash & 0xffffffff:x}"  # same on every rank: comms are created collectively
+        self._order_final = os.environ.get("DMPI_BUCKET_REBUILD", "1") != "1"   # launch order not yet rebuilt
+        self._bcast_inline = os.environ.get("DMPI_BCAST_INLINE", "0") == "1"    # A/B: broadcast at the head of forward
+        self.launch_order = list(range(self.n_buckets))
         self._install_hooks()
 
     # ------------------------------------------------------------------ construction helpers
@@ -226,6 +235,38 @@ class DistributedDataParallel(nn.Module):
         for w in self._pending_work:
             w.wait()
         self._pending_work.clear()
+        if not self._order_final:
+            self._rebuild_launch_order()
+
+    def _rebuild_launch_order(self) -> None:
+        """Once, after the first complete backward pass: launch buckets in the order in which they became complete
+        (every rank observed the same autograd graph; the result is still compared across ranks, and on any
+        disagreement all ranks keep the initial order)."""
+        self._order_final = True
+        host = N.host()
+        if host.dmpi_reducer_rebuild(self._reducer) < 0:
+            return
+        buf = (C.c_int * max(self.n_buckets, 1))()
+        host.dmpi_reducer_launch_order(self._reducer, buf, self.n_buckets)
+        order = [buf[i] for i in range(self.n_buckets)]
+        if self.world > 1:
+            st = self._st
+            if st.kind == "p2p":
+                tag = f"order{self._uid}"
+                mine = ",".join(map(str, order)).encode()
+                agree = all(o == mine for o in st.store.all_gather(tag, self.rank, self.world, mine))
+            else:
+                import torch.distributed as tdist
+
+                t = torch.tensor(order, dtype=torch.int64, device=self.arena.device if self._is_cuda else "cpu")
+                parts = [torch.zeros_like(t) for _ in range(self.world)]
+                tdist.all_gather(parts, t)
+                agree = all(torch.equal(p, parts[0]) for p in parts)
+            if not agree:
+                ident = (C.c_int * self.n_buckets)(*range(self.n_buckets))
+                host.dmpi_reducer_set_launch_order(self._reducer, ident, self.n_buckets)
+                order = list(range(self.n_buckets))
+        self.launch_order = order
 
     def _sync_buffers(self) -> None:
         if self.world == 1 or not self.broadcast_buffers or self.arena.buffer_bytes == 0:
@@ -265,15 +306,29 @@ class DistributedDataParallel(nn.Module):
             self.require_backward_grad_sync = old
 
     def forward(self, *inputs, **kwargs):
-        if torch.is_grad_enabled() and self.training:
+        sync = torch.is_grad_enabled() and self.training
+        side = (sync and self._cuda_red is not None and self.world > 1 and self.broadcast_buffers
+                and self.arena.buffer_bytes > 0 and not self._bcast_inline)
+        if self._cuda_red is not None:
+            # a buffer broadcast issued after the previous forward must have landed before BatchNorm touches the buffers
+            N.cuda().dmpi_reducer_cuda_join_broadcast(self._cuda_red, N.stream_ptr())
+        if sync:
             if self._fault.active and self.require_backward_grad_sync:
                 self._fault.tick(self.rank)
-            self._sync_buffers()
+            if not side:
+                self._sync_buffers()
             if self.require_backward_grad_sync:
                 self._arm()
             else:
                 self._armed = False
-        return self.module(*inputs, **kwargs)
+        out = self.module(*inputs, **kwargs)
+        if side:
+            rc = N.cuda().dmpi_reducer_cuda_side_broadcast(self._cuda_red, self._off["buffers"],
+                                                           _round_up(self.arena.buffer_bytes, 256), 0, 4, N.stream_ptr())
+            N.count_launch()
+            if rc != 0:
+                raise RuntimeError(f"DDP: buffer broadcast launch failed ({rc})")
+        return out
 
     def _arm(self) -> None:
         """Prepare the reducer for one synchronising backward pass (c10d: prepare_for_backward)."""

@@ -307,3 +307,71 @@ def test_fault_injector_spec():
         FaultInjector("rank=1,when=now")
     with pytest.raises(ValueError):
         FaultInjector("rank=1,step=1,kind=explode")
+
+
+def test_reducer_launch_order_rebuild():
+    """Bucket launch order re-derived from the observed gradient-ready order: a bucket holding a late
+    gradient no longer blocks the buckets behind it; the order is a permutation and can be reset."""
+    import ctypes as C
+
+    from deeplearning_mpi_b200 import _native as N
+
+    host = N.host()
+    bucket_of = (C.c_int * 6)(0, 0, 1, 1, 2, 2)
+    r = host.dmpi_reducer_create(6, bucket_of, 3)
+    out = (C.c_int * 3)()
+    launched = []
+
+    def mark(i):
+        n = host.dmpi_reducer_mark_ready(r, i, out, 3)
+        assert n >= 0
+        launched.extend(out[j] for j in range(n))
+
+    # iteration 0: parameter 1 (bucket 0) arrives last -> with the initial order nothing can go out before it
+    host.dmpi_reducer_reset(r)
+    for i in (0, 2, 3, 4, 5):
+        mark(i)
+    assert launched == []
+    mark(1)
+    assert launched == [0, 1, 2]
+    assert host.dmpi_reducer_pending(r) == 0
+    assert host.dmpi_reducer_rebuild(r) == 3
+    host.dmpi_reducer_launch_order(r, out, 3)
+    assert [out[i] for i in range(3)] == [1, 2, 0]
+    # iteration 1, same arrival order: buckets 1 and 2 leave as soon as they are complete
+    launched.clear()
+    host.dmpi_reducer_reset(r)
+    mark(0); mark(2); mark(3)
+    assert launched == [1]
+    mark(4); mark(5)
+    assert launched == [1, 2]
+    mark(1)
+    assert launched == [1, 2, 0]
+    # incomplete iteration: rebuild refuses; bad permutations are rejected; identity can be restored
+    host.dmpi_reducer_reset(r)
+    mark(0)
+    assert host.dmpi_reducer_rebuild(r) == -1
+    assert host.dmpi_reducer_set_launch_order(r, (C.c_int * 3)(0, 0, 1), 3) == -2
+    assert host.dmpi_reducer_set_launch_order(r, (C.c_int * 3)(0, 1, 2), 3) == 0
+    host.dmpi_reducer_destroy(r)
+
+
+def test_frozen_parameters_stay_out_of_buckets_and_updates():
+    """requires_grad=False parameters sit behind the trainable ones in the arena: not bucketed, not updated."""
+    from deeplearning_mpi_b200 import optim
+    from deeplearning_mpi_b200.utils.arena import ensure_arena
+
+    torch.manual_seed(0)
+    m = torch.nn.Sequential(torch.nn.Linear(8, 16), torch.nn.ReLU(), torch.nn.Linear(16, 4))
+    m[0].weight.requires_grad_(False)
+    frozen_before = m[0].weight.detach().clone()
+    arena = ensure_arena(m)
+    assert arena.n_trainable == 3 and len(arena.slots) == 4 and arena.slots[-1].param is m[0].weight
+    assert arena.total_trainable <= arena.slots[-1].offset
+    opt = optim.SGD([p for p in m.parameters() if p.requires_grad], lr=0.1, momentum=0.9, weight_decay=1e-2)
+    for _ in range(2):
+        opt.zero_grad()
+        m(torch.randn(5, 8)).square().mean().backward()
+        opt.step()
+    assert torch.equal(m[0].weight, frozen_before) and m[0].weight.grad is None
+    assert not torch.equal(m[2].weight, torch.zeros_like(m[2].weight))
