@@ -364,6 +364,22 @@ __global__ void __launch_bounds__(kCommThreads) recv_kernel(uint4* __restrict__ 
   if (threadIdx.x == 0) st_release_sys(peer_ack, seq);
 }
 
+// Plain grid-stride copy with kInFlight vectors per thread in flight: the measuring stick for the NVLink roofline
+// (src or dst is a mapped peer pointer: peer read or peer write bandwidth; both local: the HBM copy rate).
+__global__ void __launch_bounds__(kCommThreads) peer_copy_kernel(uint4* __restrict__ dst, const uint4* __restrict__ src,
+                                                                 long long nvec) {
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i0 = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i0 < nvec; i0 += stride * kInFlight) {
+    uint4 v[kInFlight];
+#pragma unroll
+    for (int u = 0; u < kInFlight; ++u)
+      if (i0 + u * stride < nvec) v[u] = ld_peer_u4(src + i0 + u * stride);
+#pragma unroll
+    for (int u = 0; u < kInFlight; ++u)
+      if (i0 + u * stride < nvec) st_peer_u4(dst + i0 + u * stride, v[u]);
+  }
+}
+
 // Emulated pair for single-GPU tests: one launch, block 0 sends and block 1 receives.
 __global__ void __launch_bounds__(kCommThreads) sendrecv_emulated_kernel(const uint4* src, uint4* mailbox, uint4* dst,
                                                                          long long nvec, uint32_t* seq_flag,
@@ -469,6 +485,14 @@ extern "C" int dmpi_broadcast(const dmpi_comm_ptrs* ptrs, long long off_bytes, l
   const int nb = clamp_blocks(nblocks, nvec);
   dim3 grid(nb, emulate_ranks > 0 ? emulate_ranks : 1);
   broadcast_kernel<<<grid, kCommThreads, 0, static_cast<cudaStream_t>(stream)>>>(*ptrs, off_bytes, nvec, root);
+  return cudaGetLastError() == cudaSuccess ? 0 : -2;
+}
+
+extern "C" int dmpi_peer_copy(void* dst, const void* src, long long nbytes, int nblocks, void* stream) {
+  if (nbytes % 16) return -1;
+  if (nblocks < 1) nblocks = 1;
+  peer_copy_kernel<<<nblocks, kCommThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<uint4*>(dst), static_cast<const uint4*>(src), nbytes / 16);
   return cudaGetLastError() == cudaSuccess ? 0 : -2;
 }
 

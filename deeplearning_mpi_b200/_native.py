@@ -216,6 +216,7 @@ def _bind_cuda(lib) -> None:
     _sig(lib, "dmpi_allreduce_oneshot", I, [VP, I64, I64, I, F, I64, I, I, VP])
     _sig(lib, "dmpi_broadcast", I, [VP, I64, I64, I, I, I, VP])
     _sig(lib, "dmpi_comm_set_timeout", I, [C.c_double])
+    _sig(lib, "dmpi_peer_copy", I, [VP, VP, I64, I, VP])
     _sig(lib, "dmpi_send", I, [VP, VP, I64, VP, VP, C.c_uint32, VP])
     _sig(lib, "dmpi_recv", I, [VP, VP, I64, VP, VP, C.c_uint32, VP])
     _sig(lib, "dmpi_sendrecv_emulated", I, [VP, VP, VP, I64, VP, VP, C.c_uint32, VP])

@@ -93,6 +93,8 @@ int dmpi_allreduce_oneshot(const dmpi_comm_ptrs* ptrs, long long off_bytes, long
 /* Copies [off_bytes, +nbytes) of root's data region into the same range of every rank. */
 int dmpi_broadcast(const dmpi_comm_ptrs* ptrs, long long off_bytes, long long nbytes, int root, int nblocks,
                    int emulate_ranks, void* stream);
+/* Grid-stride 16-byte copy (either pointer may be a mapped peer address): NVLink read / write bandwidth probe. */
+int dmpi_peer_copy(void* dst, const void* src, long long nbytes, int nblocks, void* stream);
 /* Point-to-point: message number `seq` (1, 2, ...) of the (source, destination) pair. */
 int dmpi_send(const void* src, void* peer_mailbox, long long nbytes, uint32_t* peer_seq, const uint32_t* my_ack,
               uint32_t seq, void* stream);

@@ -61,6 +61,40 @@ comm.allreduce(0, n * 2, 1.0, dtype=1, algo="twoshot")
 torch.cuda.synchronize()
 assert (stage_b.float() - refb).abs().max().item() <= 3e-2 * refb.abs().max().item()
 
+# ---- flag-protocol stress: thousands of back-to-back collectives of random kind / size / block count, every rank
+# delayed by its own random amount before each launch (sizes straddle the one-shot / two-shot / NVLS crossovers).
+# Inputs are (rank + 1) * c, so the expected value is known without an oracle call; mismatches are counted on the
+# device and read once at the end.
+import random  # noqa: E402
+
+rng_all = random.Random(4242)          # same sequence of operations on every rank
+rng_me = random.Random(977 + rank)     # this rank's own delays
+n_stress = int(os.environ.get("DMPI_STRESS_ITERS", "3000"))
+bad = torch.zeros((), dtype=torch.int32, device=dev)
+tri = world * (world + 1) / 2
+for it in range(n_stress):
+    kind = rng_all.choice(["oneshot", "oneshot", "twoshot", "nvls", "bcast"])
+    if kind == "nvls" and not comm.has_multicast:
+        kind = "twoshot"
+    n = rng_all.choice([4, 64, 1024, 16384, 65532, 65536, 65540, 262144, 1 << 20]) + 4 * rng_all.randrange(0, 8)
+    if kind == "oneshot" and n * 4 > comm.slot_bytes:
+        n = comm.slot_bytes // 4
+    nb = rng_all.choice([1, 3, 8, 16, 32, 64])
+    c = float(1 + it % 7)
+    if rng_me.random() < 0.5:
+        torch.cuda._sleep(rng_me.randrange(0, 300000))   # up to ~150 us of skew
+    if kind == "bcast":
+        root = rng_all.randrange(world)
+        stage[:n].fill_(c * (rank + 1))
+        comm.broadcast(0, n * 4, root, nblocks=min(nb, 16))
+        bad += (stage[:n] != c * (root + 1)).any().int()
+    else:
+        stage[:n].fill_(c * (rank + 1))
+        comm.allreduce(0, n * 4, 1.0, algo=kind, nblocks=nb)
+        bad += (stage[:n] != c * tri).any().int()
+torch.cuda.synchronize()
+assert bad.item() == 0, f"flag-protocol stress: {bad.item()} of {n_stress} collectives returned wrong data"
+
 # ---- broadcast + generic all_reduce / broadcast on user tensors
 t = torch.full((1000,), float(rank), device=dev)
 dist.broadcast(t, src=world - 1)
@@ -118,6 +152,10 @@ for it in range(4):
     opt.step()
     losses.append(loss.item())
 all_equal(ddp.arena.flat_p, "parameters diverged")
+# BatchNorm buffers: rank 0's running statistics reach every rank (broadcast issued on the comm stream after the
+# forward pass, joined by finalize / the next forward)
+all_equal(ddp.arena.flat_b, "buffers differ across ranks after the per-iteration broadcast")
+assert sorted(ddp.launch_order) == list(range(ddp.n_buckets)), ddp.launch_order
 
 # ---- the reducer averages exactly: inject a known, rank-dependent gradient arena and run the bucket machinery
 class _Trigger(torch.autograd.Function):
