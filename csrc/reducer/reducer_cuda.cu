@@ -25,6 +25,7 @@ struct ReducerCuda {
   cudaEvent_t done = nullptr;
   cudaEvent_t fwd_done = nullptr, bcast_done = nullptr;  // buffer broadcast on the comm stream (see side_broadcast)
   bool bcast_pending = false;
+  bool bcast_captured = false;  // the pending broadcast was recorded while its stream was being captured into a graph
   cudaStream_t compute = nullptr, comm = nullptr;
   bool own_comm = false;
   long long oneshot_max_bytes = 0, slot_bytes = 0;
@@ -110,6 +111,7 @@ extern "C" int dmpi_reducer_cuda_finalize(void* h) {
   ReducerCuda* r = static_cast<ReducerCuda*>(h);
   if (r->launched != static_cast<int>(r->ready.size())) return -1;
   cudaStreamWaitEvent(r->compute, r->done, 0);
+  r->bcast_pending = false;  // `done` was recorded on the comm stream after the broadcast: already joined
   const int e = r->last_error;
   r->last_error = 0;
   return e;
@@ -132,14 +134,23 @@ extern "C" int dmpi_reducer_cuda_side_broadcast(void* h, long long off_bytes, lo
   const int rc = dmpi_broadcast(&r->ptrs, off_bytes, nbytes, root, nblocks, 0, r->comm);
   cudaEventRecord(r->bcast_done, r->comm);
   r->bcast_pending = true;
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing(cs, &cap);
+  r->bcast_captured = cap == cudaStreamCaptureStatusActive;
   return rc;
 }
 
 extern "C" void dmpi_reducer_cuda_join_broadcast(void* h, void* stream) {
   ReducerCuda* r = static_cast<ReducerCuda*>(h);
   if (!r->bcast_pending) return;
-  cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), r->bcast_done, 0);
   r->bcast_pending = false;
+  // An event may only be waited for on the side of the capture boundary it was recorded on.  Crossing it needs no
+  // wait: stream capture begins and ends with the device quiesced (torch.cuda.graph synchronises before capturing, and
+  // a captured step joins the comm stream in its own finalize).
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing(static_cast<cudaStream_t>(stream), &cap);
+  if ((cap == cudaStreamCaptureStatusActive) != r->bcast_captured) return;
+  cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), r->bcast_done, 0);
 }
 
 extern "C" void* dmpi_reducer_cuda_comm_stream(void* h) { return static_cast<ReducerCuda*>(h)->comm; }
