@@ -251,7 +251,7 @@ def build_reference(args, batch, size):
         import pytorch.unet.train as ref_train  # noqa: F401  (env parsing + helpers, unmodified)
 
         ref_train.set_random_seeds(42)
-        tdist.init_process_group("nccl")
+        _init_nccl_once(tdist)
         ddp = ref_train.build_model(False, "unused.pth")          # UNet(out_classes=1) -> .to(device) -> DDP
         opt = toptim.Adam(ddp.parameters(), lr=1e-4)
         crit = nn.BCEWithLogitsLoss()
@@ -274,7 +274,7 @@ def build_reference(args, batch, size):
         ref_main.resume = False
         ref_main.model_filepath = "unused.pth"
         ref_main.set_random_seeds()                                # cudnn.benchmark = True etc.
-        tdist.init_process_group("nccl")
+        _init_nccl_once(tdist)
         if args.model == "resnet18":
             ddp = ref_main.build_model()                           # the script's own builder, verbatim
         else:
@@ -299,9 +299,14 @@ def build_reference(args, batch, size):
         tdist.all_reduce(t, op=tdist.ReduceOp.MAX)
         return float(t.item())
 
+    # the NCCL group lives for the whole process (one init, every model of the run uses it; torn down in main())
     return dict(step=step, device=device, barrier=tdist.barrier, max_over_ranks=max_over_ranks, launches=lambda: 0,
-                finish=tdist.destroy_process_group, rank=tdist.get_rank(), world=tdist.get_world_size(),
-                backend="nccl")
+                finish=lambda: None, rank=tdist.get_rank(), world=tdist.get_world_size(), backend="nccl")
+
+
+def _init_nccl_once(tdist) -> None:
+    if not tdist.is_initialized():
+        tdist.init_process_group("nccl")
 
 
 # ---------------------------------------------------------------------------------------------- measurement
@@ -475,7 +480,34 @@ def main():
         if rec is not None:
             rec["secondary"] = extra
     if rec is not None:
-        print(json.dumps(rec))
+        print(json.dumps(rec), flush=True)
+    _final_teardown()
+
+
+def _final_teardown(grace_s: float = 30.0) -> None:
+    """The result line is out; leave.  Process-group teardown is collective in spirit (NCCL communicators, peer-mapped
+    arenas): a rank that is still tearing down while its peers' processes are already gone can wait forever, so a
+    watchdog ends the process (exit code 0: the measurement is complete) if teardown has not returned in time."""
+    import threading
+
+    def _bail():
+        time.sleep(grace_s)
+        os._exit(0)
+
+    threading.Thread(target=_bail, daemon=True).start()
+    try:
+        import torch.distributed as tdist
+
+        if tdist.is_initialized():
+            try:
+                tdist.barrier()
+            except Exception:
+                pass
+    except Exception:
+        pass
+    _force_teardown()
+    sys.stdout.flush()
+    os._exit(0)   # skip interpreter-exit destructors of CUDA / NCCL objects: nothing left to save
 
 
 if __name__ == "__main__":

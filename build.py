@@ -5,6 +5,7 @@ source snapshot; they are git-ignored):
 
   deeplearning_mpi_b200/_lib/libdmpi_host.so   TCP store + reducer core       (no CUDA dependency)
   deeplearning_mpi_b200/_lib/libdmpi_cuda.so   all sm_100a kernels + P2P arena + CUDA reducer glue
+  deeplearning_mpi_b200/_lib/dmpi_torch_hooks.so   C++ autograd hooks of the DDP wrapper (pybind11 module, links libtorch)
 
 Objects are rebuilt only when the content hash of the translation unit, its local headers and the
 flags changes.  Usage:  python build.py [--force] [--verbose]
@@ -34,7 +35,9 @@ NVCC_FLAGS += os.environ.get("DMPI_NVCC_EXTRA", "").split()  # e.g. -DDMPI_ABLAT
 CXX_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-Wall", "-pthread"]
 
 CUDA_SOURCES = sorted(str(p.relative_to(ROOT)) for p in (ROOT / "csrc").rglob("*.cu"))
-HOST_SOURCES = sorted(str(p.relative_to(ROOT)) for p in (ROOT / "csrc").rglob("*.cpp"))
+HOST_SOURCES = sorted(str(p.relative_to(ROOT)) for p in (ROOT / "csrc").rglob("*.cpp") if "hooks" not in p.parts)
+TORCH_EXT_SOURCE = ROOT / "csrc" / "hooks" / "autograd_hooks.cpp"   # links against libtorch: built separately
+TORCH_EXT_NAME = "dmpi_torch_hooks"
 
 
 def _headers_digest() -> str:
@@ -107,7 +110,42 @@ def build(force: bool = False, verbose: bool = False) -> dict[str, str]:
     link(host_lib, host_objs, ["-pthread"])
     link(cuda_lib, cuda_objs, ["-L/usr/local/cuda/lib64", "-lcudart", "-pthread", "-ldl",
                                "-Wl,-rpath,/usr/local/cuda/lib64"])
-    return {"host": str(host_lib), "cuda": str(cuda_lib)}
+    out = {"host": str(host_lib), "cuda": str(cuda_lib)}
+    ext = build_torch_ext(force)
+    if ext:
+        out["torch_hooks"] = ext
+    return out
+
+
+def build_torch_ext(force: bool = False) -> str:
+    """The pybind11 / libtorch module with the C++ autograd hooks.  Optional: when it cannot be built (no torch headers)
+    the DDP wrapper falls back to its Python hooks, so a failure here is reported and swallowed."""
+    out = LIB_DIR / f"{TORCH_EXT_NAME}.so"
+    stamp = OBJ_DIR / f"{TORCH_EXT_NAME}.hash"
+    try:
+        import sysconfig
+
+        import torch
+        from torch.utils import cpp_extension as ce
+
+        flags = ["-O2", "-std=c++17", "-fPIC", "-shared", "-pthread", f"-DTORCH_EXTENSION_NAME={TORCH_EXT_NAME}",
+                 "-DTORCH_API_INCLUDE_EXTENSION_H", f"-D_GLIBCXX_USE_CXX11_ABI={int(torch._C._GLIBCXX_USE_CXX11_ABI)}"]
+        incs = [f"-I{p}" for p in ce.include_paths()] + [f"-I{sysconfig.get_paths()['include']}"]
+        libdirs = ce.library_paths()
+        dig = hashlib.sha256(TORCH_EXT_SOURCE.read_bytes() + " ".join(flags).encode() + torch.__version__.encode()).hexdigest()
+        if not force and out.exists() and stamp.exists() and stamp.read_text() == dig:
+            return str(out)
+        cmd = ([CXX] + flags + incs + [str(TORCH_EXT_SOURCE), "-o", str(out)] + [f"-L{d}" for d in libdirs] +
+               ["-lc10", "-ltorch_cpu", "-ltorch", "-ltorch_python"] + [f"-Wl,-rpath,{d}" for d in libdirs])
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            print(f"[build] {TORCH_EXT_NAME}: compile failed, Python hooks will be used\n{r.stderr[-1500:]}")
+            return ""
+        stamp.write_text(dig)
+        return str(out)
+    except Exception as e:  # pragma: no cover
+        print(f"[build] {TORCH_EXT_NAME}: skipped ({type(e).__name__}: {e})")
+        return ""
 
 
 if __name__ == "__main__":

@@ -89,6 +89,44 @@ def cuda():
     return _cuda
 
 
+_torch_hooks = None
+
+
+def torch_hooks():
+    """The pybind11 module with the C++ autograd hooks (csrc/hooks/autograd_hooks.cpp), or None when it was not built
+    or DMPI_PY_HOOKS=1 asks for the Python hooks."""
+    global _torch_hooks
+    import os
+
+    if os.environ.get("DMPI_PY_HOOKS", "0") == "1":
+        return None
+    if _torch_hooks is None:
+        path = _LIB_DIR / "dmpi_torch_hooks.so"
+        if not path.exists():
+            _torch_hooks = False
+        else:
+            import importlib.util
+
+            import torch  # noqa: F401  (libtorch must be loaded before the extension)
+
+            spec = importlib.util.spec_from_file_location("dmpi_torch_hooks", str(path))
+            mod = importlib.util.module_from_spec(spec)
+            try:
+                spec.loader.exec_module(mod)
+                _torch_hooks = mod
+            except Exception as e:  # ABI mismatch after a torch upgrade: rebuild with `python build.py --force`
+                import warnings
+
+                warnings.warn(f"dmpi_torch_hooks.so could not be loaded ({e}); using the Python hooks")
+                _torch_hooks = False
+    return _torch_hooks or None
+
+
+def fn_addr(lib, name: str) -> int:
+    """Address of an exported C function (handed to the C++ hooks as a plain function pointer)."""
+    return C.cast(getattr(lib, name), C.c_void_p).value
+
+
 def cuda_available() -> bool:
     try:
         import torch

@@ -167,6 +167,27 @@ class DistributedDataParallel(nn.Module):
             self._broadcast_buffers_torch()
 
     def _install_hooks(self) -> None:
+        ext = N.torch_hooks() if self._cuda_red is not None else None
+        self._hx = None
+        if ext is not None:
+            # C++ path (csrc/hooks/autograd_hooks.cpp): post-accumulate-grad hooks and the finalize callback are C++
+            # objects; the fused kernels' wrappers report readiness through a pybind call that drops the GIL
+            from ..utils.arena import _logical_view
+
+            host, lib = N.host(), N.cuda()
+            self._ext = ext
+            self._hx = ext.create(self._reducer, self._cuda_red, N.fn_addr(host, "dmpi_reducer_mark_ready"),
+                                  N.fn_addr(host, "dmpi_reducer_pending"), N.fn_addr(lib, "dmpi_reducer_cuda_finalize"),
+                                  self.n_buckets)
+            flags = torch.zeros(len(self._slots), dtype=torch.uint8)
+            for i, slot in enumerate(self._slots):
+                flags[i] = 1 if slot.fused else 0
+            self.arena.fused_flags = flags
+            ext.install(self._hx, [s.param for s in self._slots],
+                        [_logical_view(self.arena.flat_g, s) for s in self._slots], [s.name for s in self._slots], flags)
+            for i, slot in enumerate(self._slots):
+                slot.ready_cb = (lambda idx=i: ext.mark_ready(self._hx, idx))
+            return
         for i, slot in enumerate(self._slots):
             slot.ready_cb = (lambda idx=i: self._mark_ready(idx))
             # parameters whose gradient comes from stock autograd (not from our fused backward)
@@ -193,6 +214,9 @@ class DistributedDataParallel(nn.Module):
         self._mark_ready(idx)
 
     def _mark_ready(self, idx: int) -> None:
+        if self._hx is not None:
+            self._ext.mark_ready(self._hx, idx)
+            return
         if not self._armed:
             return
         if not self._finalize_queued:
@@ -321,6 +345,8 @@ class DistributedDataParallel(nn.Module):
                 self._arm()
             else:
                 self._armed = False
+                if self._hx is not None:
+                    self._ext.arm(self._hx, False)
         out = self.module(*inputs, **kwargs)
         if side:
             rc = N.cuda().dmpi_reducer_cuda_side_broadcast(self._cuda_red, self._off["buffers"],
@@ -332,11 +358,18 @@ class DistributedDataParallel(nn.Module):
 
     def _arm(self) -> None:
         """Prepare the reducer for one synchronising backward pass (c10d: prepare_for_backward)."""
+        if self._hx is not None:
+            if self.world > 1:
+                N.count_launch(self._ext.take_launched(self._hx))
+            if not self._order_final and self._ext.completed(self._hx) > 0:
+                self._rebuild_launch_order()  # needs the ready order of the finished pass: before the reset below
         N.host().dmpi_reducer_reset(self._reducer)
         if self._cuda_red is not None:
             N.cuda().dmpi_reducer_cuda_begin(self._cuda_red, N.stream_ptr())
         self._armed = True
         self._marked = bytearray(len(self._slots))
+        if self._hx is not None:
+            self._ext.arm(self._hx, True)
 
     def __del__(self):  # pragma: no cover
         try:

@@ -224,6 +224,7 @@ class ParamArena:
             if entries:
                 self.t_table = build_transpose_table(entries, device)
         self._shadow_version = -1
+        self.fused_flags: Optional[torch.Tensor] = None  # CPU uint8 per slot, shared with the C++ autograd hooks
         self.bn_scratch: Optional[torch.Tensor] = None
         self._bn_slices: Dict[int, Tuple[torch.Tensor, torch.Tensor, torch.Tensor]] = {}
         self._bn_dirty: Dict[int, bool] = {}
@@ -331,7 +332,10 @@ class ParamArena:
         """fp32 gradient slot in physical element order (what the wgrad kernels accumulate into)."""
         s = self.by_param[id(p)]
         self._ensure_grad(s)
-        s.fused = True  # this parameter's gradient is published by grad_ready(), never by an autograd hook
+        if not s.fused:
+            s.fused = True  # this parameter's gradient is published by grad_ready(), never by an autograd hook
+            if self.fused_flags is not None and s.index < self.fused_flags.numel():
+                self.fused_flags[s.index] = 1
         v = self.flat_g[s.offset: s.offset + s.numel]
         if s.kind in ("conv", "stem"):
             k, c, r, q = s.shape

@@ -375,3 +375,50 @@ def test_frozen_parameters_stay_out_of_buckets_and_updates():
         opt.step()
     assert torch.equal(m[0].weight, frozen_before) and m[0].weight.grad is None
     assert not torch.equal(m[2].weight, torch.zeros_like(m[2].weight))
+
+
+def test_cpp_autograd_hooks_drive_the_reducer():
+    """csrc/hooks/autograd_hooks.cpp on the CPU: C++ post-accumulate-grad hooks re-home fresh gradient tensors into
+    their bucket views, mark the reducer core ready and run the finalize callback at the end of backward."""
+    import ctypes as C
+
+    from deeplearning_mpi_b200 import _native as N
+
+    ext = N.torch_hooks()
+    if ext is None:
+        pytest.skip("dmpi_torch_hooks.so not built")
+    host = N.host()
+    torch.manual_seed(0)
+    net = torch.nn.Sequential(torch.nn.Linear(4, 8), torch.nn.Tanh(), torch.nn.Linear(8, 2))
+    params = list(reversed(list(net.parameters())))          # bucket-fill order: reverse registration
+    names = [f"p{i}" for i in range(len(params))]
+    bucket_of = (C.c_int * 4)(0, 0, 1, 1)
+    red = host.dmpi_reducer_create(4, bucket_of, 2)
+    views = [torch.zeros_like(p) for p in params]
+    ctx = ext.create(red, 0, N.fn_addr(host, "dmpi_reducer_mark_ready"), N.fn_addr(host, "dmpi_reducer_pending"), 0, 2)
+    flags = torch.zeros(4, dtype=torch.uint8)
+    ext.install(ctx, params, views, names, flags)
+    x = torch.randn(6, 4)
+    # not armed (no_sync): gradients are re-homed, nothing is marked
+    net(x).square().sum().backward()
+    assert ext.completed(ctx) == 0 and ext.take_launched(ctx) == 0
+    assert all(p.grad.data_ptr() == v.data_ptr() for p, v in zip(params, views))
+    # armed: both buckets launch, finalize runs once
+    for p in params:
+        p.grad = None
+    host.dmpi_reducer_reset(red)
+    ext.arm(ctx, True)
+    net(x).square().sum().backward()
+    assert ext.completed(ctx) == 1 and ext.take_launched(ctx) == 2 and host.dmpi_reducer_pending(red) == 0
+    ref = torch.nn.Sequential(torch.nn.Linear(4, 8), torch.nn.Tanh(), torch.nn.Linear(8, 2))
+    ref.load_state_dict(net.state_dict())
+    ref(x).square().sum().backward()
+    for v, q in zip(views, reversed(list(ref.parameters()))):
+        assert torch.allclose(v, q.grad)
+    # a parameter owned by a fused kernel is never published by its hook: the pass ends with a bucket incomplete
+    flags[3] = 1
+    host.dmpi_reducer_reset(red)
+    ext.arm(ctx, True)
+    with pytest.raises(RuntimeError, match="incomplete"):
+        net(x).square().sum().backward()
+    host.dmpi_reducer_destroy(red)
