@@ -55,9 +55,26 @@ class GraphedTrainStep:
         self._capture()
 
     def __call__(self, *inputs: torch.Tensor) -> torch.Tensor:
+        if any(tuple(d.shape) != tuple(s.shape) or d.dtype != s.dtype for d, s in zip(self.static_inputs, inputs)):
+            # e.g. the short last batch of an epoch: run it eagerly (same kernels, launched one by one)
+            return self.step_fn(*inputs)
         for dst, src in zip(self.static_inputs, inputs):
             if dst.data_ptr() != src.data_ptr():
                 dst.copy_(src, non_blocking=True)
         self.graph.replay()
         N.count_launch(self.launches_per_replay)
         return self.static_out
+
+
+class LazyGraphedStep:
+    """``GraphedTrainStep`` that captures at its first call, from that call's inputs — for training loops that only see
+    tensors once the data loader runs (examples/resnet/main.py --graph, examples/unet/train.py --graph)."""
+
+    def __init__(self, step_fn: Callable[..., torch.Tensor], warmup: int = 3):
+        self.step_fn, self.warmup, self._graphed = step_fn, warmup, None
+
+    def __call__(self, *inputs: torch.Tensor) -> torch.Tensor:
+        if self._graphed is None:
+            # the warm-up steps inside the capture helper are real optimizer steps on this batch
+            self._graphed = GraphedTrainStep(self.step_fn, inputs, warmup=self.warmup)
+        return self._graphed(*inputs)

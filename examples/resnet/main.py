@@ -8,7 +8,8 @@ Everything under the nn.Module surface runs on this framework (NVLink all-reduce
 
     torchrun --nproc_per_node 8 --nnodes 1 --master_addr 127.0.0.1 --master_port 29500 examples/resnet/main.py --synthetic
 
-``--synthetic`` replaces CIFAR-10 (which needs a download, examples/resnet/download.py) with random data of its shape;
+``--graph`` replays the whole iteration as one CUDA graph (the speed bench.py reports; 3-4x on this launch-bound
+configuration).  ``--synthetic`` replaces CIFAR-10 (which needs a download, examples/resnet/download.py) with random data of its shape;
 ``--arch resnet50 --image_size 224`` selects the BASELINE.json configuration.
 """
 import os
@@ -85,6 +86,18 @@ def run(cfg, args):
     train_loader, test_loader = build_loaders(cfg, args)
     criterion = dnn.CrossEntropyLoss()
     optimizer = optim.SGD(ddp_model.parameters(), lr=cfg.learning_rate, momentum=0.9, weight_decay=1e-5)
+
+    def train_step(inputs, labels):
+        optimizer.zero_grad()
+        loss = criterion(ddp_model(inputs), labels)
+        loss.backward()
+        optimizer.step()
+        return loss
+
+    if cfg.graph and on_gpu:
+        from deeplearning_mpi_b200.utils.graph import LazyGraphedStep
+
+        train_step = LazyGraphedStep(train_step)
     for epoch in range(cfg.num_epochs):
         if args.variant == "legacy" and epoch % 10 == 0 and LOCAL_RANK == 0:
             evaluate_and_save(ddp_model, device, test_loader, cfg, epoch)
@@ -98,13 +111,9 @@ def run(cfg, args):
             if args.variant != "legacy":
                 print(f"Local Rank: {LOCAL_RANK}, index: {index}", end="\r")
             inputs, labels = data[0].to(device), data[1].to(device)
-            optimizer.zero_grad()
-            outputs = ddp_model(inputs)
-            loss = criterion(outputs, labels)
+            loss = train_step(inputs, labels)
             if args.variant != "legacy":
                 total_loss.append(loss.item())
-            loss.backward()
-            optimizer.step()
         if total_loss:
             print("Local Rank: {}, Epoch: {}, Loss: {}".format(LOCAL_RANK, epoch, np.mean(total_loss)))
         if args.variant != "legacy" and epoch % 10 == 0 and LOCAL_RANK == 0:

@@ -75,6 +75,22 @@ def train_model(model, train_loader, test_loader, device, cfg, log_file):
     optimizer = optim.Adam(model.parameters(), lr=cfg.learning_rate)
     criterion = dnn.BCEWithLogitsLoss()
     on_gpu = device.type == "cuda"
+
+    def graph_step(images, true_masks):   # the whole iteration, for --graph (no data-dependent skip inside a graph)
+        predicted = model(images)
+        if predicted.dim() == 4:
+            predicted = predicted.squeeze(1)
+        loss = criterion(predicted, true_masks)
+        optimizer.zero_grad()
+        loss.backward()
+        dnn.clip_grad_norm_(model.parameters(), max_norm=1.0)
+        optimizer.step()
+        return loss
+
+    if cfg.graph and on_gpu:
+        from deeplearning_mpi_b200.utils.graph import LazyGraphedStep
+
+        graph_step = LazyGraphedStep(graph_step)
     for epoch in range(cfg.num_epochs):
         start_time = time.time()
         model.train()
@@ -86,6 +102,15 @@ def train_model(model, train_loader, test_loader, device, cfg, log_file):
                 break
             images = batch["image"].to(device, dtype=torch.float32)
             true_masks = batch["mask"].to(device, dtype=torch.float32)
+            if cfg.graph and on_gpu:
+                value = graph_step(images, true_masks).item()
+                if value != value or value in (float("inf"), float("-inf")):
+                    # eager mode skips such a step on all ranks; a replayed graph has already applied it
+                    raise RuntimeError(f"non-finite loss {value} under --graph: rerun without --graph to skip bad batches")
+                epoch_loss += value
+                num_batches += 1
+                loop.set_postfix(loss=value)
+                continue
             predicted_masks = model(images)
             if predicted_masks.dim() == 4:
                 predicted_masks = predicted_masks.squeeze(1)

@@ -441,3 +441,174 @@ def test_training_step_is_reproducible():
         assert torch.equal(g[0], g[1]), "level 2: gradients are not bit-reproducible"
     finally:
         CV._DETERMINISTIC_WGRAD = saved
+
+
+def _oracle_resnet(model, x):
+    """fp32 math with bf16 rounding wherever the kernels store bf16 (see _q): stem, every block, pooled features."""
+    a = _q(F.relu(model.bn1(_q(model.conv1(x)))))
+    a = model.maxpool(a)
+    for layer in (model.layer1, model.layer2, model.layer3, model.layer4):
+        for blk in layer:
+            a = _oracle_block(blk, a)
+    a = _q(model.avgpool(a).flatten(1))
+    return model.fc(a)
+
+
+@pytest.mark.parametrize("arch", ["resnet18", "resnet50"])
+def test_resnet_gradients_vs_bf16_oracle(arch):
+    """Whole-network gradients are ASSERTED (not only finite): against an oracle that rounds to bf16 exactly where the
+    kernels store bf16, the ReLU gates agree and what remains is accumulation-order noise amplified by depth."""
+    import deeplearning_mpi_b200.nn as dnn
+    from deeplearning_mpi_b200 import models
+
+    torch.manual_seed(0)
+    ref = getattr(models, arch)(num_classes=100)
+    ref.train()
+    for m in ref.modules():
+        if isinstance(m, torch.nn.BatchNorm2d):
+            torch.nn.init.uniform_(m.weight, 0.5, 1.5)
+            torch.nn.init.normal_(m.bias, 0, 0.2)
+    _round_weights_to_bf16(ref)
+    fast = copy.deepcopy(ref).to(DEV)
+    x = torch.randn(16, 3, 64, 64).bfloat16().float()
+    y = torch.randint(0, 100, (16,))
+    loss_ref = F.cross_entropy(_oracle_resnet(ref, x), y)
+    loss_ref.backward()
+    loss = dnn.cross_entropy(fast(x.to(DEV)), y.to(DEV))
+    loss.backward()
+    torch.cuda.synchronize()
+    g_ref = {n: p.grad for n, p in ref.named_parameters()}
+    g = _grads_logical(fast)
+    worst, worst_cos, tot_num, tot_den = 0.0, 1.0, 0.0, 0.0
+    for n in g_ref:
+        r, c = _rel(g[n], g_ref[n]), _cos(g[n], g_ref[n])
+        worst, worst_cos = max(worst, r), min(worst_cos, c)
+        tot_num += (g[n].float().cpu() - g_ref[n]).norm().item() ** 2
+        tot_den += g_ref[n].norm().item() ** 2
+    glob = (tot_num / tot_den) ** 0.5
+    print(f"[{arch}] loss {loss.item():.4f} vs {loss_ref.item():.4f}; gradients: global rel {glob:.3e}, worst tensor rel "
+          f"{worst:.3e}, worst cos {worst_cos:.4f}")
+    assert abs(loss.item() - loss_ref.item()) < 2e-2 * abs(loss_ref.item())
+    assert glob < 0.15 and worst_cos > 0.9, (glob, worst, worst_cos)
+
+
+def test_loss_curve_matches_stock_torch():
+    """N optimizer steps of this framework against stock PyTorch (torchvision ResNet-18,
+    cuDNN, fp32, torch.optim.SGD) from the same weights on the same batches: the two loss curves stay together."""
+    import torchvision
+
+    import deeplearning_mpi_b200.nn as dnn
+    from deeplearning_mpi_b200 import optim
+    from deeplearning_mpi_b200.models import resnet18
+
+    torch.manual_seed(11)
+    ours = resnet18(num_classes=10).to(DEV)
+    stock = torchvision.models.resnet18(weights=None)
+    stock.fc = torch.nn.Linear(512, 10)
+    stock.load_state_dict(ours.state_dict())
+    stock = stock.to(DEV).train()
+    o1 = optim.SGD(ours.parameters(), lr=0.02, momentum=0.9, weight_decay=1e-5)
+    o2 = torch.optim.SGD(stock.parameters(), lr=0.02, momentum=0.9, weight_decay=1e-5)
+    g = torch.Generator().manual_seed(5)
+    proto = torch.randn(10, 3, 32, 32, generator=g)
+    batches = []
+    for _ in range(4):   # learnable data: class prototype + noise
+        y = torch.randint(0, 10, (128,), generator=g)
+        batches.append(((proto[y] + 0.7 * torch.randn(128, 3, 32, 32, generator=g)).to(DEV), y.to(DEV)))
+    la, lb = [], []
+    for step in range(24):
+        x, y = batches[step % 4]
+        o1.zero_grad()
+        l1 = dnn.cross_entropy(ours(x), y)
+        l1.backward()
+        o1.step()
+        o2.zero_grad()
+        l2 = F.cross_entropy(stock(x), y)
+        l2.backward()
+        o2.step()
+        la.append(l1.item())
+        lb.append(l2.item())
+    print("ours ", [round(v, 3) for v in la])
+    print("stock", [round(v, 3) for v in lb])
+    diffs = [abs(a - b) for a, b in zip(la, lb)]
+    assert la[-1] < 0.5 * la[0] and lb[-1] < 0.5 * lb[0]
+    assert diffs[0] < 2e-2 and max(diffs[:6]) < 0.1
+    assert sum(diffs) / len(diffs) < 0.1 and max(diffs) < 0.3, (max(diffs), sum(diffs) / len(diffs))
+
+
+@pytest.mark.parametrize("kind", ["resnet", "unet"])
+def test_reference_script_resumes_from_our_checkpoint(kind, tmp_path):
+    """save_checkpoint() output goes through the REFERENCE's own build_model(resume) (baseline/_ref, unmodified,
+    ref:pytorch/resnet/main.py:36-54 / ref:pytorch/unet/train.py:60-75) in a separate process: strict load_state_dict
+    through stock DDP succeeds and its eval output equals ours."""
+    import os
+    import subprocess
+    import sys
+
+    from deeplearning_mpi_b200.models import UNet, resnet18
+    from deeplearning_mpi_b200.parallel import dist
+    from deeplearning_mpi_b200.parallel.ddp import DistributedDataParallel
+    from deeplearning_mpi_b200.utils.checkpoint import save_checkpoint
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if not os.path.isdir(os.path.join(root, "baseline", "_ref", "pytorch")):
+        pytest.skip("reference arm not installed (baseline/_ref)")
+    for k, v in dict(RANK="0", LOCAL_RANK="0", WORLD_SIZE="1", LOCAL_WORLD_SIZE="1", MASTER_ADDR="127.0.0.1",
+                     MASTER_PORT="29877").items():
+        os.environ.setdefault(k, v)
+    torch.manual_seed(2)
+    created = not dist.is_initialized()
+    if created:
+        dist.init_process_group("nccl")
+    try:
+        model = (resnet18(num_classes=10) if kind == "resnet" else UNet(out_classes=1)).to(DEV)
+        ddp = DistributedDataParallel(model, device_ids=[0], output_device=0)
+        x = torch.randn(4, 3, 32, 32)
+        ddp.train()
+        ddp(x.to(DEV))              # one training forward so that the running statistics are not the initial ones
+        path = str(tmp_path / "ckpt.pth")
+        save_checkpoint(ddp, path)
+        ddp.eval()
+        with torch.no_grad():
+            mine = ddp(x.to(DEV)).float().cpu()
+    finally:
+        if created:
+            dist.destroy_process_group()
+    torch.save(x, tmp_path / "x.pt")
+    env = dict(os.environ, MASTER_PORT="29878")
+    r = subprocess.run([sys.executable, os.path.join(root, "tests", "mp", "ref_resume_worker.py"), kind, path,
+                        str(tmp_path / "x.pt"), str(tmp_path / "y.pt")], capture_output=True, text=True, timeout=600,
+                       env=env, cwd=root)
+    assert r.returncode == 0 and "REF_RESUME_OK" in r.stdout, (r.stdout + r.stderr)[-3000:]
+    theirs = torch.load(tmp_path / "y.pt")
+    rel = _rel(mine, theirs)
+    print(f"[{kind}] ours vs reference-loaded eval output: rel {rel:.3e}")
+    assert rel < 5e-2
+
+
+@pytest.mark.parametrize("example", ["resnet", "unet"])
+def test_example_trainers_graph_flag(example, tmp_path):
+    """The shipped CLIs reach the benchmarked (CUDA-graph) path: `--graph` trains and the loss falls."""
+    import os
+    import re
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, RANK="0", LOCAL_RANK="0", WORLD_SIZE="1", LOCAL_WORLD_SIZE="1", MASTER_ADDR="127.0.0.1",
+               MASTER_PORT="29881")
+    for d in ("saved_models", "logs", "data"):
+        (tmp_path / d).mkdir()
+    if example == "resnet":
+        cmd = [sys.executable, os.path.join(root, "examples", "resnet", "main.py"), "--synthetic", "--graph", "--num_epochs",
+               "3", "--batch_size", "64", "--synthetic_size", "256", "--learning_rate", "0.05"]
+        pat = r"Epoch: (\d+), Loss: ([0-9.]+)"
+    else:
+        cmd = [sys.executable, os.path.join(root, "examples", "unet", "train.py"), "--synthetic", "--graph", "--num_epochs",
+               "3", "--batch_size", "4", "--synthetic_size", "20", "--image_size", "64", "--learning_rate", "0.001"]
+        pat = r"Epoch (\d+) finished with loss: ([0-9.]+)"
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env, cwd=str(tmp_path))
+    assert r.returncode == 0, (r.stdout + r.stderr)[-3000:]
+    losses = [float(m[1]) for m in re.findall(pat, r.stdout)]
+    print(example, losses)
+    assert len(losses) == 3 and losses[-1] < losses[0]
