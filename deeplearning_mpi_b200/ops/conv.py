@@ -227,24 +227,14 @@ def choose_patch_tile(ow: int, oh: int, halo: int = 1) -> Optional[Tuple[int, in
 _PATCH_PAIR = int(os.environ.get("DMPI_PATCH_PAIR", "1"))  # patch mode together with CTA pairs for N >= 128
 
 
-def _patch_ok(R, S, stride, pad, c_in, ow, oh, n_out=64, cg=1):
-    """Patch-mode tile for a 3x3 stride-1 layer, or None.  With N <= 64 the whole filter stays resident in shared
-    memory (56x56x64: 88 vs 136 us).  With wider N the filter taps stream; that only pays together with CTA pairs
-    (each CTA loads its own patch and half of every tap tile, ~2.3x less L2 -> SM traffic than per-tap loads), so the
-    single-CTA streamed variant is used only when forced (DMPI_PATCH=2)."""
-    if not _PATCH or R != S or R != 3 or stride != 1 or pad != 1 or c_in % 64 != 0:
+def _patch_geom(R, S, stride, pad, c_in, ow, oh, bn, cg):
+    """Patch-mode tile for a 3x3 stride-1 layer when the geometry and the kernel's shared-memory ring allow it (no
+    policy): two patch stages plus at least two filter-tap tiles must fit (igemm.cu: kRingBytes)."""
+    if R != S or R != 3 or stride != 1 or pad != 1 or c_in % 64 != 0 or (cg == 2 and bn < 128):
         return None
-    if _PATCH != 2 and n_out > 64:
-        # bench/igemm_patch_ab.py: with CTA pairs the 128-wide tile gains 8-15 % on large images (256x256: 318 -> 282 us)
-        # and ties on small ones; the 256-wide tile loses 8-12 % (its per-tap loads were already amortised)
-        # (on 28x28 it costs ResNet-50 1.4 %: only the wide images, whose row-segment tiles waste no accumulator rows)
-        if not (cg == 2 and _PATCH_PAIR and _pick_bn(n_out, 9 * c_in) == 128 and ow >= 128):
-            return None
     t = choose_patch_tile(ow, oh, pad)
     if t is None or t[2] < _PATCH_MIN_EFF:
         return None
-    # two patch stages plus at least two filter-tap tiles must fit in the kernel's operand ring (igemm.cu: kRingBytes)
-    bn = _pick_bn(n_out, 9 * c_in)
     if cg == 2:
         ring = {128: 144, 256: 160}[bn] * 1024
         tap_bytes = bn * 64
@@ -253,10 +243,114 @@ def _patch_ok(R, S, stride, pad, c_in, ow, oh, n_out=64, cg=1):
         tap_bytes = bn * 128
     pw = t[0] + 2 * pad
     rows = max(128 + 2 * pad * pw + 2 * pad, pw * (t[1] + 2 * pad))
-    stride = -(-rows * 128 // 1024) * 1024
-    if ring - 2 * stride < 2 * tap_bytes:
+    stride_b = -(-rows * 128 // 1024) * 1024
+    if ring - 2 * stride_b < 2 * tap_bytes:
         return None
     return t
+
+
+def _patch_ok(R, S, stride, pad, c_in, ow, oh, n_out=64, cg=1):
+    """Heuristic choice (used when a shape has not been autotuned).  With N <= 64 the whole filter stays resident in
+    shared memory (56x56x64: 88 vs 136 us).  With wider N the filter taps stream; that only pays together with CTA pairs
+    (each CTA loads its own patch and half of every tap tile, ~2.3x less L2 -> SM traffic than per-tap loads), so the
+    single-CTA streamed variant is used only when forced (DMPI_PATCH=2)."""
+    if not _PATCH:
+        return None
+    bn = _pick_bn(n_out, 9 * c_in)
+    if _PATCH != 2 and n_out > 64:
+        # bench/igemm_patch_ab.py: with CTA pairs the 128-wide tile gains 8-15 % on large images (256x256: 318 -> 282 us)
+        # and ties on small ones; the 256-wide tile loses 8-12 % (its per-tap loads were already amortised)
+        if not (cg == 2 and _PATCH_PAIR and bn == 128 and ow >= 128):
+            return None
+    return _patch_geom(R, S, stride, pad, c_in, ow, oh, bn, cg)
+
+
+# --------------------------------------------------------------------------------------- autotuning
+# The reference runs with torch.backends.cudnn.benchmark = True (ref:pytorch/resnet/main.py:29): cuDNN times its
+# algorithms on the first call of every shape and keeps the fastest.  Same here: the first eager call of a convolution
+# shape times every legal tile configuration of the implicit GEMM (N tile 64 / 128 / 256, one CTA or a CTA pair, per-tap
+# loads or patch mode) on scratch outputs and the shape keeps the winner - which also settles wave quantisation (196
+# tiles on 148 SMs) and the L2-bound / epilogue-bound trade-offs that a closed-form rule gets wrong somewhere.
+# Opt-in (DMPI_AUTOTUNE=1): on the three benchmark models the closed-form rules below already sit at the tuner's
+# optimum (A/B on one box: ResNet-50 18.88 vs 18.95 ms, UNet 30.41 vs 30.56 ms, ResNet-18 32x32 1.370 vs 1.349 ms per
+# step), and without it the tile shapes - hence the summation order of the BatchNorm statistics - are identical from
+# run to run, which keeps results bit-identical across processes.  Nothing is timed while a stream is being captured.
+_AUTOTUNE = os.environ.get("DMPI_AUTOTUNE", "0") == "1"
+_tuned: dict = {}
+_forced = None  # (bn, cg, use_patch) set by force_config(): tests / A-B scripts
+
+
+class force_config:
+    """Context manager that pins the implicit-GEMM tile configuration: (bn, cg, patch) with patch True / False."""
+
+    def __init__(self, bn: int, cg: int, patch: bool):
+        self.cfg = (bn, cg, patch)
+
+    def __enter__(self):
+        global _forced
+        self.prev, _forced = _forced, self.cfg
+        return self
+
+    def __exit__(self, *exc):
+        global _forced
+        _forced = self.prev
+
+
+def tile_candidates(n_out, R, S, stride, pad, c_in, ow, oh):
+    """Every (bn, cg, patch tile or None) the kernel can run for this layer."""
+    out = []
+    for bn in (64, 128, 256):
+        if bn > 64 and bn > n_out and bn // 2 >= n_out:
+            continue  # a narrower tile already covers all filters
+        for cg in (1, 2):
+            if cg == 2 and bn < 128:
+                continue
+            out.append((bn, cg, None))
+            t = _patch_geom(R, S, stride, pad, c_in, ow, oh, bn, cg) if _PATCH else None
+            if t is not None:
+                out.append((bn, cg, t))
+    return out
+
+
+def _can_time(device) -> bool:
+    return _AUTOTUNE and _forced is None and device.type == "cuda" and not torch.cuda.is_current_stream_capturing()
+
+
+def _choose(skey, heuristic, cands, run, device):
+    """Configuration for shape ``skey``: forced > tuned > (tune now) > heuristic.  ``run(cfg)`` executes one launch on
+    scratch outputs."""
+    if _forced is not None:
+        bn, cg, want_patch = _forced
+        for c in cands:
+            if c[0] == bn and c[1] == cg and (c[2] is not None) == bool(want_patch):
+                return c
+        raise ValueError(f"forced tile configuration {_forced} is not legal for this layer (candidates: {cands})")
+    got = _tuned.get(skey)
+    if got is not None:
+        return got
+    if not _can_time(device) or len(cands) < 2:
+        return heuristic
+    best, best_t = heuristic, float("inf")
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    for c in cands:
+        try:
+            run(c)  # plan creation + first launch
+            ts = []
+            for _ in range(3):
+                ev[0].record()
+                run(c)
+                ev[1].record()
+                ev[1].synchronize()
+                ts.append(ev[0].elapsed_time(ev[1]))
+            t = min(ts)
+        except RuntimeError:
+            continue  # a configuration the kernel refuses (e.g. patch ring too small): not a candidate
+        if t < best_t * (0.97 if c != heuristic else 1.0):  # the closed-form choice wins ties (3 %)
+            best, best_t = c, min(t, best_t) if c == heuristic else t
+    _tuned[skey] = best
+    if os.environ.get("DMPI_AUTOTUNE_LOG"):
+        print(f"[dmpi autotune] {skey}: {best} ({best_t * 1e3:.1f} us; heuristic {heuristic})", flush=True)
+    return best
 
 
 # --------------------------------------------------------------------------------------- fprop
@@ -279,60 +373,82 @@ def conv2d_fprop(x: torch.Tensor, w2d: torch.Tensor, R: int, S: int, stride: int
     bn = _pick_bn(kout, R * S * c)
     cg = _pick_cg(bn, R * S * c)
     ptile = _patch_ok(R, S, stride, pad, c, ow, oh, kout, cg)
-    key = ("fprop", n, h, w, c, sn, sh, sw, kout, R, S, stride, pad, osn, osh, osw, bias is not None,
-           stats is not None, relu, bn, cg, ptile)
+    heur = (bn, cg, ptile)
+    skey = ("fprop", n, h, w, c, sn, sh, sw, kout, R, S, stride, pad, osn, osh, osw, bias is not None, stats is not None, relu)
 
-    def build():
-        d = N.ConvDesc()
-        if flat:
-            m = n * h * w
-            d.a_nviews = 1
-            d.a_view[0] = _t4((c, m, 1, 1), (sw, m * sw, m * sw))
-            d.box_w, d.box_h, d.box_n = 128, 1, 1
-            d.grid_w, d.grid_h, d.grid_n = m, 1, 1
-            d.ntaps = 1
-            d.tap_view[0] = 0
-            d.o_nviews = 1
-            d.o_view[0] = _t4((kout, m, 1, 1), (osw, m * osw, m * osw))
-        else:
-            views, vid = _views_for_stride(h, w, c, sn, sh, sw, n, stride)
-            d.a_nviews = len(views)
-            for i, v in enumerate(views):
-                d.a_view[i] = v
-            if ptile is not None:
-                bw, bh, bnn = ptile[0], ptile[1], 1
-                d.patch, d.halo = 1, pad
+    def go(cfg, out, stats):
+        bn, cg, ptile = cfg
+        on, ohh, oww, oc, osn, osh, osw = _nhwc_meta(out)
+        key = ("fprop", n, h, w, c, sn, sh, sw, kout, R, S, stride, pad, osn, osh, osw, bias is not None,
+               stats is not None, relu, bn, cg, ptile)
+
+        def build():
+            d = N.ConvDesc()
+            if flat:
+                m = n * h * w
+                d.a_nviews = 1
+                d.a_view[0] = _t4((c, m, 1, 1), (sw, m * sw, m * sw))
+                d.box_w, d.box_h, d.box_n = 128, 1, 1
+                d.grid_w, d.grid_h, d.grid_n = m, 1, 1
+                d.ntaps = 1
+                d.tap_view[0] = 0
+                d.o_nviews = 1
+                d.o_view[0] = _t4((kout, m, 1, 1), (osw, m * osw, m * osw))
             else:
-                bw, bh, bnn = choose_box(ow, oh, n)
-            d.box_w, d.box_h, d.box_n = bw, bh, bnn
-            d.grid_w, d.grid_h, d.grid_n = ow, oh, n
-            d.ntaps = R * S
-            assert d.ntaps <= N.MAX_TAPS
-            t = 0
-            for r in range(R):
-                for s in range(S):
-                    if stride == 1:
-                        d.tap_view[t], d.tap_dh[t], d.tap_dw[t] = 0, r - pad, s - pad
-                    else:
-                        a, b = (r - pad) % 2, (s - pad) % 2
-                        d.tap_view[t] = vid(a, b)
-                        d.tap_dh[t], d.tap_dw[t] = (r - pad - a) // 2, (s - pad - b) // 2
-                    d.tap_koff[t] = t * c
-                    t += 1
-            d.o_nviews = 1
-            d.o_view[0] = _t4((kout, ow, oh, n), (osw, osh, osn))
-        d.cblocks = c // 64
-        d.b_rows, d.b_k = kout, R * S * c
-        d.nblk_per_oview = 0
-        d.n_out, d.bn = kout, bn
-        d.cta_group = cg
-        d.bias_mod = kout if bias is not None else 0
-        d.stat_mod = kout if stats is not None else 0
-        d.relu = int(relu)
-        d.out_mode = 0
-        return d
+                views, vid = _views_for_stride(h, w, c, sn, sh, sw, n, stride)
+                d.a_nviews = len(views)
+                for i, v in enumerate(views):
+                    d.a_view[i] = v
+                if ptile is not None:
+                    bw, bh, bnn = ptile[0], ptile[1], 1
+                    d.patch, d.halo = 1, pad
+                else:
+                    bw, bh, bnn = choose_box(ow, oh, n)
+                d.box_w, d.box_h, d.box_n = bw, bh, bnn
+                d.grid_w, d.grid_h, d.grid_n = ow, oh, n
+                d.ntaps = R * S
+                assert d.ntaps <= N.MAX_TAPS
+                t = 0
+                for r in range(R):
+                    for s in range(S):
+                        if stride == 1:
+                            d.tap_view[t], d.tap_dh[t], d.tap_dw[t] = 0, r - pad, s - pad
+                        else:
+                            a, b = (r - pad) % 2, (s - pad) % 2
+                            d.tap_view[t] = vid(a, b)
+                            d.tap_dh[t], d.tap_dw[t] = (r - pad - a) // 2, (s - pad - b) // 2
+                        d.tap_koff[t] = t * c
+                        t += 1
+                d.o_nviews = 1
+                d.o_view[0] = _t4((kout, ow, oh, n), (osw, osh, osn))
+            d.cblocks = c // 64
+            d.b_rows, d.b_k = kout, R * S * c
+            d.nblk_per_oview = 0
+            d.n_out, d.bn = kout, bn
+            d.cta_group = cg
+            d.bias_mod = kout if bias is not None else 0
+            d.stat_mod = kout if stats is not None else 0
+            d.relu = int(relu)
+            d.out_mode = 0
+            return d
 
-    _run_igemm(_get_plan(key, build), x, w2d, out, bias, stats)
+
+        _run_igemm(_get_plan(key, build), x, w2d, out, bias, stats)
+
+    cfg = _tuned.get(skey) if _forced is None else None
+    if cfg is None:
+        cfg = heur
+        if _forced is not None or _can_time(x.device):
+            scratch = []
+
+            def trial(c_):  # launches on scratch outputs (same strides): timing never touches the caller's tensors
+                if not scratch:
+                    scratch.append(torch.empty_strided(out.shape, out.stride(), dtype=out.dtype, device=out.device))
+                    scratch.append((torch.zeros_like(stats[0]), torch.zeros_like(stats[1])) if stats is not None else None)
+                go(c_, scratch[0], scratch[1])
+
+            cfg = _choose(skey, heur, tile_candidates(kout, R, S, stride, pad, c, ow, oh), trial, x.device)
+    go(cfg, out, stats)
     return out
 
 
@@ -361,54 +477,74 @@ def conv2d_dgrad(dy: torch.Tensor, wt2d: torch.Tensor, R: int, S: int, stride: i
     cg = _pick_cg(bn, ktot)
     if stride == 1:
         flat = R == 1 and S == 1 and pad == 0 and _is_flat(n, oh, ow, sn, sh, sw) and _is_flat(n, ih, iw, osn, osh, osw)
-        ptile = _patch_ok(R, S, 1, pad, k, iw, ih, c, cg)
-        key = ("dgrad1", n, oh, ow, k, sn, sh, sw, c, R, S, pad, osn, osh, osw, bn, cg, ptile)
-
-        def build():
-            d = N.ConvDesc()
-            d.a_nviews = 1
-            if flat:
-                m = n * oh * ow
-                d.a_view[0] = _t4((k, m, 1, 1), (sw, m * sw, m * sw))
-                d.box_w, d.box_h, d.box_n = 128, 1, 1
-                d.grid_w, d.grid_h, d.grid_n = m, 1, 1
-                d.ntaps = 1
-                d.o_view[0] = _t4((c, m, 1, 1), (osw, m * osw, m * osw))
-            else:
-                d.a_view[0] = _t4((k, ow, oh, n), (sw, sh, sn))
-                if ptile is not None:
-                    bw, bh, bnn = ptile[0], ptile[1], 1
-                    d.patch, d.halo = 1, pad
-                else:
-                    bw, bh, bnn = choose_box(iw, ih, n)
-                d.box_w, d.box_h, d.box_n = bw, bh, bnn
-                d.grid_w, d.grid_h, d.grid_n = iw, ih, n
-                d.ntaps = R * S
-                t = 0
-                for r in range(R):
-                    for s in range(S):
-                        d.tap_view[t], d.tap_dh[t], d.tap_dw[t], d.tap_koff[t] = 0, pad - r, pad - s, t * k
-                        t += 1
-                d.o_view[0] = _t4((c, iw, ih, n), (osw, osh, osn))
-            d.o_nviews = 1
-            d.cblocks = k // 64
-            d.b_rows, d.b_k = c, R * S * k
-            d.n_out, d.bn = c, bn
-            d.cta_group = cg
-            return d
-
+        heur = (bn, cg, _patch_ok(R, S, 1, pad, k, iw, ih, c, cg))
+        skey = ("dgrad1", n, oh, ow, k, sn, sh, sw, c, R, S, pad, osn, osh, osw, addend is not None)
+        add_strides = None
         if addend is not None:
             an, ah, aw, ac, asn, ash, asw = _nhwc_meta(addend)
             assert (an, ah, aw, ac) == (n, ih, iw, c), (addend.shape, (n, ih, iw, c))
             if flat:
                 assert _is_flat(n, ih, iw, asn, ash, asw)
-                m = n * ih * iw
-                strides = (m * asw, m * asw, asw)  # same (c, m, 1, 1) view convention as the flat output
+                m_ = n * ih * iw
+                add_strides = (m_ * asw, m_ * asw, asw)  # same (c, m, 1, 1) view convention as the flat output
             else:
-                strides = (asn, ash, asw)
-            _run_igemm(_get_plan(key, build), dy, wt2d, out, None, None, addend, strides)
-        else:
-            _run_igemm(_get_plan(key, build), dy, wt2d, out, None, None)
+                add_strides = (asn, ash, asw)
+
+        def go(cfg, out):
+            bn, cg, ptile = cfg
+            key = ("dgrad1", n, oh, ow, k, sn, sh, sw, c, R, S, pad, osn, osh, osw, bn, cg, ptile)
+
+            def build():
+                d = N.ConvDesc()
+                d.a_nviews = 1
+                if flat:
+                    m = n * oh * ow
+                    d.a_view[0] = _t4((k, m, 1, 1), (sw, m * sw, m * sw))
+                    d.box_w, d.box_h, d.box_n = 128, 1, 1
+                    d.grid_w, d.grid_h, d.grid_n = m, 1, 1
+                    d.ntaps = 1
+                    d.o_view[0] = _t4((c, m, 1, 1), (osw, m * osw, m * osw))
+                else:
+                    d.a_view[0] = _t4((k, ow, oh, n), (sw, sh, sn))
+                    if ptile is not None:
+                        bw, bh, bnn = ptile[0], ptile[1], 1
+                        d.patch, d.halo = 1, pad
+                    else:
+                        bw, bh, bnn = choose_box(iw, ih, n)
+                    d.box_w, d.box_h, d.box_n = bw, bh, bnn
+                    d.grid_w, d.grid_h, d.grid_n = iw, ih, n
+                    d.ntaps = R * S
+                    t = 0
+                    for r in range(R):
+                        for s in range(S):
+                            d.tap_view[t], d.tap_dh[t], d.tap_dw[t], d.tap_koff[t] = 0, pad - r, pad - s, t * k
+                            t += 1
+                    d.o_view[0] = _t4((c, iw, ih, n), (osw, osh, osn))
+                d.o_nviews = 1
+                d.cblocks = k // 64
+                d.b_rows, d.b_k = c, R * S * k
+                d.n_out, d.bn = c, bn
+                d.cta_group = cg
+                return d
+
+            if addend is not None:
+                _run_igemm(_get_plan(key, build), dy, wt2d, out, None, None, addend, add_strides)
+            else:
+                _run_igemm(_get_plan(key, build), dy, wt2d, out, None, None)
+
+        cfg = _tuned.get(skey) if _forced is None else None
+        if cfg is None:
+            cfg = heur
+            if _forced is not None or _can_time(dy.device):
+                scratch = []
+
+                def trial(c_):
+                    if not scratch:
+                        scratch.append(torch.empty_strided(out.shape, out.stride(), dtype=out.dtype, device=out.device))
+                    go(c_, scratch[0])
+
+                cfg = _choose(skey, heur, tile_candidates(c, R, S, 1, pad, k, iw, ih), trial, dy.device)
+        go(cfg, out)
         return out
 
     assert stride == 2 and addend is None

@@ -342,3 +342,57 @@ def test_fprop_statistics_atomics_mode():
             _close(ssq, (yf * yf).sum(dim=(0, 1, 2)), 2e-3, f"atomic_stats_sq{(n, h, c, k, R)}")
     finally:
         C._DETERMINISTIC = saved
+
+
+TUNE_CASES = [
+    (2, 56, 56, 64, 64, 3, 1, 1),      # N = 64: per-tap vs resident-filter patch mode
+    (2, 28, 28, 128, 256, 3, 1, 1),    # N tiles 64 / 128 / 256, one CTA or pairs, streamed patch mode
+    (4, 14, 14, 256, 512, 1, 1, 0),    # flat 1x1: every N tile / pair combination
+    (1, 130, 136, 128, 128, 3, 1, 1),  # wide image: row-segment patch tiles with pairs
+    (3, 7, 7, 512, 512, 3, 1, 1),      # tiny M: wave quantisation decides
+]
+
+
+@pytest.mark.parametrize("case", TUNE_CASES)
+def test_every_tile_configuration(case):
+    """Every configuration the autotuner may pick (ops/conv.py::tile_candidates) is numerically the same convolution:
+    fprop with BatchNorm statistics and dgrad with a residual addend, each forced in turn."""
+    from deeplearning_mpi_b200.ops import conv as C
+
+    _torch_setup()
+    n, h, w, c, k, R, stride, pad = case
+    x = _rand(n, h, w, c)
+    wt = _rand(k, c, R, R, scale=(c * R * R) ** -0.5)
+    ref = F.conv2d(x.float().permute(0, 3, 1, 2), wt.float(), stride=stride, padding=pad).permute(0, 2, 3, 1)
+    dy = _rand(n, h, w, k)
+    add = _rand(n, h, w, c)
+    ref_dx = torch.nn.grad.conv2d_input((n, c, h, w), wt.float(), dy.float().permute(0, 3, 1, 2), stride=stride,
+                                        padding=pad).permute(0, 2, 3, 1) + add.float()
+    cands = C.tile_candidates(k, R, R, stride, pad, c, w, h)
+    assert len(cands) >= 2
+    for bn, cg, pt in cands:
+        with C.force_config(bn, cg, pt is not None):
+            ssum, ssq = torch.zeros(k, device=_dev()), torch.zeros(k, device=_dev())
+            y = C.conv2d_fprop(x, _w2d(wt), R, R, stride, pad, stats=(ssum, ssq))
+            _close(y, ref, 1e-2, f"fprop{case} bn={bn} cg={cg} patch={pt}")
+            _close(ssum, y.float().sum(dim=(0, 1, 2)), 2e-3, f"stats bn={bn} cg={cg} patch={pt}")
+    for bn, cg, pt in C.tile_candidates(c, R, R, stride, pad, k, w, h):
+        with C.force_config(bn, cg, pt is not None):
+            dx = C.conv2d_dgrad(dy, _wt2d(wt), R, R, stride, pad, (h, w), addend=add)
+            _close(dx, ref_dx, 1e-2, f"dgrad+add{case} bn={bn} cg={cg} patch={pt}")
+
+
+def test_autotune_picks_and_caches():
+    from deeplearning_mpi_b200.ops import conv as C
+
+    if not C._AUTOTUNE:
+        pytest.skip("DMPI_AUTOTUNE=0")
+    _torch_setup()
+    x = _rand(4, 14, 14, 256)
+    wt = _rand(512, 256, 1, 1, scale=256 ** -0.5)
+    C._tuned.clear()
+    y1 = C.conv2d_fprop(x, _w2d(wt), 1, 1)
+    keys = [k for k in C._tuned if k[0] == "fprop"]
+    assert len(keys) == 1 and C._tuned[keys[0]] in C.tile_candidates(512, 1, 1, 1, 0, 256, 14, 14)
+    y2 = C.conv2d_fprop(x, _w2d(wt), 1, 1)
+    assert torch.equal(y1, y2)
