@@ -135,11 +135,39 @@ static int lgrid(long long items) {
   return b < 1 ? 1 : static_cast<int>(b);
 }
 
-// Clears a byte range with the copy engine's memset (no SM time, graph-capturable): gradient arena, BatchNorm
-// accumulators, loss accumulators — everything the step has to start from zero.
+// Clears a byte range (gradient arena, BatchNorm / loss accumulators - everything a step has to start from zero) with
+// a plain store kernel.  Not cudaMemsetAsync: inside a replayed CUDA graph a memset NODE delays the kernel behind it by
+// ~16 us on this driver (measured with bench/timeline.py: 4-byte memset -> next kernel), a kernel node by ~0.3 us.
+namespace dmpi {
+__global__ void __launch_bounds__(256) zero_fill_kernel(uint4* __restrict__ p16, long long nvec, unsigned char* __restrict__ tail,
+                                                        int ntail, unsigned char* __restrict__ head, int nhead) {
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < nvec; i += stride) p16[i] = z;
+  if (blockIdx.x == 0) {
+    if (static_cast<int>(threadIdx.x) < ntail) tail[threadIdx.x] = 0;
+    if (static_cast<int>(threadIdx.x) < nhead) head[threadIdx.x] = 0;
+  }
+}
+}  // namespace dmpi
+
 extern "C" int dmpi_memset_async(void* p, int value, long long bytes, void* stream) {
   if (bytes <= 0) return 0;
-  return cudaMemsetAsync(p, value, static_cast<size_t>(bytes), static_cast<cudaStream_t>(stream)) == cudaSuccess ? 0 : -2;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (value != 0)
+    return cudaMemsetAsync(p, value, static_cast<size_t>(bytes), s) == cudaSuccess ? 0 : -2;
+  unsigned char* b = static_cast<unsigned char*>(p);
+  const int nhead = static_cast<int>((16 - (reinterpret_cast<uintptr_t>(b) & 15)) & 15) < bytes
+                        ? static_cast<int>((16 - (reinterpret_cast<uintptr_t>(b) & 15)) & 15) : static_cast<int>(bytes);
+  const long long body = bytes - nhead;
+  const long long nvec = body / 16;
+  const int ntail = static_cast<int>(body - nvec * 16);
+  long long blocks = (nvec + 256 * 8 - 1) / (256 * 8);
+  if (blocks < 1) blocks = 1;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  dmpi::zero_fill_kernel<<<static_cast<int>(blocks), 256, 0, s>>>(reinterpret_cast<uint4*>(b + nhead), nvec,
+                                                                  b + nhead + nvec * 16, ntail, b, nhead);
+  return cudaGetLastError() == cudaSuccess ? 0 : -2;
 }
 
 extern "C" int dmpi_nchw_to_nhwc8_padded(const float* x, void* out, int N, int C, int H, int W, int pad, int Hp, int Wp,

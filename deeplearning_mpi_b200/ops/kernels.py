@@ -35,13 +35,29 @@ def _rows_ld(x: torch.Tensor) -> Tuple[int, int]:
 
 
 def zero_(t: torch.Tensor) -> torch.Tensor:
-    """In-place clear of a dense tensor with cudaMemsetAsync on the current stream (CPU tensors: Tensor.zero_)."""
+    """In-place clear of a dense tensor with the store kernel behind dmpi_memset_async (CPU tensors: Tensor.zero_)."""
     if not t.is_cuda:
         return t.zero_()
     assert t.is_contiguous()
     rc = N.cuda().dmpi_memset_async(_p(t), 0, t.numel() * t.element_size(), N.stream_ptr())
+    N.count_launch()
     _chk(rc, "dmpi_memset_async")
     return t
+
+
+def copy_(dst: torch.Tensor, src: torch.Tensor) -> torch.Tensor:
+    """dst <- src on the current stream with the framework's own copy kernel when both are dense, same dtype and a
+    multiple of 16 bytes (a memcpy NODE in a replayed CUDA graph costs several us of latency); Tensor.copy_ otherwise."""
+    nbytes = src.numel() * src.element_size()
+    if (dst.is_cuda and src.is_cuda and dst.dtype == src.dtype and dst.is_contiguous() and src.is_contiguous()
+            and dst.shape == src.shape and nbytes % 16 == 0 and nbytes > 0 and dst.data_ptr() % 16 == 0
+            and src.data_ptr() % 16 == 0 and dst.device == src.device):
+        blocks = max(1, min(148 * 4, nbytes // (512 * 16 * 4)))
+        rc = N.cuda().dmpi_peer_copy(_p(dst), _p(src), nbytes, blocks, N.stream_ptr())
+        N.count_launch()
+        _chk(rc, "dmpi_peer_copy")
+        return dst
+    return dst.copy_(src, non_blocking=True)
 
 
 # ------------------------------------------------------------------------------------------ BatchNorm

@@ -23,6 +23,7 @@ from typing import Callable, Sequence
 import torch
 
 from .. import _native as N
+from ..ops import kernels as K
 
 
 class GraphedTrainStep:
@@ -60,7 +61,7 @@ class GraphedTrainStep:
             return self.step_fn(*inputs)
         for dst, src in zip(self.static_inputs, inputs):
             if dst.data_ptr() != src.data_ptr():
-                dst.copy_(src, non_blocking=True)
+                K.copy_(dst, src)
         self.graph.replay()
         N.count_launch(self.launches_per_replay)
         return self.static_out

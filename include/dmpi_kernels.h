@@ -127,7 +127,9 @@ int dmpi_scale_by_clip(float* g, long long n, const float* sumsq, float max_norm
 int dmpi_cast_bf16(const float* src, void* dst, long long n, void* stream);
 
 /* ---- layout / staging (ref:pytorch/resnet/main.py:126 input .to(device)) */
-int dmpi_memset_async(void* p, int value, long long bytes, void* stream); /* cudaMemsetAsync on `stream` */
+/* Fills [p, p + bytes) on `stream`; value 0 runs a store kernel (a memset NODE in a replayed CUDA graph delays the next
+ * kernel by ~16 us), other values go to cudaMemsetAsync. */
+int dmpi_memset_async(void* p, int value, long long bytes, void* stream);
 int dmpi_nchw_to_nhwc8_padded(const float* x, void* out, int N, int C, int H, int W, int pad, int Hp, int Wp,
                               void* stream);
 int dmpi_nchw_to_nhwc(const float* x, void* out, int N, int C, int HW, void* stream);

@@ -437,6 +437,19 @@ def test_linear_bwd_prep_and_scale():
     z = torch.randn(1000, device=DEV)
     K.zero_(z)
     assert torch.all(z == 0)
+    # unaligned heads / tails and tiny ranges: only the requested bytes are cleared
+    for lo, hi in [(3, 1001), (1, 2), (5, 9), (0, 1 << 20), (7, (1 << 20) + 5)]:
+        buf = torch.ones((1 << 20) + 16, device=DEV)
+        K.zero_(buf[lo:hi])
+        assert torch.all(buf[lo:hi] == 0) and torch.all(buf[:lo] == 1) and torch.all(buf[hi:] == 1), (lo, hi)
+    hb = torch.ones(64, dtype=torch.uint8, device=DEV)
+    K.zero_(hb[5:18])
+    assert hb[5:18].sum() == 0 and hb.sum() == 64 - 13
+    src = torch.randn(3, 1024, device=DEV)
+    dst = torch.empty_like(src)
+    assert torch.equal(K.copy_(dst, src), src)
+    odd = torch.randn(5, device=DEV)
+    assert torch.equal(K.copy_(torch.empty_like(odd), odd), odd)
 
 
 def test_oneshot_alternating_sizes_and_blocks():
