@@ -48,7 +48,8 @@ def build_data_loaders(cfg, args):
         dataset = SyntheticSegmentation(args.synthetic_size, (args.image_size, args.image_size), seed=cfg.random_seed)
         workers = 0
     else:
-        dataset = CarvanaDataset(images_dir=os.path.join("data", "images"), mask_dir=os.path.join("data", "masks"), scale=0.2)
+        # rank 0 alone decodes the masks for the value palette and shares it through the process group
+        dataset = CarvanaDataset.shared(os.path.join("data", "images"), os.path.join("data", "masks"), 0.2)
         workers = int((os.cpu_count() or 2) // 2)
     train_size = int(0.8 * len(dataset))
     # the split uses the global torch RNG, identical on every rank thanks to the shared seed
