@@ -154,6 +154,16 @@ __global__ void __launch_bounds__(256) cast_bf16_kernel(const float* __restrict_
   }
 }
 
+__global__ void __launch_bounds__(256) cast_f32_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ dst,
+                                                       long long n) {
+  const long long n4 = n >> 2;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const uint2 v = reinterpret_cast<const uint2*>(src)[i];
+    reinterpret_cast<float4*>(dst)[i] = make_float4(bf16lo(v.x), bf16hi(v.x), bf16lo(v.y), bf16hi(v.y));
+  }
+}
+
 static int flat_grid(long long n) {
   long long b = (n / 4 + 255) / 256;
   if (b > 148LL * 8) b = 148LL * 8;
@@ -204,6 +214,12 @@ extern "C" int dmpi_sumsq(const float* g, long long n, float* out, void* stream)
 extern "C" int dmpi_scale_by_clip(float* g, long long n, const float* sumsq, float max_norm, void* stream) {
   if (n % 4) return -1;
   scale_by_clip_kernel<<<flat_grid(n), 256, 0, static_cast<cudaStream_t>(stream)>>>(g, n, sumsq, max_norm);
+  return cudaGetLastError() == cudaSuccess ? 0 : -2;
+}
+
+extern "C" int dmpi_cast_f32(const void* src, float* dst, long long n, void* stream) {
+  if (n % 4) return -1;
+  cast_f32_kernel<<<flat_grid(n), 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(src), dst, n);
   return cudaGetLastError() == cudaSuccess ? 0 : -2;
 }
 

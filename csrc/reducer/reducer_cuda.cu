@@ -16,11 +16,13 @@
 #include <vector>
 
 #include "../../include/dmpi_comm.h"
+#include "../../include/dmpi_kernels.h"
 
 struct ReducerCuda {
   dmpi_comm_ptrs ptrs;
   int world = 1;
   std::vector<long long> off, bytes;
+  long long off_base = 0;  // offset of the gradient region (= of the lowest bucket)
   std::vector<cudaEvent_t> ready;
   cudaEvent_t done = nullptr;
   cudaEvent_t fwd_done = nullptr, bcast_done = nullptr;  // buffer broadcast on the comm stream (see side_broadcast)
@@ -31,6 +33,7 @@ struct ReducerCuda {
   long long oneshot_max_bytes = 0, slot_bytes = 0;
   int nblocks = 32;
   int wire_bf16 = 0;
+  long long wire_off = -1;  // byte offset (in the data region) of the bf16 wire buffer; -1: none
   bool use_nvls = false;
   float scale = 1.f;
   int launched = 0;
@@ -46,6 +49,8 @@ extern "C" void* dmpi_reducer_cuda_create(const dmpi_comm_ptrs* ptrs, int n_buck
   r->world = ptrs->world;
   r->off.assign(off_bytes, off_bytes + n_buckets);
   r->bytes.assign(nbytes, nbytes + n_buckets);
+  r->off_base = n_buckets > 0 ? r->off[0] : 0;
+  for (long long o : r->off) r->off_base = o < r->off_base ? o : r->off_base;
   r->ready.resize(n_buckets);
   for (auto& e : r->ready) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
   cudaEventCreateWithFlags(&r->done, cudaEventDisableTiming);
@@ -65,6 +70,19 @@ extern "C" void* dmpi_reducer_cuda_create(const dmpi_comm_ptrs* ptrs, int n_buck
   r->use_nvls = ptrs->mc_data != nullptr && ptrs->world > 2;
   if (const char* e = getenv("DMPI_NVLS")) r->use_nvls = ptrs->mc_data != nullptr && atoi(e) != 0;
   return r;
+}
+
+// bf16 wire buffer: `bytes` >= half the gradient region, 16-byte aligned offset inside the symmetric data region.
+extern "C" int dmpi_reducer_cuda_set_wire_buffer(void* h, long long off_bytes, long long bytes) {
+  ReducerCuda* r = static_cast<ReducerCuda*>(h);
+  long long need = 0;
+  for (size_t b = 0; b < r->off.size(); ++b) {
+    const long long end = (r->off[b] - r->off_base + r->bytes[b]) / 2;
+    need = end > need ? end : need;
+  }
+  if (off_bytes % 16 || bytes < need) return -1;
+  r->wire_off = off_bytes;
+  return 0;
 }
 
 extern "C" void dmpi_reducer_cuda_destroy(void* h) {
@@ -91,7 +109,20 @@ extern "C" void dmpi_reducer_cuda_launch(void* h, int bucket) {
   cudaEventRecord(r->ready[bucket], r->compute);
   cudaStreamWaitEvent(r->comm, r->ready[bucket], 0);
   int rc = 0;
-  if (r->world > 1) {
+  if (r->world > 1 && r->wire_bf16 && r->wire_off >= 0 && r->bytes[bucket] > r->oneshot_max_bytes) {
+    // bf16 wire format for the large buckets: cast the fp32 bucket into the (symmetric, multicast-mapped) wire buffer,
+    // all-reduce that with fp32 accumulation (half the NVLink bytes), cast the mean back.  Three launches on the comm
+    // stream instead of one; worth it where the link, not the launch, bounds the bucket.
+    const long long n = r->bytes[bucket] / 4;
+    const long long woff = r->wire_off + (r->off[bucket] - r->off_base) / 2;
+    char* base = static_cast<char*>(r->ptrs.data[r->ptrs.rank_base]);
+    rc = dmpi_cast_bf16(reinterpret_cast<const float*>(base + r->off[bucket]), base + woff, n, r->comm);
+    if (rc == 0) {
+      if (r->use_nvls) rc = dmpi_allreduce_nvls(&r->ptrs, woff, n * 2, DMPI_BF16, r->scale, r->nblocks, r->comm);
+      else rc = dmpi_allreduce_twoshot(&r->ptrs, woff, n * 2, DMPI_BF16, r->scale, r->nblocks, 0, r->comm);
+    }
+    if (rc == 0) rc = dmpi_cast_f32(base + woff, reinterpret_cast<float*>(base + r->off[bucket]), n, r->comm);
+  } else if (r->world > 1) {
     if (r->bytes[bucket] <= r->oneshot_max_bytes && r->bytes[bucket] <= r->slot_bytes)
       rc = dmpi_allreduce_oneshot(&r->ptrs, r->off[bucket], r->bytes[bucket], r->wire_bf16, r->scale, r->slot_bytes,
                                   r->nblocks, 0, r->comm);

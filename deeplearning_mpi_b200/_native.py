@@ -215,6 +215,7 @@ def _bind_cuda(lib) -> None:
     _sig(lib, "dmpi_sumsq", I, [VP, I64, VP, VP])
     _sig(lib, "dmpi_scale_by_clip", I, [VP, I64, VP, F, VP])
     _sig(lib, "dmpi_cast_bf16", I, [VP, VP, I64, VP])
+    _sig(lib, "dmpi_cast_f32", I, [VP, VP, I64, VP])
     # layout
     _sig(lib, "dmpi_memset_async", I, [VP, I, I64, VP])
     _sig(lib, "dmpi_nchw_to_nhwc8_padded", I, [VP, VP, I, I, I, I, I, I, I, VP])
@@ -261,6 +262,7 @@ def _bind_cuda(lib) -> None:
     # reducer (CUDA glue)
     _sig(lib, "dmpi_reducer_cuda_create", VP, [VP, I, C.POINTER(I64), C.POINTER(I64), F, I64, I64, I, I])
     _sig(lib, "dmpi_reducer_cuda_destroy", None, [VP])
+    _sig(lib, "dmpi_reducer_cuda_set_wire_buffer", I, [VP, I64, I64])
     _sig(lib, "dmpi_reducer_cuda_begin", None, [VP, VP])
     _sig(lib, "dmpi_reducer_cuda_launch", None, [VP, I])
     _sig(lib, "dmpi_reducer_cuda_finalize", I, [VP])

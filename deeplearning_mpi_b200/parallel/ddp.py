@@ -46,7 +46,8 @@ _MIB = 1 << 20
 class DistributedDataParallel(nn.Module):
     def __init__(self, module: nn.Module, device_ids: Optional[List[int]] = None, output_device=None,
                  broadcast_buffers: bool = True, bucket_cap_mb: float = 25.0, first_bucket_mb: float = 1.0,
-                 find_unused_parameters: bool = False, gradient_as_bucket_view: bool = True, **_ignored):
+                 find_unused_parameters: bool = False, gradient_as_bucket_view: bool = True,
+                 grad_wire_dtype: Optional[str] = None, **_ignored):
         super().__init__()
         st = D._require()
         self.module = module
@@ -55,6 +56,13 @@ class DistributedDataParallel(nn.Module):
         self._st = st
         self.world, self.rank = st.world, st.rank
         self._fault = FaultInjector()  # DMPI_FAULT test hook; inactive unless the variable is set
+        # gradient wire format of the large buckets: None / "fp32" = exact fp32 sums (default), "bf16" = each rank's
+        # bucket is rounded to bf16 for the transfer and summed in fp32 (half the NVLink bytes; DMPI_WIRE_BF16=1)
+        if grad_wire_dtype is None and os.environ.get("DMPI_WIRE_BF16", "0") == "1":
+            grad_wire_dtype = "bf16"
+        if grad_wire_dtype not in (None, "fp32", "bf16"):
+            raise ValueError("grad_wire_dtype must be None, 'fp32' or 'bf16'")
+        self.grad_wire_dtype = grad_wire_dtype or "fp32"
         if find_unused_parameters:
             raise NotImplementedError("find_unused_parameters is not used by the reference and not supported")
         params = [p for p in module.parameters() if p.requires_grad]
@@ -73,9 +81,10 @@ class DistributedDataParallel(nn.Module):
             g_bytes = _round_up(total * 4, 256)
             p_bytes = g_bytes
             b_bytes = _round_up(buf_bytes, 256)
-            self._comm = st.new_comm(g_bytes + p_bytes + b_bytes)
-            self._off = {"grads": 0, "params": g_bytes, "buffers": g_bytes + p_bytes}
-            self._sizes = {"grads": g_bytes, "params": p_bytes, "buffers": b_bytes}
+            w_bytes = _round_up(g_bytes // 2, 256) if self.grad_wire_dtype == "bf16" else 0
+            self._comm = st.new_comm(g_bytes + p_bytes + b_bytes + w_bytes)
+            self._off = {"grads": 0, "params": g_bytes, "buffers": g_bytes + p_bytes, "wire": g_bytes + p_bytes + b_bytes}
+            self._sizes = {"grads": g_bytes, "params": p_bytes, "buffers": b_bytes, "wire": w_bytes}
             comm = self._comm
 
             def alloc(name: str, nbytes: int) -> torch.Tensor:
@@ -116,7 +125,11 @@ class DistributedDataParallel(nn.Module):
             nbytes = (C.c_int64 * self.n_buckets)(*[n * 4 for _, n in self.bucket_ranges])
             self._cuda_red = lib.dmpi_reducer_cuda_create(self._comm.ptrs, self.n_buckets, offs, nbytes,
                                                           1.0 / self.world, st.oneshot_max_bytes,
-                                                          self._comm.slot_bytes, 32, 0)
+                                                          self._comm.slot_bytes, 32,
+                                                          1 if self.grad_wire_dtype == "bf16" else 0)
+            if self.grad_wire_dtype == "bf16":
+                if lib.dmpi_reducer_cuda_set_wire_buffer(self._cuda_red, self._off["wire"], self._sizes["wire"]) != 0:
+                    raise RuntimeError("DDP: bf16 wire buffer could not be attached")
             host.dmpi_reducer_set_launch_cb(self._reducer, lib.dmpi_reducer_cuda_launch_fn(), self._cuda_red)
         self._out_buckets = (C.c_int * max(self.n_buckets, 1))()
         self._pending_work = []

@@ -125,6 +125,7 @@ int dmpi_adam_step_dev(float* p, const float* g, float* m, float* v, void* bf16_
 int dmpi_sumsq(const float* g, long long n, float* out, void* stream);
 int dmpi_scale_by_clip(float* g, long long n, const float* sumsq, float max_norm, void* stream);
 int dmpi_cast_bf16(const float* src, void* dst, long long n, void* stream);
+int dmpi_cast_f32(const void* src_bf16, float* dst, long long n, void* stream); /* n % 4 == 0 */
 
 /* ---- layout / staging (ref:pytorch/resnet/main.py:126 input .to(device)) */
 /* Fills [p, p + bytes) on `stream`; value 0 runs a store kernel (a memset NODE in a replayed CUDA graph delays the next

@@ -218,6 +218,35 @@ opt.step()
 torch.cuda.synchronize()
 all_equal(ddp.arena.flat_p, "parameters diverged after the rank-0-only eval")
 
+# ---- bf16 wire format (DistributedDataParallel(grad_wire_dtype="bf16")): large buckets travel as bf16, sums in fp32
+torch.manual_seed(300 + rank)
+model16 = resnet18(num_classes=10).to(dev)
+ddp16 = DistributedDataParallel(model16, device_ids=[dev.index], output_device=dev.index, grad_wire_dtype="bf16")
+
+
+class _Trigger16(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, t):
+        return t.clone()
+
+    @staticmethod
+    def backward(ctx, grad):
+        idx16 = torch.arange(ddp16.arena.flat_g.numel(), device=dev, dtype=torch.float32)
+        ddp16.arena.flat_g.copy_(((idx16 % 977) * 0.003 - 1.0) * (rank + 1))
+        for i in range(len(ddp16.arena.slots)):
+            ddp16._mark_ready(i)
+        return grad
+
+
+ddp16._arm()
+_Trigger16.apply(torch.ones(1, device=dev, requires_grad=True)).sum().backward()
+torch.cuda.synchronize()
+idx16 = torch.arange(ddp16.arena.flat_g.numel(), device=dev, dtype=torch.float32)
+want16 = ((idx16 % 977) * 0.003 - 1.0) * (sum(r + 1 for r in range(world)) / world)
+err16 = (ddp16.arena.flat_g - want16).abs().max().item()
+assert err16 <= 1.2e-2 * want16.abs().max().item(), f"bf16-wire all-reduce error {err16}"
+all_equal(ddp16.arena.flat_g, "bf16-wire gradients differ across ranks")
+
 tdist.barrier()
 tdist.destroy_process_group()
 dist.destroy_process_group()
