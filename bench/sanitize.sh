@@ -14,7 +14,9 @@ PY="python -m pytest -x -q -m gpu -p no:cacheprovider"
 export DMPI_COMM_TIMEOUT_S=0
 rc=0
 if [ "$tool" = "memcheck" ]; then
-  $CS --tool memcheck --error-exitcode 9 --launch-timeout 120 $PY tests/test_kernels_gpu.py tests/test_conv_gpu.py || rc=$?
+  # SANITIZE_SELECT narrows the run (pytest -k expression) when GPU minutes are short
+  $CS --tool memcheck --error-exitcode 9 --launch-timeout 120 $PY tests/test_kernels_gpu.py tests/test_conv_gpu.py \
+      ${SANITIZE_SELECT:+-k "$SANITIZE_SELECT"} || rc=$?
 else
   $CS --tool "$tool" --error-exitcode 9 $PY tests/test_kernels_gpu.py -k "bn or maxpool or head or allreduce" || rc=$?
 fi

@@ -47,6 +47,32 @@ __global__ void __launch_bounds__(kBnThreads) bn_fwd_kernel(const BnFwdArgs a) {
   extern __shared__ float sm[];  // scale[C], shift[C]
   float* scale = sm;
   float* shift = sm + a.C;
+  // Thread (tx, ty): tx owns 8 consecutive channels (16 bytes) for the whole kernel -> scale/shift in registers,
+  // ty strides the rows; U rows per iteration with all loads issued up front.
+  const int vecC = a.C >> 3;
+  const int tx = threadIdx.x % vecC;
+  const int ty = threadIdx.x / vecC;
+  const int rows_per_block = blockDim.x / vecC;
+  const bool active = ty < rows_per_block;
+  const int c0 = tx << 3;
+  const long long stride = static_cast<long long>(gridDim.x) * rows_per_block;
+  long long row0 = blockIdx.x * static_cast<long long>(rows_per_block) + ty;
+  // The first batch of rows is requested BEFORE the per-channel constants are derived: the two are independent, and
+  // with the constants first (then a block barrier, then the rows) every launch paid two memory round trips in a row -
+  // a third of the run time of the small late-layer launches.
+  uint4 v[U], r[kRes ? U : 1];
+  auto load_rows = [&](long long base) {
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long row = base + u * stride;
+      if (row < a.M) {
+        v[u] = *reinterpret_cast<const uint4*>(a.y + row * a.ldy + c0);
+        if (kRes) r[u] = *reinterpret_cast<const uint4*>(a.res + row * a.ldr + c0);
+      }
+    }
+  };
+  if (active) load_rows(row0);
+
   const float invM = 1.f / static_cast<float>(a.M);
   for (int c = threadIdx.x; c < a.C; c += blockDim.x) {
     float mean, invstd;
@@ -74,32 +100,14 @@ __global__ void __launch_bounds__(kBnThreads) bn_fwd_kernel(const BnFwdArgs a) {
   }
   if (blockIdx.x == 0 && threadIdx.x == 0 && a.training && a.num_batches_tracked) *a.num_batches_tracked += 1;
   __syncthreads();
-
-  // Thread (tx, ty): tx owns 8 consecutive channels (16 bytes) for the whole kernel -> scale/shift in registers,
-  // ty strides the rows; two rows per iteration with all loads issued up front.
-  const int vecC = a.C >> 3;
-  const int tx = threadIdx.x % vecC;
-  const int ty = threadIdx.x / vecC;
-  const int rows_per_block = blockDim.x / vecC;
-  if (ty >= rows_per_block) return;
-  const int c0 = tx << 3;
+  if (!active) return;
   float sc[8], sh[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     sc[j] = scale[c0 + j];
     sh[j] = shift[c0 + j];
   }
-  const long long stride = static_cast<long long>(gridDim.x) * rows_per_block;
-  for (long long row0 = blockIdx.x * static_cast<long long>(rows_per_block) + ty; row0 < a.M; row0 += U * stride) {
-    uint4 v[U], r[kRes ? U : 1];
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const long long row = row0 + u * stride;
-      if (row < a.M) {
-        v[u] = *reinterpret_cast<const uint4*>(a.y + row * a.ldy + c0);
-        if (kRes) r[u] = *reinterpret_cast<const uint4*>(a.res + row * a.ldr + c0);
-      }
-    }
+  while (row0 < a.M) {
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const long long row = row0 + u * stride;
@@ -125,6 +133,8 @@ __global__ void __launch_bounds__(kBnThreads) bn_fwd_kernel(const BnFwdArgs a) {
       *reinterpret_cast<uint4*>(a.out + row * a.ldo + c0) = make_uint4(oi[0], oi[1], oi[2], oi[3]);
       if (a.relu_mask) a.relu_mask[row * vecC + tx] = static_cast<uint8_t>(bits);
     }
+    row0 += U * stride;
+    if (row0 < a.M) load_rows(row0);
   }
 }
 
