@@ -67,7 +67,7 @@ template <int BN, int CG>
 struct IgemmCfg {
   // Pipeline depth is what hides the ~1000-cycle L2/HBM latency of the TMA loads: one stage is only 128 (BN=64),
   // 256 (BN=128) or 512 (BN=256) tensor-core cycles of work, so the narrow tiles need the most stages.
-  static constexpr int kStages = CG == 2 ? (BN == 256 ? 5 : 6) : (BN == 256 ? 3 : (BN == 128 ? 5 : 8));
+  static constexpr int kStages = CG == 2 ? (BN == 256 ? 5 : (BN == 128 ? 6 : 9)) : (BN == 256 ? 3 : (BN == 128 ? 5 : 8));
   static constexpr int kBRows = BN / CG;              // B rows (filters) this CTA loads per K block
   static constexpr int kBBytes = kBRows * kBlockK * 2;
   static constexpr int kSubN = BN < 128 ? BN : 128;   // columns per staged sub-tile
@@ -78,7 +78,8 @@ struct IgemmCfg {
       kStages * (kABytes + kBBytes) + kOutBufs * kOutBytes + 1024 /*align slack*/ + 512 /*barriers*/ + 128 /*tap table*/;
   static constexpr int kRingBytes = kStages * (kABytes + kBBytes);  // patch mode re-carves this region (2 rings)
   static constexpr int kTmemCols = 2 * BN;
-  static_assert(CG == 1 || BN >= 128, "CTA pairs are used for the wide tiles only");
+  // (BN = 64 with pairs: each CTA holds 32 filters of every tile - for narrow layers whose filter is too large to stay
+  // resident, e.g. the UNet decoder's 192 -> 64 at 512x512, where the streamed filter taps were the L2 -> SM bottleneck)
 };
 
 // Walks the persistent tile sequence without a division per tile: the grid step is decomposed once into
@@ -1069,7 +1070,7 @@ extern "C" int dmpi_igemm_run_add(dmpi_conv_plan* plan, const void* a, const voi
     kp.pa_bytes = kp.pw * ph * 128;
     kp.pa_stride = ((rows_alloc * 128 + 1023) / 1024) * 1024;
     const bool pair = d.cta_group == 2;
-    const int ring = d.bn == 64 ? IgemmCfg<64, 1>::kRingBytes
+    const int ring = d.bn == 64 ? (pair ? IgemmCfg<64, 2>::kRingBytes : IgemmCfg<64, 1>::kRingBytes)
                                 : (d.bn == 128 ? (pair ? IgemmCfg<128, 2>::kRingBytes : IgemmCfg<128, 1>::kRingBytes)
                                                : (pair ? IgemmCfg<256, 2>::kRingBytes : IgemmCfg<256, 1>::kRingBytes));
     const int bbytes = (pair ? d.bn / 2 : d.bn) * kBlockK * 2;  // a CTA of a pair holds half of every filter-tap tile
@@ -1177,7 +1178,8 @@ extern "C" int dmpi_igemm_run_add(dmpi_conv_plan* plan, const void* a, const voi
   if (d.cta_group == 2) {
     if (d.bn == 128) return launch_igemm<128, 2>(kp, plan->num_sms, s, plan->stat_scratch_bytes);
     if (d.bn == 256) return launch_igemm<256, 2>(kp, plan->num_sms, s, plan->stat_scratch_bytes);
-    set_err("igemm: CTA pairs need bn 128 or 256");
+    if (d.bn == 64) return launch_igemm<64, 2>(kp, plan->num_sms, s, plan->stat_scratch_bytes);
+    set_err("igemm: bn must be 64, 128 or 256");
     return -2;
   }
   switch (d.bn) {

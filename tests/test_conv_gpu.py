@@ -350,6 +350,8 @@ TUNE_CASES = [
     (4, 14, 14, 256, 512, 1, 1, 0),    # flat 1x1: every N tile / pair combination
     (1, 130, 136, 128, 128, 3, 1, 1),  # wide image: row-segment patch tiles with pairs
     (3, 7, 7, 512, 512, 3, 1, 1),      # tiny M: wave quantisation decides
+    (1, 40, 136, 192, 64, 3, 1, 1),    # UNet decoder shape: 3 channel blocks into 64 filters (64-wide tile with CTA pairs)
+    (1, 40, 72, 64, 192, 3, 1, 1),     # 192 filters: one partly filled 256-wide tile vs two 128-wide ones
 ]
 
 
