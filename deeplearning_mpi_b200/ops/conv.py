@@ -89,6 +89,7 @@ def _is_flat(n, h, w, sn, sh, sw) -> bool:
 
 
 _BN256_MIN_K = int(os.environ.get("DMPI_BN256_MIN_K", "256"))
+_BN256_ODD = os.environ.get("DMPI_BN256_ODD", "1") == "1"  # A/B switch of the rule for widths such as 192
 
 
 def _pick_bn(n_out: int, ktot: int = 1 << 30) -> int:
@@ -101,7 +102,7 @@ def _pick_bn(n_out: int, ktot: int = 1 << 30) -> int:
         return 256
     # widths such as 192 (the UNet decoder's 64 -> [128 | 64] concat gradient): two 128-wide tiles and one 256-wide tile
     # pad to the same 256 columns, but the wide tile reads the pixel operand once (tuner: 866 vs 1 099 us at 512x512)
-    if n_out > 128 and ktot >= _BN256_MIN_K and -(-n_out // 256) * 256 <= -(-n_out // 128) * 128:
+    if _BN256_ODD and n_out > 128 and ktot >= _BN256_MIN_K and -(-n_out // 256) * 256 <= -(-n_out // 128) * 128:
         return 256
     return 128
 

@@ -218,6 +218,45 @@ opt.step()
 torch.cuda.synchronize()
 all_equal(ddp.arena.flat_p, "parameters diverged after the rank-0-only eval")
 
+# ---- loss curves: this framework's DDP against stock torch DDP (torchvision ResNet-18, cuDNN, fp32, NCCL) from the same
+# weights, every rank on its own batches (multi-GPU form)
+import torch.nn.functional as F  # noqa: E402
+import torchvision  # noqa: E402
+
+torch.manual_seed(77)                      # same initial weights on every rank and in both stacks
+ours_m = resnet18(num_classes=10).to(dev)
+stock_m = torchvision.models.resnet18(weights=None)
+stock_m.fc = torch.nn.Linear(512, 10)
+stock_m.load_state_dict(ours_m.state_dict())
+stock_m = stock_m.to(dev).train()
+ours_ddp = DistributedDataParallel(ours_m, device_ids=[dev.index], output_device=dev.index)
+stock_ddp = torch.nn.parallel.DistributedDataParallel(stock_m, device_ids=[dev.index], output_device=dev.index)
+o_opt = optim.SGD(ours_ddp.parameters(), lr=0.02, momentum=0.9, weight_decay=1e-5)
+s_opt = torch.optim.SGD(stock_ddp.parameters(), lr=0.02, momentum=0.9, weight_decay=1e-5)
+gen = torch.Generator().manual_seed(5)
+proto = torch.randn(10, 3, 32, 32, generator=gen)            # shared class prototypes: a learnable task
+gen_r = torch.Generator().manual_seed(900 + rank)            # rank-specific samples
+lo, ls = [], []
+for step_i in range(16):
+    yb = torch.randint(0, 10, (64,), generator=gen_r)
+    xb = (proto[yb] + 0.7 * torch.randn(64, 3, 32, 32, generator=gen_r)).to(dev)
+    yb = yb.to(dev)
+    o_opt.zero_grad()
+    l1 = dnn.cross_entropy(ours_ddp(xb), yb)
+    l1.backward()
+    o_opt.step()
+    s_opt.zero_grad()
+    l2 = F.cross_entropy(stock_ddp(xb), yb)
+    l2.backward()
+    s_opt.step()
+    lo.append(l1.item())
+    ls.append(l2.item())
+dl = [abs(a - b) for a, b in zip(lo, ls)]
+assert lo[-1] < 0.6 * lo[0] and ls[-1] < 0.6 * ls[0], (lo, ls)
+assert dl[0] < 2e-2 and sum(dl) / len(dl) < 0.12 and max(dl) < 0.35, f"rank {rank}: loss curves diverge {list(zip(lo, ls))}"
+all_equal(ours_ddp.arena.flat_p, "parameters diverged in the loss-curve run")
+del stock_ddp
+
 # ---- bf16 wire format (DistributedDataParallel(grad_wire_dtype="bf16")): large buckets travel as bf16, sums in fp32
 torch.manual_seed(300 + rank)
 model16 = resnet18(num_classes=10).to(dev)
