@@ -49,6 +49,9 @@ def parse_args():
     ap.add_argument("--no-graph", dest="graph", action="store_false",
                     help="ours: launch eagerly instead of replaying the CUDA graph of the whole iteration "
                          "(deeplearning_mpi_b200.utils.graph.GraphedTrainStep, the default)")
+    ap.add_argument("--max-seconds", type=float, default=1500.0,
+                    help="hard wall-clock limit of the whole run: a hung collective ends the process (exit code 3) "
+                         "instead of occupying the GPUs until an outer timeout fires")
     ap.set_defaults(graph=True, secondary=True)
     return ap.parse_args()
 
@@ -450,9 +453,22 @@ SECONDARY = (("unet", 16, 512), ("resnet18", 128, 32))   # BASELINE.json configs
                                                          # ref:pytorch/resnet/main.py:40-41,164)
 
 
+def _arm_global_watchdog(limit_s: float) -> None:
+    import threading
+
+    def _bail():
+        time.sleep(limit_s)
+        sys.stderr.write(f"bench.py: no result after {limit_s:.0f} s - giving up\n")
+        sys.stderr.flush()
+        os._exit(3)
+
+    threading.Thread(target=_bail, daemon=True).start()
+
+
 def main():
     args = parse_args()
     setup_env(args)
+    _arm_global_watchdog(args.max_seconds)
     import copy
 
     import torch
