@@ -69,6 +69,10 @@ extern "C" void* dmpi_reducer_cuda_create(const dmpi_comm_ptrs* ptrs, int n_buck
   // profiles/allreduce_sweep_w8.json: NVLS beats two-shot at every size above the one-shot range at W=8, loses at W=2
   r->use_nvls = ptrs->mc_data != nullptr && ptrs->world > 2;
   if (const char* e = getenv("DMPI_NVLS")) r->use_nvls = ptrs->mc_data != nullptr && atoi(e) != 0;
+  // profiles/allreduce_sweep_w8.json (round 2, 4 reductions in flight per thread): the NVLS kernel is as fast with 16
+  // blocks as with 32 or 64 at every bucket size (9.4 MB: 62 / 65 / 67 us, 25.3 MB: 103 / 109 / 115 us), so it takes
+  // half as many SMs away from the persistent convolution kernels it overlaps with; two-shot still wants 32
+  if (r->use_nvls && getenv("DMPI_COMM_BLOCKS") == nullptr && r->nblocks > 16) r->nblocks = 16;
   return r;
 }
 
