@@ -164,6 +164,12 @@ __global__ void __launch_bounds__(256) cast_f32_kernel(const __nv_bfloat16* __re
   }
 }
 
+// One-element bookkeeping on the device (Adam's step counter, the norm returned by clip_grad_norm_): keeps the training
+// step free of library kernels and graph-capturable.  op 0: dst = src + arg;  op 1: dst = sqrt(src).
+__global__ void scalar_op_kernel(float* dst, const float* src, int op, float arg) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) *dst = op == 0 ? *src + arg : sqrtf(*src);
+}
+
 static int flat_grid(long long n) {
   long long b = (n / 4 + 255) / 256;
   if (b > 148LL * 8) b = 148LL * 8;
@@ -208,6 +214,11 @@ extern "C" int dmpi_adam_step_dev(float* p, const float* g, float* m, float* v, 
 extern "C" int dmpi_sumsq(const float* g, long long n, float* out, void* stream) {
   if (n % 4) return -1;
   sumsq_kernel<<<flat_grid(n), 256, 0, static_cast<cudaStream_t>(stream)>>>(g, n, out);
+  return cudaGetLastError() == cudaSuccess ? 0 : -2;
+}
+
+extern "C" int dmpi_scalar_op(float* dst, const float* src, int op, float arg, void* stream) {
+  scalar_op_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(dst, src, op, arg);
   return cudaGetLastError() == cudaSuccess ? 0 : -2;
 }
 

@@ -213,6 +213,7 @@ def _bind_cuda(lib) -> None:
     _sig(lib, "dmpi_adam_step", I, [VP, VP, VP, VP, VP, I64, F, F, F, F, F, F, F, VP, F, VP])
     _sig(lib, "dmpi_adam_step_dev", I, [VP, VP, VP, VP, VP, I64, F, F, F, F, F, VP, VP, F, VP])
     _sig(lib, "dmpi_sumsq", I, [VP, I64, VP, VP])
+    _sig(lib, "dmpi_scalar_op", I, [VP, VP, I, F, VP])
     _sig(lib, "dmpi_scale_by_clip", I, [VP, I64, VP, F, VP])
     _sig(lib, "dmpi_cast_bf16", I, [VP, VP, I64, VP])
     _sig(lib, "dmpi_cast_f32", I, [VP, VP, I64, VP])

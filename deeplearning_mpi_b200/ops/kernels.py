@@ -294,6 +294,23 @@ def sumsq(g, n, out) -> None:
     _chk(rc, "dmpi_sumsq")
 
 
+def scalar_add_(t: torch.Tensor, value: float) -> torch.Tensor:
+    """t += value for a one-element fp32 device tensor (own kernel, graph-capturable)."""
+    rc = N.cuda().dmpi_scalar_op(_p(t), _p(t), 0, float(value), N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_scalar_op")
+    return t
+
+
+def scalar_sqrt(t: torch.Tensor) -> torch.Tensor:
+    """sqrt of a one-element fp32 device tensor into a new tensor (own kernel)."""
+    out = torch.empty_like(t)
+    rc = N.cuda().dmpi_scalar_op(_p(out), _p(t), 1, 0.0, N.stream_ptr())
+    N.count_launch()
+    _chk(rc, "dmpi_scalar_op")
+    return out
+
+
 def scale_by_clip(g, n, sumsq_t, max_norm) -> None:
     rc = N.cuda().dmpi_scale_by_clip(_p(g), n, _p(sumsq_t), float(max_norm), N.stream_ptr())
     N.count_launch()

@@ -85,7 +85,7 @@ class _FlatOptimizer:
         K.zero_(self._clip_sumsq)
         K.sumsq(a.flat_g, a.total_trainable, self._clip_sumsq)
         self._clip_max_norm = float(max_norm)
-        return self._clip_sumsq.sqrt()
+        return K.scalar_sqrt(self._clip_sumsq)
 
     def _take_clip(self):
         ss, mn = (self._clip_sumsq, self._clip_max_norm) if self._clip_max_norm > 0 else (None, 0.0)
@@ -162,7 +162,7 @@ class Adam(_FlatOptimizer):
                 self.state["exp_avg_sq"] = torch.zeros_like(a.flat_p)
                 # the step count also lives on the device so that a captured CUDA graph of the step stays correct
                 self.state["step_t"] = torch.full((), float(t - 1), dtype=torch.float32, device=a.device)
-            self.state["step_t"] += 1.0
+            K.scalar_add_(self.state["step_t"], 1.0)
             ss, mn = self._take_clip()
             K.adam_step_dev(a.flat_p, a.flat_g, self.state["exp_avg"], self.state["exp_avg_sq"], a.flat_s, a.total_trainable, lr,
                             b1, b2, eps, wd, self.state["step_t"], ss, mn)
@@ -189,5 +189,5 @@ def clip_grad_norm_(parameters, max_norm: float, norm_type: float = 2.0) -> torc
         ss = K.zero_(torch.empty((), dtype=torch.float32, device=a.device))
         K.sumsq(a.flat_g, a.total_trainable, ss)
         K.scale_by_clip(a.flat_g, a.total_trainable, ss, max_norm)
-        return ss.sqrt()
+        return K.scalar_sqrt(ss)
     return torch.nn.utils.clip_grad_norm_(params, max_norm, norm_type)

@@ -123,6 +123,8 @@ int dmpi_adam_step_dev(float* p, const float* g, float* m, float* v, void* bf16_
                        float beta1, float beta2, float eps, float wd, const float* step_dev, const float* clip_sumsq,
                        float max_norm, void* stream);
 int dmpi_sumsq(const float* g, long long n, float* out, void* stream);
+/* one-element device bookkeeping: op 0: *dst = *src + arg (Adam step counter); op 1: *dst = sqrt(*src) (gradient norm) */
+int dmpi_scalar_op(float* dst, const float* src, int op, float arg, void* stream);
 int dmpi_scale_by_clip(float* g, long long n, const float* sumsq, float max_norm, void* stream);
 int dmpi_cast_bf16(const float* src, void* dst, long long n, void* stream);
 int dmpi_cast_f32(const void* src_bf16, float* dst, long long n, void* stream); /* n % 4 == 0 */
