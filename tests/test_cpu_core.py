@@ -262,10 +262,18 @@ def test_conv_planner_invariants():
         for ktot in (64, 128, 256, 576, 4608):
             bn = CV._pick_bn(n_out, ktot)
             assert bn in (64, 128, 256) and (bn == 64) == (n_out <= 64)
-            assert bn != 256 or n_out % 256 == 0
+            # the 256-wide tile: exact multiples, or widths such as 192 that pad to the same columns with 128-wide tiles
+            assert bn != 256 or n_out % 256 == 0 or -(-n_out // 256) * 256 <= -(-n_out // 128) * 128
             cg = CV._pick_cg(bn, ktot)
             assert cg in (1, 2) and (cg == 1 or bn >= 128)
-    ring = {(64, 1): 192, (128, 1): 160, (256, 1): 144, (128, 2): 144, (256, 2): 160}  # KiB, igemm.cu IgemmCfg
+    ring = {(64, 1): 192, (64, 2): 180, (128, 1): 160, (256, 1): 144, (128, 2): 144, (256, 2): 160}  # KiB, igemm.cu IgemmCfg
+    for bn_, cg_ in ring:   # every candidate the autotuner may force fits its ring as well
+        for c_in in (64, 192):
+            t = CV._patch_geom(3, 3, 1, 1, c_in, 512, 512, bn_, cg_)
+            if t is not None:
+                pw = t[0] + 2
+                rows = max(128 + 2 * pw + 2, pw * (t[1] + 2))
+                assert 2 * (-(-rows * 128 // 1024) * 1024) + 2 * (bn_ * 64 * 2 // cg_) <= ring[(bn_, cg_)] * 1024
     for c_in in (64, 128, 256):
         for n_out in (64, 128, 256):
             for ow, oh in ((56, 56), (28, 28), (128, 128), (256, 256), (512, 512), (20, 12)):
