@@ -81,7 +81,7 @@ class _FlatOptimizer:
         a = self._resolve_arena()
         assert a is not None, "fused clipping needs arena-resident CUDA parameters"
         if self._clip_sumsq is None:
-            self._clip_sumsq = torch.zeros((), dtype=torch.float32, device=a.device)
+            self._clip_sumsq = torch.empty((), dtype=torch.float32, device=a.device)
         K.zero_(self._clip_sumsq)
         K.sumsq(a.flat_g, a.total_trainable, self._clip_sumsq)
         self._clip_max_norm = float(max_norm)
@@ -120,7 +120,7 @@ class SGD(_FlatOptimizer):
         first = self.step_count == 0
         if a is not None:
             if mom != 0 and "momentum_buffer" not in self.state:
-                self.state["momentum_buffer"] = torch.zeros_like(a.flat_p)
+                self.state["momentum_buffer"] = K.zero_(torch.empty_like(a.flat_p))
             ss, mn = self._take_clip()
             K.sgd_step(a.flat_p, a.flat_g, self.state.get("momentum_buffer"), a.flat_s, a.total_trainable, lr, mom, damp, wd,
                        first, ss, mn)
@@ -158,8 +158,8 @@ class Adam(_FlatOptimizer):
         a = self._resolve_arena()
         if a is not None:
             if "exp_avg" not in self.state:
-                self.state["exp_avg"] = torch.zeros_like(a.flat_p)
-                self.state["exp_avg_sq"] = torch.zeros_like(a.flat_p)
+                self.state["exp_avg"] = K.zero_(torch.empty_like(a.flat_p))
+                self.state["exp_avg_sq"] = K.zero_(torch.empty_like(a.flat_p))
                 # the step count also lives on the device so that a captured CUDA graph of the step stays correct
                 self.state["step_t"] = torch.full((), float(t - 1), dtype=torch.float32, device=a.device)
             K.scalar_add_(self.state["step_t"], 1.0)

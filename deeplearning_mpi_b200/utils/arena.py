@@ -99,7 +99,15 @@ class ParamArena:
         self.module = module
         self.device = device
         self.is_cuda = device.type == "cuda"
-        alloc = alloc or (lambda name, nbytes: torch.zeros(nbytes, dtype=torch.uint8, device=device))
+        def _zeros(shape, dtype):
+            """Zero-initialised device tensor without a library fill kernel (own zero-fill kernel on CUDA)."""
+            if not self.is_cuda:
+                return torch.zeros(shape, dtype=dtype, device=device)
+            t = torch.empty(shape, dtype=dtype, device=device)
+            self._zero(t)
+            return t
+
+        alloc = alloc or (lambda name, nbytes: _zeros(nbytes, torch.uint8))
 
         kinds: Dict[int, str] = {}
         for m in module.modules():
@@ -136,13 +144,18 @@ class ParamArena:
 
         self.flat_p = alloc("params", self.total * 4).view(torch.float32)
         self.flat_g = alloc("grads", self.total * 4).view(torch.float32)
-        self.flat_g.zero_()
-        self.flat_s = torch.zeros(self.total, dtype=torch.bfloat16, device=device) if self.is_cuda else None
+        self._zero(self.flat_g)
+        self.flat_s = _zeros(self.total, torch.bfloat16) if self.is_cuda else None
 
         with torch.no_grad():
             for s in self.slots:
                 dst = self.flat_p[s.offset: s.offset + s.numel]
-                dst.copy_(_physical(s.param.data, s.kind).reshape(-1))
+                src = s.param.data
+                if self.is_cuda and s.kind in ("conv", "stem", "convt"):
+                    # the [K,C,R,S] -> [K,R,S,C] re-layout happens once, on the host (two memcpys instead of a strided
+                    # library copy kernel per weight)
+                    src = src.cpu()
+                dst.copy_(_physical(src, s.kind).reshape(-1))
                 s.param.data = _logical_view(self.flat_p, s)
                 s.param.grad = _logical_view(self.flat_g, s) if s.param.requires_grad else None
 
@@ -203,9 +216,9 @@ class ParamArena:
                     toff += _round_up(k * npad)
                 elif s.kind == "stem":
                     k, c, r, q = s.shape
-                    self.stem_w[id(s.param)] = torch.zeros(k, r * 64, dtype=torch.bfloat16, device=device)
-                    self.stem_dw[id(s.param)] = torch.zeros(k, r * 64, dtype=torch.float32, device=device)
-            self.flat_t = torch.zeros(max(toff, PAD), dtype=torch.bfloat16, device=device)
+                    self.stem_w[id(s.param)] = _zeros((k, r * 64), torch.bfloat16)
+                    self.stem_dw[id(s.param)] = _zeros((k, r * 64), torch.float32)
+            self.flat_t = _zeros(max(toff, PAD), torch.bfloat16)
             entries = []
             for s in self.slots:
                 if s.t_offset < 0:
@@ -246,7 +259,8 @@ class ParamArena:
     def _build_bn_scratch(self) -> None:
         bns = [m for m in self.module.modules() if isinstance(m, nn.BatchNorm2d)]
         total = sum(4 * m.num_features for m in bns)
-        self.bn_scratch = torch.zeros(max(total, 4), dtype=torch.float32, device=self.device)
+        self.bn_scratch = torch.empty(max(total, 4), dtype=torch.float32, device=self.device)
+        self._zero(self.bn_scratch)
         o = 0
         for m in bns:
             c = m.num_features
