@@ -612,14 +612,15 @@ def test_example_trainers_graph_flag(example, tmp_path):
         (tmp_path / d).mkdir()
     if example == "resnet":
         cmd = [sys.executable, os.path.join(root, "examples", "resnet", "main.py"), "--synthetic", "--graph", "--num_epochs",
-               "3", "--batch_size", "64", "--synthetic_size", "256", "--learning_rate", "0.05"]
+               "8", "--batch_size", "64", "--synthetic_size", "128", "--learning_rate", "0.02"]
         pat = r"Epoch: (\d+), Loss: ([0-9.]+)"
     else:
         cmd = [sys.executable, os.path.join(root, "examples", "unet", "train.py"), "--synthetic", "--graph", "--num_epochs",
-               "3", "--batch_size", "4", "--synthetic_size", "20", "--image_size", "64", "--learning_rate", "0.001"]
+               "8", "--batch_size", "4", "--synthetic_size", "20", "--image_size", "64", "--learning_rate", "0.001"]
         pat = r"Epoch (\d+) finished with loss: ([0-9.]+)"
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env, cwd=str(tmp_path))
     assert r.returncode == 0, (r.stdout + r.stderr)[-3000:]
     losses = [float(m[1]) for m in re.findall(pat, r.stdout)]
     print(example, losses)
-    assert len(losses) == 3 and losses[-1] < losses[0]
+    # (random labels / blobs: the set is memorised over the epochs; single epochs may go up)
+    assert len(losses) == 8 and all(v == v for v in losses) and min(losses[4:]) < 0.9 * losses[0], losses
