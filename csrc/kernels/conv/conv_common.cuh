@@ -46,6 +46,12 @@ struct alignas(64) ConvKernelParams {
   // result does not depend on the order in which CTAs retire (fp32 atomics made whole-network gradients differ by
   // ~20 % run to run through ReLU gate flips).  Null: atomics.
   float* stat_scratch;
+  // igemm split-K (splits > 1, one CTA per tile, no patch mode): CTA b works on tile b % units over K slice b / units,
+  // parks its fp32 partial tile in sk_part[split][unit][128][BN]; the CTA that draws the last ticket of a tile adds the
+  // partials in split order (deterministic) and runs the normal epilogue.  For layers with only a handful of tiles,
+  // where every CTA otherwise streams its whole K at the bandwidth of a single SM.
+  float* sk_part;
+  unsigned int* sk_tickets;
   int dbg;  // -DDMPI_ABLATE builds only (otherwise always 0): 1 no TMA store, 2 no statistics, 4 no loads, 8 no MMAs
 };
 
@@ -61,6 +67,8 @@ struct dmpi_conv_plan {
   long long cached_add_strides[3];  // (sn, sh, sw) the addend map was encoded with: they are per-call arguments
   void* stat_scratch;
   long long stat_scratch_bytes;
+  void* sk_scratch;          // split-K: tickets (first kSkHeaderBytes, zero-initialised) + partial tiles
+  long long sk_scratch_bytes;
   bool maps_valid;
   int num_sms;
 };

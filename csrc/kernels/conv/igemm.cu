@@ -58,6 +58,7 @@ constexpr int kABytes = kTileM * kBlockK * 2;
 constexpr int kDetInFlight = 4;  // partial-sum rows a thread of the tail reduction keeps in flight
 constexpr int kTailCtas = 8;     // CTAs that share the deterministic statistics tail
 constexpr int kStatHdr = 64;  // floats reserved at the head of the statistics scratch (ticket counter)
+constexpr int kSkHeaderBytes = 4096;  // split-K scratch: one ticket per tile (<= 1024 tiles) ahead of the partial tiles
 
 // CG = 1: one CTA per tile.  CG = 2: a CTA pair (cluster of two SMs of one TPC) works on a 256-row tile with
 // tcgen05.mma.cta_group::2 — each CTA loads its own 128 A rows and only HALF of the B tile (the tensor cores of both
@@ -95,7 +96,10 @@ struct TileWalk {
     cg = cg_;
     const int m_units = (p.num_m_tiles + cg - 1) / cg;  // M tiles or M-tile pairs
     const int total = m_units * p.num_n_tiles;
-    const int first = blockIdx.x / cg, step = gridDim.x / cg;
+    // split-K: the grid holds `splits` CTAs per tile, CTA b takes tile b % total (exactly one work item each)
+    const bool sk = p.splits > 1;
+    const int first = sk ? static_cast<int>(blockIdx.x) % total : static_cast<int>(blockIdx.x) / cg;
+    const int step = sk ? total : static_cast<int>(gridDim.x) / cg;
     remaining = first < total ? (total - first + step - 1) / step : 0;
     n_blk = first % p.num_n_tiles;
     int m = (first / p.num_n_tiles) * cg + rank;
@@ -131,7 +135,8 @@ struct TileWalk {
   }
 };
 
-template <int BN, int CG>
+// SK: the split-K variant (a separate instantiation so that its extra registers do not touch the main kernels).
+template <int BN, int CG, bool SK = false>
 __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constant__ ConvKernelParams p) {
   using Cfg = IgemmCfg<BN, CG>;
   constexpr int S = Cfg::kStages;
@@ -206,6 +211,15 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
   const uint32_t tmem_base = *tmem_slot;
 
   const int num_kb = p.ntaps * p.cblocks;
+  // split-K slice of this CTA (the whole range without it)
+  const bool splitk = SK && p.splits > 1;
+  const int sk_units = p.num_m_tiles * p.num_n_tiles;
+  const int sk_split = splitk ? static_cast<int>(blockIdx.x) / sk_units : 0;
+  const int sk_unit = splitk ? static_cast<int>(blockIdx.x) % sk_units : 0;
+  const int kb_per = splitk ? (num_kb + p.splits - 1) / p.splits : num_kb;
+  const int kb_lo = sk_split * kb_per;
+  const int kb_hi = kb_lo + kb_per < num_kb ? kb_lo + kb_per : num_kb;
+  uint32_t* sk_flag = reinterpret_cast<uint32_t*>(smem_o + Cfg::kOutBufs * Cfg::kOutBytes + 512 + 120);  // 1: this CTA finalises
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -267,31 +281,34 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
       TileWalk tk;
       for (tk.init(p, CG, rank); tk.remaining > 0; tk.next(p)) {
         const int w0 = tk.tw * p.box_w, h0 = tk.th * p.box_h, n0 = tk.tn * p.box_n;
-        for (int t = 0; t < p.ntaps; ++t) {
+        int t = kb_lo / p.cblocks, cb = kb_lo - t * p.cblocks;
+        for (int kb = kb_lo; kb < kb_hi; ++kb) {
           const CUtensorMap* amap = &p.a_map[p.tap_view[t]];
           const int cw = w0 + p.tap_dw[t], ch = h0 + p.tap_dh[t], koff = p.tap_koff[t];
-          for (int cb = 0; cb < p.cblocks; ++cb) {
-            mbar_wait_spin(&empty[stage], phase ^ 1u);
-            if (DMPI_DBG(p, 4)) {  // experiment: no loads, barriers only (MMA runs on stale shared memory)
-              if (CG == 1 || rank == 0) mbar_arrive(&full[stage]);
-              else mbar_arrive_cluster(mapa_u32(smem_u32(&full[stage]), 0));
-            } else if (CG == 1) {
-              mbar_arrive_expect_tx(&full[stage], tx_bytes);
-              tma_load_4d(smem_a + stage * kABytes, amap, &full[stage], cb * kBlockK, cw, ch, n0);
-              tma_load_2d(smem_b + stage * Cfg::kBBytes, &p.b_map, &full[stage], koff + cb * kBlockK, tk.n_blk * BN);
-            } else {
-              // both CTAs report to the leader's barrier; the leader registers the bytes of the pair
-              const uint32_t lead_full = mapa_u32(smem_u32(&full[stage]), 0);
-              if (rank == 0) mbar_arrive_expect_tx(&full[stage], 2 * tx_bytes);
-              else mbar_arrive_cluster(lead_full);
-              tma_load_4d_pair(smem_a + stage * kABytes, amap, lead_full, cb * kBlockK, cw, ch, n0);
-              tma_load_2d_pair(smem_b + stage * Cfg::kBBytes, &p.b_map, lead_full, koff + cb * kBlockK,
-                               tk.n_blk * BN + rank * Cfg::kBRows);
-            }
-            if (++stage == S) {
-              stage = 0;
-              phase ^= 1u;
-            }
+          mbar_wait_spin(&empty[stage], phase ^ 1u);
+          if (DMPI_DBG(p, 4)) {  // experiment: no loads, barriers only (MMA runs on stale shared memory)
+            if (CG == 1 || rank == 0) mbar_arrive(&full[stage]);
+            else mbar_arrive_cluster(mapa_u32(smem_u32(&full[stage]), 0));
+          } else if (CG == 1) {
+            mbar_arrive_expect_tx(&full[stage], tx_bytes);
+            tma_load_4d(smem_a + stage * kABytes, amap, &full[stage], cb * kBlockK, cw, ch, n0);
+            tma_load_2d(smem_b + stage * Cfg::kBBytes, &p.b_map, &full[stage], koff + cb * kBlockK, tk.n_blk * BN);
+          } else {
+            // both CTAs report to the leader's barrier; the leader registers the bytes of the pair
+            const uint32_t lead_full = mapa_u32(smem_u32(&full[stage]), 0);
+            if (rank == 0) mbar_arrive_expect_tx(&full[stage], 2 * tx_bytes);
+            else mbar_arrive_cluster(lead_full);
+            tma_load_4d_pair(smem_a + stage * kABytes, amap, lead_full, cb * kBlockK, cw, ch, n0);
+            tma_load_2d_pair(smem_b + stage * Cfg::kBBytes, &p.b_map, lead_full, koff + cb * kBlockK,
+                             tk.n_blk * BN + rank * Cfg::kBRows);
+          }
+          if (++stage == S) {
+            stage = 0;
+            phase ^= 1u;
+          }
+          if (++cb == p.cblocks) {
+            cb = 0;
+            ++t;
           }
         }
       }
@@ -437,7 +454,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
         tc_fence_after_sync();
         const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
         uint32_t accum = 0;
-        for (int kb = 0; kb < num_kb; ++kb) {
+        for (int kb = kb_lo; kb < kb_hi; ++kb) {
           mbar_wait_spin(&full[stage], phase);
           tc_fence_after_sync();
           const uint32_t a_lo = a_lo_ring + static_cast<uint32_t>(stage) * (kABytes >> 4);
@@ -510,6 +527,47 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after_sync();
       const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(acc * BN);
+      const size_t sk_tile = static_cast<size_t>(kTileM) * BN;  // floats per partial tile
+      if (splitk) {
+        // split-K, phase A: park this CTA's fp32 partial tile (each thread its accumulator row), hand the accumulator
+        // back, then draw the tile's ticket; only the CTA that draws the last one carries on into the epilogue
+        float* mine = p.sk_part + (static_cast<size_t>(sk_split) * sk_units + sk_unit) * sk_tile + static_cast<size_t>(row) * BN;
+#pragma unroll
+        for (int sub = 0; sub < kSubs; ++sub) {
+#pragma unroll
+          for (int ci = 0; ci < CHs; ++ci) {
+            const int col_t = sub * SN + (hf * CHs + ci) * 32;
+            uint32_t v[32];
+            tmem_ld_32x32(t_addr + col_t, v);
+            tmem_ld_wait();
+            float4* dst = reinterpret_cast<float4*>(mine + col_t);
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+              dst[i] = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]), __uint_as_float(v[4 * i + 2]),
+                                   __uint_as_float(v[4 * i + 3]));
+          }
+        }
+        tc_fence_before_sync();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty[acc]);
+        __threadfence();
+        named_bar_sync(3, kCvtThreads);
+        if (threadIdx.x == 4 * 32) {
+          const uint32_t t = atomicAdd(&p.sk_tickets[sk_unit], 1u);
+          const bool last = t == static_cast<uint32_t>(p.splits - 1);
+          if (last) {
+            __threadfence();
+            p.sk_tickets[sk_unit] = 0u;  // re-armed for the next launch (every split of this tile has drawn)
+          }
+          *sk_flag = last ? 1u : 0u;
+        }
+        named_bar_sync(4, kCvtThreads + kStatThreads);  // the store / statistics warps learn the outcome here too
+        if (*sk_flag == 0u) {
+          acc ^= 1;
+          if (acc == 0) acc_phase ^= 1u;
+          continue;
+        }
+      }
 #pragma unroll
       for (int sub = 0; sub < kSubs; ++sub) {
         const uint32_t b = u & 1u;
@@ -525,7 +583,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
           const int col_t = sub * SN + cs * 32;     // column inside the tile
           const int col0 = tk.n_blk * BN + col_t;   // global output column
           uint32_t v[32];
-          tmem_ld_32x32(t_addr + col_t, v);
+          if (!splitk) tmem_ld_32x32(t_addr + col_t, v);
           const uint32_t half_base = obuf + (cs >> 1) * (kTileM * 128) + srow * 128;
           const int c16_0 = (cs & 1) * 4;
           uint4 ad[4];
@@ -533,10 +591,31 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
 #pragma unroll
             for (int i = 0; i < 4; ++i) ad[i] = lds128(half_base + (((c16_0 + i) ^ (srow & 7)) * 16));
           }
-          tmem_ld_wait();
           float f[32];
+          if (!splitk) {
+            tmem_ld_wait();
 #pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+            for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+          } else {
+            // split-K, phase B: the partial tiles of all splits added in split order (the same order on every launch)
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = 0.f;
+            const float* src0 = p.sk_part + static_cast<size_t>(sk_unit) * sk_tile + static_cast<size_t>(row) * BN + col_t;
+#pragma unroll 1
+            for (int sp = 0; sp < p.splits; ++sp) {
+              const float4* src = reinterpret_cast<const float4*>(src0 + static_cast<size_t>(sp) * sk_units * sk_tile);
+              float4 qv[8];
+#pragma unroll
+              for (int i = 0; i < 8; ++i) qv[i] = __ldcg(src + i);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                f[4 * i] += qv[i].x;
+                f[4 * i + 1] += qv[i].y;
+                f[4 * i + 2] += qv[i].z;
+                f[4 * i + 3] += qv[i].w;
+              }
+            }
+          }
           if (p.bias_mod > 0) {
             const int b0 = col0 % p.bias_mod;  // chunks never straddle a bias period (bias_mod % 32 == 0 or col < n_out)
 #pragma unroll
@@ -577,7 +656,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
               if (col0 + j < p.n_out) dst[j] = f[j];
           }
         }
-        if (sub == kSubs - 1) {
+        if (sub == kSubs - 1 && !splitk) {
           // every TMEM read of this accumulator has completed: hand it back to the MMA issuer
           tc_fence_before_sync();
           __syncwarp();
@@ -640,7 +719,14 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
         ++ua;
         if (ua % kSubs == 0) ahead.next(p);
       };
-      if (has_add && st == 0) {
+      // split-K: only the CTA that drew a tile's last ticket stores anything; the others still take part in the
+      // statistics bookkeeping below (with zero sums), so that every CTA of the grid draws its statistics ticket
+      bool sk_skip = false;
+      if (splitk) {
+        named_bar_sync(4, kCvtThreads + kStatThreads);  // the converters have decided (see phase A there)
+        sk_skip = *sk_flag == 0u;
+      }
+      if (has_add && st == 0 && !sk_skip) {
         ahead.init(p, CG, rank);
         prefetch_addend();
         prefetch_addend();
@@ -665,6 +751,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
           }
           st_nblk = tk.n_blk;
         }
+        if (sk_skip) continue;
 #pragma unroll
         for (int sub = 0; sub < kSubs; ++sub) {
           const uint32_t b = u & 1u;
@@ -733,9 +820,22 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
           }
           const int gcol = st_nblk * BN + c;
           if (p.stat_scratch != nullptr) {
-            // deterministic path: park the partial sums; the last CTA adds all of them up in CTA order (below)
-            p.stat_scratch[kStatHdr + (blockIdx.x * 2 + 0) * BN + c] = t1;
-            p.stat_scratch[kStatHdr + (blockIdx.x * 2 + 1) * BN + c] = t2;
+            // deterministic path: park the partial sums; the last CTAs add all of them up in CTA order (below)
+            if (!splitk) {
+              p.stat_scratch[kStatHdr + (blockIdx.x * 2 + 0) * BN + c] = t1;
+              p.stat_scratch[kStatHdr + (blockIdx.x * 2 + 1) * BN + c] = t2;
+            } else {
+              // split-K: WHICH CTA finalises a tile changes from launch to launch, so its sums go to the slot of the
+              // tile's first CTA (index sk_unit) and every other slot holds zeros - a fixed summation order again
+              if (!sk_skip) {
+                p.stat_scratch[kStatHdr + (sk_unit * 2 + 0) * BN + c] = t1;
+                p.stat_scratch[kStatHdr + (sk_unit * 2 + 1) * BN + c] = t2;
+              }
+              if (static_cast<int>(blockIdx.x) >= sk_units) {
+                p.stat_scratch[kStatHdr + (blockIdx.x * 2 + 0) * BN + c] = 0.f;
+                p.stat_scratch[kStatHdr + (blockIdx.x * 2 + 1) * BN + c] = 0.f;
+              }
+            }
           } else if (gcol < p.n_out) {
             atomicAdd(p.stat_sum + (gcol % p.stat_mod), t1);
             atomicAdd(p.stat_sq + (gcol % p.stat_mod), t2);
@@ -879,14 +979,14 @@ static int encode_view(CUtensorMap* map, const void* base, const dmpi_tensor4& v
   return encode_bf16_map(map, ptr, 4, v.dims, v.strides, box);
 }
 
-template <int BN, int CG>
+template <int BN, int CG, bool SK = false>
 static int launch_igemm(const ConvKernelParams& kp, int num_sms, cudaStream_t stream, long long scratch_bytes) {
   using Cfg = IgemmCfg<BN, CG>;
   static bool attr_set = false;
   static int max_clusters = 0;
   if (!attr_set) {
     cudaError_t e =
-        cudaFuncSetAttribute(igemm_kernel<BN, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+        cudaFuncSetAttribute(igemm_kernel<BN, CG, SK>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
     if (getenv("DMPI_TRACE")) fprintf(stderr, "[dmpi] cudaFuncSetAttribute: %s\n", cudaGetErrorString(e));
     if (e != cudaSuccess) {
       set_err(cudaGetErrorString(e));
@@ -906,7 +1006,7 @@ static int launch_igemm(const ConvKernelParams& kp, int num_sms, cudaStream_t st
       qc.attrs = qa;
       qc.numAttrs = 1;
       int n = 0;
-      e = cudaOccupancyMaxActiveClusters(&n, igemm_kernel<BN, CG>, &qc);
+      e = cudaOccupancyMaxActiveClusters(&n, igemm_kernel<BN, CG, SK>, &qc);
       if (e != cudaSuccess || n <= 0) {
         cudaGetLastError();
         n = num_sms / 2;
@@ -919,11 +1019,19 @@ static int launch_igemm(const ConvKernelParams& kp, int num_sms, cudaStream_t st
   const int units = (CG == 2 ? (kp.num_m_tiles + 1) / 2 : kp.num_m_tiles) * kp.num_n_tiles;  // tiles or pair tiles
   const int slots = CG == 2 ? max_clusters : num_sms;
   int grid = units < slots ? units : slots;
+  if (kp.splits > 1) {
+    if (CG != 1 || units * kp.splits > slots) {
+      set_err("igemm: split-K needs single-CTA tiles and units * splits <= number of SMs");
+      return -13;
+    }
+    grid = units * kp.splits;  // every CTA exactly one (tile, K slice); all resident at once
+  }
   // A grid that is a multiple of the N-tile count keeps n_blk fixed per CTA, so the BatchNorm partial sums stay
   // in registers for the whole kernel (one flush per CTA).
-  if (grid == slots && kp.num_n_tiles > 1 && kp.num_n_tiles <= slots) grid = (slots / kp.num_n_tiles) * kp.num_n_tiles;
+  if (kp.splits <= 1 && grid == slots && kp.num_n_tiles > 1 && kp.num_n_tiles <= slots)
+    grid = (slots / kp.num_n_tiles) * kp.num_n_tiles;
   // deterministic statistics need every CTA to stay on one N tile and the scratch to hold one partial per CTA
-  const bool one_n_tile_per_cta = grid == units || grid % kp.num_n_tiles == 0;
+  const bool one_n_tile_per_cta = grid == units || grid % kp.num_n_tiles == 0;  // (split-K: grid = units * splits)
   grid *= CG;
   ConvKernelParams kp2;
   const ConvKernelParams* kpp = &kp;
@@ -948,9 +1056,9 @@ static int launch_igemm(const ConvKernelParams& kp, int num_sms, cudaStream_t st
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    e = cudaLaunchKernelEx(&cfg, igemm_kernel<BN, CG>, *kpp);
+    e = cudaLaunchKernelEx(&cfg, igemm_kernel<BN, CG, SK>, *kpp);
   } else {
-    igemm_kernel<BN, CG><<<grid, kThreads, Cfg::kSmemBytes, stream>>>(*kpp);
+    igemm_kernel<BN, CG, SK><<<grid, kThreads, Cfg::kSmemBytes, stream>>>(*kpp);
     e = cudaGetLastError();
   }
   if (getenv("DMPI_TRACE")) {
@@ -977,6 +1085,8 @@ extern "C" dmpi_conv_plan* dmpi_conv_plan_create(const dmpi_conv_desc* desc) {
   plan->cached_a = plan->cached_b = plan->cached_o = plan->cached_add = nullptr;
   plan->stat_scratch = nullptr;
   plan->stat_scratch_bytes = 0;
+  plan->sk_scratch = nullptr;
+  plan->sk_scratch_bytes = 0;
   plan->maps_valid = false;
   plan->num_sms = 0;
   ConvKernelParams& kp = plan->params;
@@ -1026,6 +1136,14 @@ extern "C" void dmpi_conv_plan_destroy(dmpi_conv_plan* plan) { delete plan; }
 extern "C" void dmpi_conv_plan_set_stat_scratch(dmpi_conv_plan* plan, void* scratch, long long bytes) {
   plan->stat_scratch = scratch;
   plan->stat_scratch_bytes = scratch ? bytes : 0;
+}
+
+// Split-K scratch for dmpi_igemm_run* plans created with desc.splits > 1: device memory whose first 4 KiB (the tile
+// tickets) are ZERO at the first use - the kernel leaves them zero - followed by room for splits * tiles partial tiles of
+// 128 x bn floats; not shared with a concurrently running launch.
+extern "C" void dmpi_conv_plan_set_splitk_scratch(dmpi_conv_plan* plan, void* scratch, long long bytes) {
+  plan->sk_scratch = scratch;
+  plan->sk_scratch_bytes = scratch ? bytes : 0;
 }
 
 extern "C" int dmpi_conv_last_error(char* buf, int buflen) {
@@ -1158,6 +1276,25 @@ extern "C" int dmpi_igemm_run_add(dmpi_conv_plan* plan, const void* a, const voi
     }
     kp.has_add = 1;
   }
+  kp.splits = d.splits > 1 ? d.splits : 0;
+  kp.sk_part = nullptr;
+  kp.sk_tickets = nullptr;
+  if (kp.splits > 1) {
+    const int num_kb = d.ntaps * d.cblocks;
+    const int per = (num_kb + kp.splits - 1) / kp.splits;
+    const long long units = static_cast<long long>(kp.num_m_tiles) * kp.num_n_tiles;
+    const long long need = kSkHeaderBytes + static_cast<long long>(kp.splits) * units * kTileM * d.bn * 4;
+    if (d.patch || d.cta_group == 2 || d.out_mode != 0 || per * (kp.splits - 1) >= num_kb || units > kSkHeaderBytes / 4) {
+      set_err("igemm: split-K needs per-tap loads, one CTA per tile, bf16 output and a K range for every split");
+      return -13;
+    }
+    if (plan->sk_scratch == nullptr || plan->sk_scratch_bytes < need) {
+      set_err("igemm: split-K scratch missing or too small (dmpi_conv_plan_set_splitk_scratch)");
+      return -13;
+    }
+    kp.sk_tickets = static_cast<unsigned int*>(plan->sk_scratch);
+    kp.sk_part = reinterpret_cast<float*>(static_cast<char*>(plan->sk_scratch) + kSkHeaderBytes);
+  }
   kp.stat_scratch = (d.stat_mod > 0 && stat_sum != nullptr) ? static_cast<float*>(plan->stat_scratch) : nullptr;
   kp.bias = bias;
   kp.stat_sum = stat_sum;
@@ -1181,6 +1318,13 @@ extern "C" int dmpi_igemm_run_add(dmpi_conv_plan* plan, const void* a, const voi
     if (d.bn == 64) return launch_igemm<64, 2>(kp, plan->num_sms, s, plan->stat_scratch_bytes);
     set_err("igemm: bn must be 64, 128 or 256");
     return -2;
+  }
+  if (kp.splits > 1) {
+    switch (d.bn) {
+      case 64: return launch_igemm<64, 1, true>(kp, plan->num_sms, s, plan->stat_scratch_bytes);
+      case 128: return launch_igemm<128, 1, true>(kp, plan->num_sms, s, plan->stat_scratch_bytes);
+      default: return launch_igemm<256, 1, true>(kp, plan->num_sms, s, plan->stat_scratch_bytes);
+    }
   }
   switch (d.bn) {
     case 64: return launch_igemm<64, 1>(kp, plan->num_sms, s, plan->stat_scratch_bytes);

@@ -178,6 +178,7 @@ def _bind_cuda(lib) -> None:
     _sig(lib, "dmpi_conv_plan_create", VP, [C.POINTER(ConvDesc)])
     _sig(lib, "dmpi_conv_plan_destroy", None, [VP])
     _sig(lib, "dmpi_conv_plan_set_stat_scratch", None, [VP, VP, I64])
+    _sig(lib, "dmpi_conv_plan_set_splitk_scratch", None, [VP, VP, I64])
     _sig(lib, "dmpi_igemm_run", I, [VP, VP, VP, VP, VP, VP, VP, VP])
     _sig(lib, "dmpi_igemm_run_add", I, [VP, VP, VP, VP, VP, VP, VP, VP, I64, I64, I64, VP])
     _sig(lib, "dmpi_wgrad_run", I, [VP, VP, VP, VP, VP])

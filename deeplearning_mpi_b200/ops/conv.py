@@ -171,6 +171,49 @@ def _det_wgrad_plan(plan, device):
     return plan
 
 
+# Split-K for layers with only a handful of output tiles (the 2x2 / 1x1 feature maps at the end of ResNet-18 on 32x32
+# inputs): each CTA otherwise streams its whole reduction at the bandwidth one SM gets (55-120 GB/s), 20-35 us per launch
+# whatever the tile shape (DMPI_AUTOTUNE_LOG).  With splits the K range is spread over up to 8 CTAs per tile; the CTA
+# that finishes a tile last adds the fp32 partial tiles in split order (deterministic, bit-identical run to run).
+# OPT-IN (DMPI_SPLITK=1): correct (tests/test_conv_gpu.py::test_splitk_tiny_layers) but, as built, SLOWER end to end -
+# ResNet-18 32x32 batch 128: 1.95 ms/step with it, 1.40 ms without (same box): parking and re-reading the partial tiles
+# plus 64-144 resident 200 KB CTAs per tiny launch cost more than the streaming they save.  Kept as the starting point
+# for a cluster / DSMEM reduction; off by default.
+_SPLITK = os.environ.get("DMPI_SPLITK", "0") == "1"
+_SK_BYTES = 16 << 20  # 4 KiB of tickets + up to 148 partial tiles of 128 x 128 floats
+_sk_scratch = {}
+
+
+def _pick_splitk(n_out: int, num_kb: int, m_tiles: int):
+    """(bn, splits) for a split-K launch, or None."""
+    if not _SPLITK or _forced is not None or num_kb < 16 or n_out % 64:
+        return None
+    bn = 128 if n_out >= 128 else 64
+    units = m_tiles * -(-n_out // bn)
+    if units > 24:
+        return None
+    splits = min(8, 148 // units, num_kb // 4)
+    while splits > 1 and (splits - 1) * -(-num_kb // splits) >= num_kb:
+        splits -= 1
+    return (bn, splits) if splits >= 2 else None
+
+
+def _attach_splitk_scratch(plan, device) -> None:
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    t = _sk_scratch.get(key)
+    if t is None:
+        t = torch.zeros(_SK_BYTES, dtype=torch.uint8, device=device)  # tickets must start at zero; the kernel keeps them so
+        _sk_scratch[key] = t
+    N.cuda().dmpi_conv_plan_set_splitk_scratch(plan, t.data_ptr(), _SK_BYTES)
+
+
+def _m_tiles(ow: int, oh: int, n: int, flat: bool) -> int:
+    if flat:
+        return -(-(n * oh * ow) // 128)
+    bw, bh, bnn = choose_box(ow, oh, n)
+    return -(-ow // bw) * -(-oh // bh) * -(-n // bnn)
+
+
 def _run_igemm(plan, a, b, out, bias, stats, addend=None, add_strides=(0, 0, 0)):
     s0 = stats[0].data_ptr() if stats is not None else None
     s1 = stats[1].data_ptr() if stats is not None else None
@@ -382,11 +425,16 @@ def conv2d_fprop(x: torch.Tensor, w2d: torch.Tensor, R: int, S: int, stride: int
     heur = (bn, cg, ptile)
     skey = ("fprop", n, h, w, c, sn, sh, sw, kout, R, S, stride, pad, osn, osh, osw, bias is not None, stats is not None, relu)
 
+    sk = _pick_splitk(kout, R * S * (c // 64), _m_tiles(ow, oh, n, flat)) if (_tuned.get(skey) is None) else None
+
     def go(cfg, out, stats):
         bn, cg, ptile = cfg
+        splits = 0
+        if sk is not None and cfg == heur:
+            bn, cg, ptile, splits = sk[0], 1, None, sk[1]
         on, ohh, oww, oc, osn, osh, osw = _nhwc_meta(out)
         key = ("fprop", n, h, w, c, sn, sh, sw, kout, R, S, stride, pad, osn, osh, osw, bias is not None,
-               stats is not None, relu, bn, cg, ptile)
+               stats is not None, relu, bn, cg, ptile, splits)
 
         def build():
             d = N.ConvDesc()
@@ -436,10 +484,13 @@ def conv2d_fprop(x: torch.Tensor, w2d: torch.Tensor, R: int, S: int, stride: int
             d.stat_mod = kout if stats is not None else 0
             d.relu = int(relu)
             d.out_mode = 0
+            d.splits = splits
             return d
 
-
-        _run_igemm(_get_plan(key, build), x, w2d, out, bias, stats)
+        plan = _get_plan(key, build)
+        if splits:
+            _attach_splitk_scratch(plan, x.device)
+        _run_igemm(plan, x, w2d, out, bias, stats)
 
     cfg = _tuned.get(skey) if _forced is None else None
     if cfg is None:
@@ -496,9 +547,14 @@ def conv2d_dgrad(dy: torch.Tensor, wt2d: torch.Tensor, R: int, S: int, stride: i
             else:
                 add_strides = (asn, ash, asw)
 
+        sk = _pick_splitk(c, R * S * (k // 64), _m_tiles(iw, ih, n, flat)) if (_tuned.get(skey) is None) else None
+
         def go(cfg, out):
             bn, cg, ptile = cfg
-            key = ("dgrad1", n, oh, ow, k, sn, sh, sw, c, R, S, pad, osn, osh, osw, bn, cg, ptile)
+            splits = 0
+            if sk is not None and cfg == heur:
+                bn, cg, ptile, splits = sk[0], 1, None, sk[1]
+            key = ("dgrad1", n, oh, ow, k, sn, sh, sw, c, R, S, pad, osn, osh, osw, bn, cg, ptile, splits)
 
             def build():
                 d = N.ConvDesc()
@@ -531,12 +587,16 @@ def conv2d_dgrad(dy: torch.Tensor, wt2d: torch.Tensor, R: int, S: int, stride: i
                 d.b_rows, d.b_k = c, R * S * k
                 d.n_out, d.bn = c, bn
                 d.cta_group = cg
+                d.splits = splits
                 return d
 
+            plan = _get_plan(key, build)
+            if splits:
+                _attach_splitk_scratch(plan, dy.device)
             if addend is not None:
-                _run_igemm(_get_plan(key, build), dy, wt2d, out, None, None, addend, add_strides)
+                _run_igemm(plan, dy, wt2d, out, None, None, addend, add_strides)
             else:
-                _run_igemm(_get_plan(key, build), dy, wt2d, out, None, None)
+                _run_igemm(plan, dy, wt2d, out, None, None)
 
         cfg = _tuned.get(skey) if _forced is None else None
         if cfg is None:

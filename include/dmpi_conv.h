@@ -63,7 +63,8 @@ typedef struct {
   int k_out, c_total;
   int64_t w_ld;
   int tap_woff[DMPI_MAX_TAPS];
-  int splits; /* wgrad split-K factor over pixel tiles (0: auto) */
+  int splits; /* wgrad: split-K factor over pixel tiles (0: auto).  igemm: > 1 = split-K over the taps x channel blocks
+               * (needs dmpi_conv_plan_set_splitk_scratch; per-tap loads, cta_group 1, bf16 output) */
   int cta_group; /* igemm: 2 = CTA pairs (tcgen05.mma.cta_group::2, 256-row tiles; bn must be 128 or 256), else 1 */
   /* igemm patch mode (stride-1 R x S convolutions, halo = pad): the M tile is box_h output rows x box_w output columns;
    * ONE shared-memory patch of (box_h + 2*halo) x (box_w + 2*halo) input pixels per 64-channel block serves every
@@ -82,6 +83,10 @@ void dmpi_conv_plan_destroy(dmpi_conv_plan* plan);
  * (CTAs * 2 * bn + 64) * 4 bytes (512 KiB covers every configuration on 148 SMs) that no concurrently running launch
  * shares.  With it the per-channel sums are added in a fixed order (bit-reproducible); without it fp32 atomics. */
 void dmpi_conv_plan_set_stat_scratch(dmpi_conv_plan* plan, void* scratch, long long bytes);
+
+/* Split-K scratch of igemm plans with desc.splits > 1: 4 KiB of tickets (zero at first use, left zero by the kernel)
+ * followed by splits * tiles * 128 * bn floats of partial tiles; not shared with a concurrently running launch. */
+void dmpi_conv_plan_set_splitk_scratch(dmpi_conv_plan* plan, void* scratch, long long bytes);
 
 /* D = A (*) B with fused bias / ReLU / BatchNorm statistics.  Returns 0 or a negative error. */
 int dmpi_igemm_run(dmpi_conv_plan* plan, const void* a, const void* b, void* out, const float* bias,

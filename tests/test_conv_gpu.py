@@ -398,3 +398,46 @@ def test_autotune_picks_and_caches():
     assert len(keys) == 1 and C._tuned[keys[0]] in C.tile_candidates(512, 1, 1, 1, 0, 256, 14, 14)
     y2 = C.conv2d_fprop(x, _w2d(wt), 1, 1)
     assert torch.equal(y1, y2)
+
+
+SPLITK_CASES = [
+    (128, 2, 2, 256, 256, 3, 1, 1),    # ResNet-18 / 32x32 layer3: 4 tiles, K = 2304
+    (128, 1, 1, 512, 512, 3, 1, 1),    # layer4: ONE tile of pixels, K = 4608
+    (128, 4, 4, 128, 256, 3, 2, 1),    # stride-2 entry of layer3 (four parity views)
+    (64, 2, 2, 1024, 64, 1, 1, 0),     # flat 1x1 into a 64-wide tile
+]
+
+
+@pytest.mark.parametrize("case", SPLITK_CASES)
+def test_splitk_tiny_layers(case, monkeypatch):
+    """Layers with a handful of output tiles run split-K (several CTAs per tile, partial tiles added in split order):
+    same numbers as the fp32 reference, BatchNorm statistics intact, residual addend in the dgrad epilogue, and
+    bit-identical from launch to launch."""
+    from deeplearning_mpi_b200.ops import conv as C
+
+    monkeypatch.setattr(C, "_SPLITK", True)  # opt-in path (off by default: see ops/conv.py)
+    _torch_setup()
+    n, h, w, c, k, R, stride, pad = case
+    oh = (h + 2 * pad - R) // stride + 1
+    ow = (w + 2 * pad - R) // stride + 1
+    assert C._pick_splitk(k, R * R * (c // 64), C._m_tiles(ow, oh, n, R == 1 and stride == 1)) is not None
+    x = _rand(n, h, w, c)
+    wt = _rand(k, c, R, R, scale=(c * R * R) ** -0.5)
+    ref = F.conv2d(x.float().permute(0, 3, 1, 2), wt.float(), stride=stride, padding=pad).permute(0, 2, 3, 1)
+    outs = []
+    for _ in range(2):
+        ssum, ssq = torch.zeros(k, device=_dev()), torch.zeros(k, device=_dev())
+        y = C.conv2d_fprop(x, _w2d(wt), R, R, stride, pad, stats=(ssum, ssq))
+        outs.append((y.clone(), ssum.clone(), ssq.clone()))
+    _close(outs[0][0], ref, 1e-2, f"splitk fprop{case}")
+    yf = outs[0][0].float()
+    _close(outs[0][1], yf.sum(dim=(0, 1, 2)), 2e-3, "splitk stats sum")
+    _close(outs[0][2], (yf * yf).sum(dim=(0, 1, 2)), 2e-3, "splitk stats sq")
+    assert all(torch.equal(a, b) for a, b in zip(outs[0], outs[1])), "split-K result differs between two launches"
+    if stride == 1:
+        dy = _rand(n, oh, ow, k)
+        add = _rand(n, h, w, c)
+        dx = C.conv2d_dgrad(dy, _wt2d(wt), R, R, stride, pad, (h, w), addend=add)
+        ref_dx = torch.nn.grad.conv2d_input((n, c, h, w), wt.float(), dy.float().permute(0, 3, 1, 2), stride=stride,
+                                            padding=pad).permute(0, 2, 3, 1) + add.float()
+        _close(dx, ref_dx, 1e-2, f"splitk dgrad+add{case}")
