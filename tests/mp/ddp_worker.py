@@ -112,6 +112,49 @@ xe = torch.randn(2, 3, 32, 32)
 with torch.no_grad():
     assert torch.allclose(ddp(xe), stock_ddp(xe), atol=1e-4)
 
+# control-plane helpers: rank 0's object reaches every rank; the segmentation dataset shares rank 0's palette scan
+obj = dist.broadcast_object({"palette": [0, 255], "who": rank} if rank == 0 else None, src=0)
+assert obj == {"palette": [0, 255], "who": 0}
+import numpy as np  # noqa: E402
+from PIL import Image  # noqa: E402
+
+from deeplearning_mpi_b200.utils.data import SegmentationFolder  # noqa: E402
+
+ds_root = os.path.join(out_dir, "seg")
+if rank == 0:
+    os.makedirs(os.path.join(ds_root, "images"))
+    os.makedirs(os.path.join(ds_root, "masks"))
+    rng = np.random.default_rng(0)
+    for i in range(4):
+        Image.fromarray(rng.integers(0, 255, (16, 16, 3), dtype=np.uint8)).save(os.path.join(ds_root, "images", f"a{i}.png"))
+        Image.fromarray(((rng.random((16, 16)) > 0.5) * 200).astype(np.uint8)).save(os.path.join(ds_root, "masks", f"a{i}.png"))
+tdist.barrier()
+ds = SegmentationFolder.shared(os.path.join(ds_root, "images"), os.path.join(ds_root, "masks"), scale=0.5)
+assert ds.mask_values == [0, 200] and len(ds) == 4 and ds[1]["mask"].shape == (8, 8)
+
+# the bucket launch order was re-derived from the first backward pass and agrees on both ranks
+assert sorted(ddp.launch_order) == list(range(ddp.n_buckets))
+lo = gathered(torch.tensor(ddp.launch_order, dtype=torch.int64))
+assert torch.equal(lo[0], lo[1]) and ddp._order_final
+
+# frozen parameters: wrapped, trained around, never bucketed or changed
+torch.manual_seed(7)
+fz = resnet18(num_classes=10)
+for p_ in fz.layer1.parameters():
+    p_.requires_grad_(False)
+before = [p_.detach().clone() for p_ in fz.layer1.parameters()]
+fz_ddp = DistributedDataParallel(fz)
+fz_opt = optim.SGD([p_ for p_ in fz_ddp.parameters() if p_.requires_grad], lr=0.05, momentum=0.9)
+for _ in range(2):
+    fz_opt.zero_grad()
+    crit(fz_ddp(torch.randn(4, 3, 32, 32)), torch.randint(0, 10, (4,))).backward()
+    fz_opt.step()
+assert all(torch.equal(a, b.detach()) for a, b in zip(before, fz.layer1.parameters()))
+assert len(fz_ddp._slots) == sum(1 for p_ in fz.parameters() if p_.requires_grad) < len(fz_ddp.arena.slots)
+for n_, p_ in fz_ddp.named_parameters():
+    a, b = gathered(p_.detach())
+    assert torch.equal(a, b), f"param {n_} diverged with frozen layers"
+
 # mismatching models must be rejected at wrap time
 try:
     bad = resnet18(num_classes=10 if rank == 0 else 11)
