@@ -386,6 +386,12 @@ class DistributedDataParallel(nn.Module):
 
     def __del__(self):  # pragma: no cover
         try:
+            if getattr(self, "_hx", None) is not None:
+                # the C++ hooks stay installed on the parameters: disarmed, they never touch the reducer again
+                self._ext.arm(self._hx, False)
+        except Exception:
+            pass
+        try:
             if getattr(self, "_reducer", None):
                 N.host().dmpi_reducer_destroy(self._reducer)
             if getattr(self, "_cuda_red", None):
