@@ -430,3 +430,34 @@ def test_cpp_autograd_hooks_drive_the_reducer():
     with pytest.raises(RuntimeError, match="incomplete"):
         net(x).square().sum().backward()
     host.dmpi_reducer_destroy(red)
+
+
+def test_tile_candidates_and_splitk_planner():
+    """Pure-Python planning helpers of ops/conv.py: the candidate list the autotuner / force_config draw from, and the
+    split-K chooser (every split must own at least one K block, the grid must fit the device)."""
+    from deeplearning_mpi_b200.ops import conv as CV
+
+    c64 = CV.tile_candidates(64, 3, 3, 1, 1, 64, 56, 56)
+    assert {(bn, cg) for bn, cg, _ in c64} == {(64, 1), (64, 2)} and any(pt is not None for _, _, pt in c64)
+    wide = CV.tile_candidates(512, 1, 1, 1, 0, 256, 14, 14)
+    assert {(bn, cg) for bn, cg, _ in wide} == {(64, 1), (64, 2), (128, 1), (128, 2), (256, 1), (256, 2)}
+    assert all(pt is None for _, _, pt in wide)                      # no patch mode for 1x1
+    assert all(bn <= 128 for bn, _, _ in CV.tile_candidates(128, 3, 3, 1, 1, 128, 28, 28))
+    with CV.force_config(128, 2, False):
+        assert CV._forced == (128, 2, False) and CV._pick_splitk(256, 36, 4) is None   # forcing disables split-K
+    assert CV._forced is None
+    old = CV._SPLITK
+    CV._SPLITK = True
+    try:
+        for n_out, num_kb, m_tiles in [(256, 36, 4), (512, 72, 1), (64, 16, 2), (128, 18, 16), (256, 17, 3)]:
+            sk = CV._pick_splitk(n_out, num_kb, m_tiles)
+            assert sk is not None
+            bn, splits = sk
+            units = m_tiles * -(-n_out // bn)
+            per = -(-num_kb // splits)
+            assert 2 <= splits <= 8 and units * splits <= 148 and per * (splits - 1) < num_kb
+        assert CV._pick_splitk(512, 72, 98) is None      # enough tiles already
+        assert CV._pick_splitk(64, 9, 2) is None         # reduction too short
+    finally:
+        CV._SPLITK = old
+    assert CV._m_tiles(2, 2, 128, False) == 4 and CV._m_tiles(1, 1, 128, True) == 1
